@@ -1,0 +1,200 @@
+/* vkr_passes.h — C ABI of the B200 (sm_100a) image-space passes.
+ *
+ * One entry point per rendergraph task of vk-renderer's image-space chain.  Each entry is
+ * what the task's exec callback (the lambda handed to RenderGraph::add_task, reference
+ * src/rendergraph/rendergraph.hpp:116-128) calls instead of recording
+ * bind_pipeline / write_set / push_constants / dispatch|draw on a gpu::CmdContext.
+ *
+ * Conventions:
+ *   - images are headless linear device buffers described by VkrImage; the callee BORROWS
+ *     them (never frees, never retains past the call's stream work);
+ *   - params structs mirror the UBO + push-constant layout of the reference task
+ *     (column-major mat4 as float[16], exactly what glm::mat4 holds);
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*; NULL = the
+ *     legacy default stream), holds no mutable global state and is re-entrant per stream;
+ *   - returns 0 on success, negative VkrStatus on failure; no exceptions cross the ABI.
+ *     The C++ host shim turns non-zero into std::runtime_error, the reference's error
+ *     convention (src/gpu/common.hpp:9, src/downsample_pass.cpp:38,:49).
+ *   - there is NO CPU fallback: without a CUDA device every compute entry returns
+ *     VKR_ERR_CUDA.
+ */
+#ifndef VKR_PASSES_H_INCLUDED
+#define VKR_PASSES_H_INCLUDED
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VKR_MAX_MIPS 16
+
+typedef enum VkrStatus {
+  VKR_OK = 0,
+  VKR_ERR_INVALID_ARGUMENT = -1, /* null pointer, wrong format, bad mip window */
+  VKR_ERR_SIZE_MISMATCH = -2,    /* reference: "Output textures have different sizes" */
+  VKR_ERR_CUDA = -3,             /* launch / runtime error; see vkr_last_error() */
+  VKR_ERR_UNSUPPORTED = -4
+} VkrStatus;
+
+/* Values are VkFormat numbers so descriptors read like gpu::ImageInfo
+ * (reference src/scene_renderer.cpp:15-27, src/gtao.cpp:26-39, src/advanced_ssr.cpp:62-92). */
+typedef enum VkrFormat {
+  VKR_FORMAT_R8G8B8A8_UNORM = 37,
+  VKR_FORMAT_R8G8B8A8_SRGB = 43,
+  VKR_FORMAT_R16_UNORM = 70,
+  VKR_FORMAT_R16_SFLOAT = 76,
+  VKR_FORMAT_R16G16_UNORM = 77,
+  VKR_FORMAT_R16G16_SFLOAT = 83,
+  VKR_FORMAT_R16G16B16A16_UNORM = 91,
+  VKR_FORMAT_R16G16B16A16_SFLOAT = 97,
+  VKR_FORMAT_R32_SFLOAT = 100,
+  VKR_FORMAT_R32G32B32A32_SFLOAT = 109,
+  VKR_FORMAT_D24_UNORM_S8_UINT = 129 /* u32 texel, depth in the low 24 bits (src/main.cpp:139) */
+} VkrFormat;
+
+/* Replaces gpu::ImagePtr + gpu::ImageViewRange (reference src/gpu/resource_info.hpp:11-45).
+ * One allocation holds the whole mip chain. */
+typedef struct VkrImage {
+  void* base;                       /* device pointer */
+  uint32_t width, height;           /* mip 0 extent; mip i = max(1, dim >> i) */
+  uint32_t format;                  /* VkrFormat */
+  uint32_t mip_count;
+  uint64_t mip_offset[VKR_MAX_MIPS]; /* bytes from base */
+  uint32_t row_pitch[VKR_MAX_MIPS];  /* bytes; multiple of 16 */
+} VkrImage;
+
+/* SSSR_trace / SSSR_filter: UBO TraceParams (reference src/advanced_ssr.cpp:138-145) +
+ * push constants {max_roughness} (:159-163) / {render_flags} (:328-338). */
+#define VKR_SSR_NORMALIZE_REFLECTIONS 1u
+#define VKR_SSR_ACCUMULATE_REFLECTIONS 2u
+#define VKR_SSR_BILATERAL_FILTER 4u
+typedef struct VkrTraceParams {
+  float normal_mat[16];
+  uint32_t frame_random;
+  float fovy, aspect, znear, zfar;
+  float max_roughness;
+  uint32_t render_flags;
+} VkrTraceParams;
+
+/* SSSR_blur: UBO {inverse_camera, prev_inverse_camera, fovy_aspect_znear_zfar} +
+ * push {max_roughness, accumulate, disable_blur} (reference src/advanced_ssr.cpp:388-401). */
+typedef struct VkrBlurParams {
+  float inverse_camera[16];
+  float prev_inverse_camera[16];
+  float fovy_aspect_znear_zfar[4];
+  float max_roughness;
+  uint32_t accumulate;
+  uint32_t disable_blur;
+} VkrBlurParams;
+
+/* GTAO_main / GTAO_filter: UBO GTAOParams (reference src/gtao.hpp:12-18) + push
+ * {angle_offset, weight_ratio, use_mis, two_directions, reflections_only} (src/gtao.cpp:101-113);
+ * the filter uses znear/zfar only (:211-216). */
+typedef struct VkrGtaoParams {
+  float normal_mat[16];
+  float fovy, aspect, znear, zfar;
+  float angle_offset, weight_ratio;
+  uint32_t use_mis, two_directions, reflections_only;
+} VkrGtaoParams;
+
+/* GTAO_accumulate: UBO AccumConstants + push {clear_history} (reference src/gtao.cpp:300-313). */
+typedef struct VkrAccumParams {
+  float inverse_camera[16];
+  float prev_inverse_camera[16];
+  float mvp[16];
+  float fovy_aspect_znear_zfar[4];
+  uint32_t clear_history;
+} VkrAccumParams;
+
+/* DeferedShading: UBO ShaderConstants (reference src/defered_shading.cpp:4-12) + push
+ * {min_max_roughness, show_ao} (:68-72).  shadow_mvp is carried but, like the reference
+ * shader, never used. */
+typedef struct VkrShadingParams {
+  float inverse_camera[16];
+  float camera[16];
+  float shadow_mvp[16];
+  float fovy, aspect, znear, zfar;
+  float min_max_roughness[2];
+  uint32_t show_ao;
+} VkrShadingParams;
+
+/* TAA: UBO TAAParams (reference src/taa.cpp:24-30). */
+typedef struct VkrTaaParams {
+  float inverse_camera[16];
+  float prev_inverse_camera[16];
+  float fovy_aspect_znear_zfar[4];
+} VkrTaaParams;
+
+/* ---- utilities ---------------------------------------------------------------- */
+const char* vkr_version(void);
+/* Thread-local text of the last failure on this thread ("" if none). */
+const char* vkr_last_error(void);
+/* Bytes per texel of a VkrFormat (0 if unknown). */
+uint32_t vkr_format_texel_size(uint32_t format);
+/* Fills width/height/format/mip_count/mip_offset/row_pitch of *img (base untouched) with the
+ * layout every pass expects (pitch = align16(width*bpp), mip offsets 256-byte aligned) and
+ * returns the allocation size in bytes (0 on bad arguments).  Replaces VMA image creation
+ * behind RenderGraph::create_image (reference src/rendergraph/rendergraph.cpp:341-369). */
+uint64_t vkr_image_layout(uint32_t width, uint32_t height, uint32_t format, uint32_t mip_count, VkrImage* img);
+/* floor(log2(max(w,h))) + 1 — the mip count Gbuffer gives its depth images
+ * (reference src/scene_renderer.cpp:13). */
+uint32_t vkr_full_mip_count(uint32_t width, uint32_t height);
+/* reference src/advanced_ssr.cpp:8-34: 128 x vec4, .x = halton(i+1,2), .y = halton(i+1,3). Host memory. */
+void vkr_halton23_seq(uint32_t count, float* out_vec4);
+
+/* ---- Hi-Z: DownsamplePass (reference src/downsample_pass.cpp) ------------------- */
+/* Task "DownsampleGbuffer" (:63-90, shaders/advanced_ssr/downsample_gbuffer.frag):
+ * depth mip0 -> depth mip1 (2x2 min), normal/velocity of the min-depth texel -> out_*. */
+int vkr_downsample_gbuffer(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity,
+                           const VkrImage* out_normal, const VkrImage* out_velocity, void* stream);
+/* Tasks "DownsampleDepth" x (L - src_mip - 1) (:107-130, shaders/advanced_ssr/depth_mips.frag):
+ * builds mips src_mip+1 .. L-1 from mip src_mip. */
+int vkr_depth_mips(const VkrImage* depth, uint32_t src_mip, void* stream);
+/* Fused DownsamplePass::run (:133-143): both of the above in one launch + one tail launch. */
+int vkr_hiz_build(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity,
+                  const VkrImage* out_normal, const VkrImage* out_velocity, void* stream);
+
+/* ---- AdvancedSSR (reference src/advanced_ssr.cpp) -------------------------------- */
+/* Task "SSR_preintegrate" (:95-114, preintegrate.comp) -> R32_SFLOAT LUT. */
+int vkr_pdf_preintegrate(const VkrImage* out_pdf, void* stream);
+/* Task "BRDF_preintegrate" (:116-136, preintegrate_ssr.comp) -> R16G16_SFLOAT LUT.
+ * halton_vec4x128: DEVICE pointer to 128 x float4 (the Halton UBO). */
+int vkr_brdf_preintegrate(const float* halton_vec4x128, const VkrImage* out_brdf, void* stream);
+/* Task "SSSR_trace" (:147-214, trace.comp). depth = whole D24 image (the callee applies the
+ * mips 1..L-1 view); out_occlusion = gtao.raw. */
+int vkr_sssr_trace(const VkrTraceParams* p, const VkrImage* depth, const VkrImage* dnormal, const VkrImage* material,
+                   const float* halton_vec4x128, const VkrImage* pdf_lut, const VkrImage* out_rays,
+                   const VkrImage* out_occlusion, void* stream);
+/* Task "SSSR_filter" (:308-369, filter.comp). */
+int vkr_sssr_filter(const VkrTraceParams* p, const VkrImage* rays, const VkrImage* depth, const VkrImage* albedo,
+                    const VkrImage* normal, const VkrImage* material, const VkrImage* out_reflections, void* stream);
+/* Task "SSSR_blur" (:371-438, blur.comp). */
+int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
+                  const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity,
+                  const VkrImage* prev_depth, const VkrImage* out_blurred, void* stream);
+
+/* ---- GTAO (reference src/gtao.cpp) ------------------------------------------------ */
+/* Task "GTAO_main" (:84-148, gtao/main.comp); raw is read-modify-write. depth_lod = GTAO::depth_lod (:23). */
+int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
+                  const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, void* stream);
+/* Task "GTAO_filter" (:198-239, gtao/filter.comp). */
+int vkr_gtao_filter(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
+                    uint32_t depth_lod, void* stream);
+/* Task "GTAO_accumulate" (:286-347, gtao/accum.comp). */
+int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth,
+                        const VkrImage* filtered, const VkrImage* accumulated, const VkrImage* dvelocity,
+                        const VkrImage* history, uint32_t depth_lod, void* stream);
+
+/* ---- DeferedShadingPass / TAA ------------------------------------------------------ */
+/* Task "DeferedShading" (reference src/defered_shading.cpp:47-118, defered_shading/shader.frag). */
+int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* albedo, const VkrImage* normal,
+                         const VkrImage* material, const VkrImage* depth, const VkrImage* occlusion,
+                         const VkrImage* brdf_lut, const VkrImage* reflections, const VkrImage* out_color, void* stream);
+/* Task "TAA" (reference src/taa.cpp:14-63, taa/resolve.comp). */
+int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
+                    const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VKR_PASSES_H_INCLUDED */

@@ -1,0 +1,120 @@
+// api.cu — C-ABI utilities: errors, image layout, host-built constant tables.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include "common.cuh"
+
+namespace vkr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return VKR_ERR_CUDA;
+  }
+  return VKR_OK;
+}
+
+CamK make_cam(float fovy, float aspect, float znear, float zfar) {
+  CamK c;
+  c.aspect = aspect; c.znear = znear; c.zfar = zfar;
+  c.tg = std::tan(fovy / 2);  // gbuffer_encode.glsl:60,:76 — hoisted, same float the shader would form
+  return c;
+}
+
+// sRGB EOTF table, built in double precision on the host, one copy per device.
+static std::mutex g_tab_mutex;
+static float* g_srgb_dev[64] = {nullptr};
+
+const float* srgb_decode_table_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(g_tab_mutex);
+  if (!g_srgb_dev[dev]) {
+    float host[256];
+    for (int i = 0; i < 256; i++) {
+      double c = i / 255.0;
+      host[i] = (float)((c <= 0.04045) ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
+    }
+    float* d = nullptr;
+    if (cudaMalloc(&d, sizeof(host)) != cudaSuccess) return nullptr;
+    if (cudaMemcpy(d, host, sizeof(host), cudaMemcpyHostToDevice) != cudaSuccess) { cudaFree(d); return nullptr; }
+    g_srgb_dev[dev] = d;
+  }
+  return g_srgb_dev[dev];
+}
+
+}  // namespace vkr
+
+extern "C" {
+
+const char* vkr_version(void) { return "vkr_b200 0.1 (sm_100a)"; }
+const char* vkr_last_error(void) { return vkr::g_err; }
+
+uint32_t vkr_format_texel_size(uint32_t f) {
+  switch (f) {
+    case VKR_FORMAT_R16_UNORM: case VKR_FORMAT_R16_SFLOAT: return 2;
+    case VKR_FORMAT_R8G8B8A8_UNORM: case VKR_FORMAT_R8G8B8A8_SRGB: case VKR_FORMAT_R16G16_UNORM:
+    case VKR_FORMAT_R16G16_SFLOAT: case VKR_FORMAT_R32_SFLOAT: case VKR_FORMAT_D24_UNORM_S8_UINT: return 4;
+    case VKR_FORMAT_R16G16B16A16_UNORM: case VKR_FORMAT_R16G16B16A16_SFLOAT: return 8;
+    case VKR_FORMAT_R32G32B32A32_SFLOAT: return 16;
+  }
+  return 0;
+}
+
+uint32_t vkr_full_mip_count(uint32_t w, uint32_t h) {
+  uint32_t m = w > h ? w : h, n = 0;
+  while (m) { n++; m >>= 1; }
+  return n;
+}
+
+uint64_t vkr_image_layout(uint32_t width, uint32_t height, uint32_t format, uint32_t mip_count, VkrImage* img) {
+  uint32_t bpp = vkr_format_texel_size(format);
+  if (!img || !bpp || !width || !height || mip_count < 1 || mip_count > VKR_MAX_MIPS) return 0;
+  if (mip_count > vkr_full_mip_count(width, height)) return 0;
+  img->width = width; img->height = height; img->format = format; img->mip_count = mip_count;
+  uint64_t off = 0;
+  for (uint32_t i = 0; i < VKR_MAX_MIPS; i++) { img->mip_offset[i] = 0; img->row_pitch[i] = 0; }
+  for (uint32_t i = 0; i < mip_count; i++) {
+    uint32_t w = vkr::mip_dim(width, i), h = vkr::mip_dim(height, i);
+    uint32_t pitch = (w * bpp + 15u) & ~15u;
+    img->mip_offset[i] = off;
+    img->row_pitch[i] = pitch;
+    off += (uint64_t)pitch * h;
+    off = (off + 255u) & ~(uint64_t)255u;
+  }
+  return off;
+}
+
+// reference src/advanced_ssr.cpp:8-34 (radical inverse evaluated in fp32, index + 1)
+static float halton_elem(uint32_t index, uint32_t base) {
+  float f = 1, r = 0;
+  uint32_t current = index;
+  do {
+    f = f / base;
+    r = r + f * (current % base);
+    current = (uint32_t)std::floor(current / float(base));
+  } while (current > 0);
+  return r;
+}
+
+void vkr_halton23_seq(uint32_t count, float* out) {
+  for (uint32_t i = 0; i < count; i++) {
+    out[4 * i] = halton_elem(i + 1, 2);
+    out[4 * i + 1] = halton_elem(i + 1, 3);
+    out[4 * i + 2] = 0.f; out[4 * i + 3] = 0.f;
+  }
+}
+
+}  // extern "C"

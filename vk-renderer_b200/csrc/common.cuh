@@ -1,0 +1,232 @@
+// common.cuh — shared device/host helpers of the sm_100a image-space passes.
+//
+// Texel codecs and the sampler follow the semantics pinned in SURVEY.md App. A
+// (reference src/gpu/samplers.hpp:36-55 DEFAULT_SAMPLER = LINEAR / CLAMP_TO_EDGE;
+// D24 texel layout reference src/main.cpp:139):
+//   bilinear: x = u*W - 0.5, i0 = floor(x), w = x - i0, clamp indices to the edge,
+//   sRGB decoded before weighting, mix in x then y; texelFetch out of range = 0.
+// Coordinate arithmetic that selects texels uses the non-contracting intrinsics
+// (__fmul_rn/__fsub_rn) so the discrete choice is identical to an unfused evaluation.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "../../include/vkr_passes.h"
+
+namespace vkr {
+
+// ---- host side ---------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+const float* srgb_decode_table_device();  // 256 floats on the current device (built once per device)
+
+// One mip level of an image as the kernels see it.
+struct Mip {
+  const unsigned char* p;
+  int w, h;
+  unsigned pitch;
+};
+
+inline int mip_dim(uint32_t d, uint32_t lod) { uint32_t v = d >> lod; return v ? (int)v : 1; }
+
+inline bool image_ok(const VkrImage* im, uint32_t format) {
+  return im && im->base && im->format == format && im->mip_count >= 1 && im->mip_count <= VKR_MAX_MIPS && im->width && im->height;
+}
+
+inline Mip make_mip(const VkrImage* im, uint32_t lod) {
+  Mip m;
+  m.p = (const unsigned char*)im->base + im->mip_offset[lod];
+  m.w = mip_dim(im->width, lod);
+  m.h = mip_dim(im->height, lod);
+  m.pitch = im->row_pitch[lod];
+  return m;
+}
+
+struct CamK {  // camera constants; tg = tanf(fovy/2) evaluated once on the host
+  float aspect, znear, zfar, tg;
+};
+CamK make_cam(float fovy, float aspect, float znear, float zfar);
+
+struct Mat4 { float m[16]; };  // column-major
+inline Mat4 make_mat(const float* p) { Mat4 r; for (int i = 0; i < 16; i++) r.m[i] = p[i]; return r; }
+
+#ifdef __CUDACC__
+// ---- device side -------------------------------------------------------------
+#define VKR_PI 3.1415926535897932384626433832795f
+
+// GLSL-spec min/max (NaN behaviour differs from fminf/fmaxf).
+__device__ __forceinline__ float gmin(float x, float y) { return (y < x) ? y : x; }
+__device__ __forceinline__ float gmax(float x, float y) { return (x < y) ? y : x; }
+__device__ __forceinline__ float gclamp(float x, float lo, float hi) { return gmin(gmax(x, lo), hi); }
+__device__ __forceinline__ float gmix(float a, float b, float t) { return a * (1.0f - t) + b * t; }
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ f3 operator/(f3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float len3(f3 a) { return sqrtf(dot3(a, a)); }
+__device__ __forceinline__ f3 norm3(f3 a) { float s = 1.0f / sqrtf(dot3(a, a)); return a * s; }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) { return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+__device__ __forceinline__ f3 mix3(f3 a, f3 b, float t) { return a * (1.0f - t) + b * t; }
+__device__ __forceinline__ f3 reflect3(f3 I, f3 N) { return I - (2.0f * dot3(N, I)) * N; }
+
+// M * (v, w)  — column-major, left-to-right accumulation like the oracle.
+__device__ __forceinline__ f3 mul_m4(const Mat4& M, f3 v, float w) {
+  return mk3(M.m[0] * v.x + M.m[4] * v.y + M.m[8] * v.z + M.m[12] * w,
+             M.m[1] * v.x + M.m[5] * v.y + M.m[9] * v.z + M.m[13] * w,
+             M.m[2] * v.x + M.m[6] * v.y + M.m[10] * v.z + M.m[14] * w);
+}
+__device__ __forceinline__ float4 mul_m4_4(const Mat4& M, f3 v, float w) {
+  return make_float4(M.m[0] * v.x + M.m[4] * v.y + M.m[8] * v.z + M.m[12] * w,
+                     M.m[1] * v.x + M.m[5] * v.y + M.m[9] * v.z + M.m[13] * w,
+                     M.m[2] * v.x + M.m[6] * v.y + M.m[10] * v.z + M.m[14] * w,
+                     M.m[3] * v.x + M.m[7] * v.y + M.m[11] * v.z + M.m[15] * w);
+}
+
+// ---- shared shader math (reference src/shaders/include/gbuffer_encode.glsl) -----
+__device__ __forceinline__ float sign_nz(float k) { return (k >= 0.0f) ? 1.0f : -1.0f; }
+
+__device__ __forceinline__ f3 decode_normal(float u, float v) {           // gbuffer_encode.glsl:29-37
+  u = 2.f * u - 1.f; v = 2.f * v - 1.f;
+  f3 n = mk3(u, v, 1.0f - fabsf(u) - fabsf(v));
+  if (n.z < 0.0f) {
+    float tx = (1.0f - fabsf(n.y)) * sign_nz(n.x);
+    float ty = (1.0f - fabsf(n.x)) * sign_nz(n.y);
+    n.x = tx; n.y = ty;
+  }
+  return norm3(n);
+}
+
+__device__ __forceinline__ float linearize_depth2(float d, float n, float f) {   // :53-56
+  return n * f / (d * (f - n) - f);
+}
+
+__device__ __forceinline__ f3 reconstruct_view_vec(float u, float v, float d, const CamK& c) {  // :58-69
+  float z = linearize_depth2(d, c.znear, c.zfar);
+  float xd = 2 * u - 1;
+  float yd = 2 * v - 1;
+  float x = -(xd) * (z * c.aspect * c.tg);
+  float y = -(yd) * (z * c.tg);
+  return mk3(x, y, z);
+}
+
+__device__ __forceinline__ f3 project_view_vec(f3 v, const CamK& c) {                          // :75-84
+  float n = c.znear, f = c.zfar;
+  float z = v.z;
+  float depth = f / (f - n) + f * n / (z * (f - n));
+  float pu = v.x / (-v.z * c.tg * c.aspect);
+  float pv = v.y / (-z * c.tg);
+  return mk3(0.5f * pu + 0.5f, 0.5f * pv + 0.5f, depth);
+}
+
+// ---- texel decode ----------------------------------------------------------------
+__device__ __forceinline__ float d24_to_float(uint32_t k) { return __fdiv_rn((float)(k & 0xFFFFFFu), 16777215.0f); }
+__device__ __forceinline__ float unorm16_to_float(uint32_t k) { return __fdiv_rn((float)k, 65535.0f); }
+__device__ __forceinline__ float unorm8_to_float(uint32_t k) { return __fdiv_rn((float)k, 255.0f); }
+
+__device__ __forceinline__ uint32_t ld32(const Mip& m, int x, int y) {
+  return __ldg((const uint32_t*)(m.p + (size_t)y * m.pitch) + x);
+}
+__device__ __forceinline__ uint2 ld64(const Mip& m, int x, int y) {
+  return __ldg((const uint2*)(m.p + (size_t)y * m.pitch) + x);
+}
+__device__ __forceinline__ uint16_t ld16(const Mip& m, int x, int y) {
+  return __ldg((const uint16_t*)(m.p + (size_t)y * m.pitch) + x);
+}
+__device__ __forceinline__ bool in_range(const Mip& m, int x, int y) { return x >= 0 && y >= 0 && x < m.w && y < m.h; }
+
+// texelFetch of a D24 texel as float; out of range = 0.
+__device__ __forceinline__ float fetch_d24(const Mip& m, int x, int y) {
+  return in_range(m, x, y) ? d24_to_float(ld32(m, x, y)) : 0.0f;
+}
+
+// Bilinear footprint: indices (clamped) and weights for uv on a w x h level.
+struct Tap { int x0, x1, y0, y1; float wx, wy; };
+__device__ __forceinline__ Tap make_tap(float u, float v, int w, int h, int ox = 0, int oy = 0) {
+  float x = __fsub_rn(__fmul_rn(u, (float)w), 0.5f), y = __fsub_rn(__fmul_rn(v, (float)h), 0.5f);
+  float fx = floorf(x), fy = floorf(y);
+  Tap t;
+  t.wx = __fsub_rn(x, fx); t.wy = __fsub_rn(y, fy);
+  int x0 = (int)fx + ox, y0 = (int)fy + oy;
+  t.x0 = min(max(x0, 0), w - 1); t.x1 = min(max(x0 + 1, 0), w - 1);
+  t.y0 = min(max(y0, 0), h - 1); t.y1 = min(max(y0 + 1, 0), h - 1);
+  return t;
+}
+__device__ __forceinline__ float bilerp(float t00, float t10, float t01, float t11, float wx, float wy) {
+  return gmix(gmix(t00, t10, wx), gmix(t01, t11, wx), wy);
+}
+
+__device__ __forceinline__ float sample_d24(const Mip& m, float u, float v, int ox = 0, int oy = 0) {
+  Tap t = make_tap(u, v, m.w, m.h, ox, oy);
+  return bilerp(d24_to_float(ld32(m, t.x0, t.y0)), d24_to_float(ld32(m, t.x1, t.y0)),
+                d24_to_float(ld32(m, t.x0, t.y1)), d24_to_float(ld32(m, t.x1, t.y1)), t.wx, t.wy);
+}
+
+__device__ __forceinline__ float2 unpack_rg16unorm(uint32_t k) { return make_float2(unorm16_to_float(k & 0xFFFFu), unorm16_to_float(k >> 16)); }
+__device__ __forceinline__ float2 unpack_rg16f(uint32_t k) { return __half22float2(*reinterpret_cast<const __half2*>(&k)); }
+
+__device__ __forceinline__ float2 sample_rg16unorm(const Mip& m, float u, float v) {
+  Tap t = make_tap(u, v, m.w, m.h);
+  float2 a = unpack_rg16unorm(ld32(m, t.x0, t.y0)), b = unpack_rg16unorm(ld32(m, t.x1, t.y0));
+  float2 c = unpack_rg16unorm(ld32(m, t.x0, t.y1)), d = unpack_rg16unorm(ld32(m, t.x1, t.y1));
+  return make_float2(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy));
+}
+__device__ __forceinline__ f3 sample_gbuffer_normal(const Mip& m, float u, float v) {   // gbuffer_encode.glsl:39-43
+  float2 e = sample_rg16unorm(m, u, v);
+  return decode_normal(e.x, e.y);
+}
+__device__ __forceinline__ float2 sample_rg16f(const Mip& m, float u, float v, int ox = 0, int oy = 0) {
+  Tap t = make_tap(u, v, m.w, m.h, ox, oy);
+  float2 a = unpack_rg16f(ld32(m, t.x0, t.y0)), b = unpack_rg16f(ld32(m, t.x1, t.y0));
+  float2 c = unpack_rg16f(ld32(m, t.x0, t.y1)), d = unpack_rg16f(ld32(m, t.x1, t.y1));
+  return make_float2(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy));
+}
+__device__ __forceinline__ float sample_r32f(const Mip& m, float u, float v) {
+  Tap t = make_tap(u, v, m.w, m.h);
+  return bilerp(__uint_as_float(ld32(m, t.x0, t.y0)), __uint_as_float(ld32(m, t.x1, t.y0)),
+                __uint_as_float(ld32(m, t.x0, t.y1)), __uint_as_float(ld32(m, t.x1, t.y1)), t.wx, t.wy);
+}
+
+// sRGB8 texel -> linear rgb (+ linear alpha in .w); srgb = 256-entry decode table.
+__device__ __forceinline__ float4 unpack_srgb8(uint32_t k, const float* __restrict__ srgb) {
+  return make_float4(__ldg(srgb + (k & 255u)), __ldg(srgb + ((k >> 8) & 255u)), __ldg(srgb + ((k >> 16) & 255u)), unorm8_to_float(k >> 24));
+}
+__device__ __forceinline__ float4 sample_srgb8(const Mip& m, float u, float v, const float* __restrict__ srgb) {
+  Tap t = make_tap(u, v, m.w, m.h);
+  float4 a = unpack_srgb8(ld32(m, t.x0, t.y0), srgb), b = unpack_srgb8(ld32(m, t.x1, t.y0), srgb);
+  float4 c = unpack_srgb8(ld32(m, t.x0, t.y1), srgb), d = unpack_srgb8(ld32(m, t.x1, t.y1), srgb);
+  return make_float4(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy),
+                     bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy), bilerp(a.w, b.w, c.w, d.w, t.wx, t.wy));
+}
+__device__ __forceinline__ f3 unpack_rgb8unorm(uint32_t k) {
+  return mk3(unorm8_to_float(k & 255u), unorm8_to_float((k >> 8) & 255u), unorm8_to_float((k >> 16) & 255u));
+}
+
+// ---- texel encode ----------------------------------------------------------------
+__device__ __forceinline__ uint32_t to_unorm(float v, float maxv) {   // clamp, NaN -> 0, floor(v*max + 0.5)
+  if (!(v > 0.0f)) return 0u;
+  if (v > 1.0f) v = 1.0f;
+  return (uint32_t)floorf(__fadd_rn(__fmul_rn(v, maxv), 0.5f));
+}
+__device__ __forceinline__ uint32_t pack_rgba8unorm(float r, float g, float b, float a) {
+  return to_unorm(r, 255.f) | (to_unorm(g, 255.f) << 8) | (to_unorm(b, 255.f) << 16) | (to_unorm(a, 255.f) << 24);
+}
+__device__ __forceinline__ uint32_t pack_half2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float srgb_encode(float l) {
+  if (!(l > 0.0f)) return 0.0f;
+  if (l >= 1.0f) return 1.0f;
+  if (l < 0.0031308f) return 12.92f * l;
+  return 1.055f * powf(l, 1.0f / 2.4f) - 0.055f;
+}
+#endif  // __CUDACC__
+
+}  // namespace vkr
