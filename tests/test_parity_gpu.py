@@ -1,0 +1,130 @@
+"""CUDA passes vs the CPU oracle through the C ABI (libvkr_b200.so), on identical input bytes.
+
+Two regimes:
+  * pass-level: before every task the CUDA chain's images are overwritten with the oracle
+    chain's, so each kernel is judged in isolation on exactly the oracle's inputs;
+  * free-running: both chains run N frames on their own state (own LUTs, own histories);
+    errors may compound, tolerances are the same and must not drift with the frame index.
+Tolerances: tests/parity.py.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import chain
+import parity
+import vkr
+
+pytestmark = pytest.mark.gpu
+OUT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+
+
+def sync_images(dst_chain, src_chain):
+    d, s = dst_chain.images(), src_chain.images()
+    for k in d:
+        d[k].buf.copy_(s[k].buf)
+
+
+@pytest.fixture(scope="module")
+def oracle_luts():
+    """Full-size 1024^2 LUTs from the oracle (reference src/advanced_ssr.cpp:88-92), built once."""
+    b = chain.OracleBackend()
+    pdf = vkr.Image(1024, 1024, vkr.R32_SFLOAT, device="cpu")
+    brdf = vkr.Image(1024, 1024, vkr.R16G16_SFLOAT, device="cpu")
+    b.pdf_lut(pdf)
+    b.brdf_lut(b.halton(), brdf)
+    return pdf, brdf
+
+
+def test_halton_table_matches():
+    import oracle_lib
+    np.testing.assert_array_equal(vkr.halton23_seq(128), oracle_lib.halton23_seq(128))
+
+
+def test_lut_kernels(cuda, oracle_luts):
+    import torch
+    pdf_ref, brdf_ref = oracle_luts
+    b = chain.CudaBackend()
+    pdf = vkr.Image(1024, 1024, vkr.R32_SFLOAT)
+    brdf = vkr.Image(1024, 1024, vkr.R16G16_SFLOAT)
+    b.pdf_lut(pdf)
+    b.brdf_lut(b.halton(), brdf)
+    torch.cuda.synchronize()
+    # The integrand has poles inside the table (reference preintegrate.comp:77-84), so texels near them are
+    # huge or inf and ill-conditioned: the kernel is built without FMA contraction and must match bit for bit.
+    g, r = pdf.download().view(np.uint32), pdf_ref.download().view(np.uint32)
+    m = dict(max_rel=0.0 if np.array_equal(g, r) else 1.0, mismatches=int((g != r).sum()))
+    print("pdf LUT", m)
+    assert parity.TOLERANCES["pdf"](m), m
+    g, r = brdf.download().astype(np.float32), brdf_ref.download().astype(np.float32)
+    m = dict(max_abs=float(np.abs(g - r).max()), frac_neq=float((g != r).mean()))
+    print("brdf LUT", m)
+    assert parity.TOLERANCES["brdf"](m), m
+
+
+@pytest.mark.parametrize("w,h,frames,view", [(1280, 720, 3, 0), (640, 360, 4, 3), (256, 256, 3, 5)])
+def test_pass_level_parity(cuda, oracle_luts, w, h, frames, view):
+    import torch
+    scene = vkr.synth_scene(view, 64)
+    pdf_ref, brdf_ref = oracle_luts
+    oc = chain.Chain(w, h, chain.OracleBackend(), luts=(pdf_ref, brdf_ref))
+    cc = chain.Chain(w, h, chain.CudaBackend(), luts=(pdf_ref.clone_to("cuda"), brdf_ref.clone_to("cuda")))
+    report, failures = [], []
+    for f in range(frames):
+        P = oc.begin_frame(scene, view_seed=view)
+        cc.begin_frame(scene, view_seed=view, gbuffer_from=oc.gb)
+        osteps, csteps = oc.steps(P), cc.steps(P)
+        for (name, othunk, outs), (_, cthunk, _) in zip(osteps, csteps):
+            sync_images(cc, oc)       # identical inputs (and identical previous contents of RMW outputs)
+            othunk()
+            cthunk()
+            torch.cuda.synchronize()
+            for o in outs:
+                m = parity.compare_image(o, cc.images()[o], oc.images()[o], task=name)
+                key = "raw_trace" if (o == "raw" and name == "SSSR_trace") else o
+                report.append(dict(frame=f, task=name, image=o, **m))
+                if not parity.TOLERANCES[key](m):
+                    failures.append(report[-1])
+        oc.end_frame()
+        cc.end_frame()
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, f"parity_pass_{w}x{h}.json"), "w") as fh:
+        json.dump(report, fh, indent=1)
+    for r in report:
+        print(r)
+    assert not failures, failures
+
+
+@pytest.mark.parametrize("w,h,frames", [(640, 360, 8)])
+def test_free_running_chain(cuda, w, h, frames):
+    """Both sides end to end on their own state: own LUTs (256^2 here to bound CPU time), own histories."""
+    import torch
+    scene = vkr.synth_scene(1, 64)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=256)
+    cc = chain.Chain(w, h, chain.CudaBackend(), lut_size=256)
+    report, failures = [], []
+    for f in range(frames):
+        oo, _ = oc.render(scene)
+        co, _ = cc.render(scene, gbuffer_from=None)
+        torch.cuda.synchronize()
+        for o in ("depth", "dn", "dv", "rays", "raw", "reflections", "blurred", "filtered", "accumulated_ao", "color", "taa"):
+            m = parity.compare_image(o, co[o], oo[o])
+            report.append(dict(frame=f, image=o, **m))
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, "parity_chain.json"), "w") as fh:
+        json.dump(report, fh, indent=1)
+    for r in report:
+        print(r)
+    # integer outputs stay bit-exact; fp outputs: PSNR must hold and must not drift with the frame index
+    for r in report:
+        if r["image"] in ("depth", "dn", "dv") and r["mismatches"]:
+            failures.append(r)
+    first = {r["image"]: r for r in report if r["frame"] == 1}
+    last = {r["image"]: r for r in report if r["frame"] == frames - 1}
+    for o in ("accumulated_ao", "blurred", "color", "taa"):
+        floor = {"accumulated_ao": 45.0, "blurred": 35.0, "color": 40.0, "taa": 40.0}[o]
+        if last[o]["psnr"] < floor or min(last[o]["psnr"], 100.0) < min(first[o]["psnr"], 100.0) - 6.0:
+            failures.append(dict(drift=o, first=first[o]["psnr"], last=last[o]["psnr"]))
+    assert not failures, failures

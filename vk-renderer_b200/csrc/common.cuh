@@ -54,75 +54,82 @@ inline Mat4 make_mat(const float* p) { Mat4 r; for (int i = 0; i < 16; i++) r.m[
 // ---- device side -------------------------------------------------------------
 #define VKR_PI 3.1415926535897932384626433832795f
 
+// Unfused fp32: the oracle evaluates every expression as separate IEEE mul/add/sub (it is
+// built with -ffp-contract=off).  The geometry helpers below use the non-contracting
+// intrinsics so that every DISCRETE decision derived from them (texel selection, history
+// rejection, closest-depth pick, blur radius, thickness break) is taken on the same bits as
+// the oracle; colour accumulation in the kernels is left to the compiler (FMA allowed).
+#define FM(a, b) __fmul_rn((a), (b))
+#define FA(a, b) __fadd_rn((a), (b))
+#define FS(a, b) __fsub_rn((a), (b))
+
 // GLSL-spec min/max (NaN behaviour differs from fminf/fmaxf).
 __device__ __forceinline__ float gmin(float x, float y) { return (y < x) ? y : x; }
 __device__ __forceinline__ float gmax(float x, float y) { return (x < y) ? y : x; }
 __device__ __forceinline__ float gclamp(float x, float lo, float hi) { return gmin(gmax(x, lo), hi); }
-__device__ __forceinline__ float gmix(float a, float b, float t) { return a * (1.0f - t) + b * t; }
+__device__ __forceinline__ float gmix(float a, float b, float t) { return FA(FM(a, FS(1.0f, t)), FM(b, t)); }
 
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(FA(a.x, b.x), FA(a.y, b.y), FA(a.z, b.z)); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(FS(a.x, b.x), FS(a.y, b.y), FS(a.z, b.z)); }
 __device__ __forceinline__ f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
-__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(FM(a.x, s), FM(a.y, s), FM(a.z, s)); }
+__device__ __forceinline__ f3 operator*(float s, f3 a) { return mk3(FM(s, a.x), FM(s, a.y), FM(s, a.z)); }
+__device__ __forceinline__ f3 operator*(f3 a, f3 b) { return mk3(FM(a.x, b.x), FM(a.y, b.y), FM(a.z, b.z)); }
 __device__ __forceinline__ f3 operator/(f3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
-__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return FA(FA(FM(a.x, b.x), FM(a.y, b.y)), FM(a.z, b.z)); }
 __device__ __forceinline__ float len3(f3 a) { return sqrtf(dot3(a, a)); }
 __device__ __forceinline__ f3 norm3(f3 a) { float s = 1.0f / sqrtf(dot3(a, a)); return a * s; }
-__device__ __forceinline__ f3 cross3(f3 a, f3 b) { return mk3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
-__device__ __forceinline__ f3 mix3(f3 a, f3 b, float t) { return a * (1.0f - t) + b * t; }
-__device__ __forceinline__ f3 reflect3(f3 I, f3 N) { return I - (2.0f * dot3(N, I)) * N; }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+  return mk3(FS(FM(a.y, b.z), FM(b.y, a.z)), FS(FM(a.z, b.x), FM(b.z, a.x)), FS(FM(a.x, b.y), FM(b.x, a.y)));
+}
+__device__ __forceinline__ f3 mix3(f3 a, f3 b, float t) { return a * FS(1.0f, t) + b * t; }
+__device__ __forceinline__ f3 reflect3(f3 I, f3 N) { return I - FM(2.0f, dot3(N, I)) * N; }
 
 // M * (v, w)  — column-major, left-to-right accumulation like the oracle.
-__device__ __forceinline__ f3 mul_m4(const Mat4& M, f3 v, float w) {
-  return mk3(M.m[0] * v.x + M.m[4] * v.y + M.m[8] * v.z + M.m[12] * w,
-             M.m[1] * v.x + M.m[5] * v.y + M.m[9] * v.z + M.m[13] * w,
-             M.m[2] * v.x + M.m[6] * v.y + M.m[10] * v.z + M.m[14] * w);
+__device__ __forceinline__ float m4row(const Mat4& M, int r, f3 v, float w) {
+  return FA(FA(FA(FM(M.m[r], v.x), FM(M.m[4 + r], v.y)), FM(M.m[8 + r], v.z)), FM(M.m[12 + r], w));
 }
+__device__ __forceinline__ f3 mul_m4(const Mat4& M, f3 v, float w) { return mk3(m4row(M, 0, v, w), m4row(M, 1, v, w), m4row(M, 2, v, w)); }
 __device__ __forceinline__ float4 mul_m4_4(const Mat4& M, f3 v, float w) {
-  return make_float4(M.m[0] * v.x + M.m[4] * v.y + M.m[8] * v.z + M.m[12] * w,
-                     M.m[1] * v.x + M.m[5] * v.y + M.m[9] * v.z + M.m[13] * w,
-                     M.m[2] * v.x + M.m[6] * v.y + M.m[10] * v.z + M.m[14] * w,
-                     M.m[3] * v.x + M.m[7] * v.y + M.m[11] * v.z + M.m[15] * w);
+  return make_float4(m4row(M, 0, v, w), m4row(M, 1, v, w), m4row(M, 2, v, w), m4row(M, 3, v, w));
 }
 
 // ---- shared shader math (reference src/shaders/include/gbuffer_encode.glsl) -----
 __device__ __forceinline__ float sign_nz(float k) { return (k >= 0.0f) ? 1.0f : -1.0f; }
 
 __device__ __forceinline__ f3 decode_normal(float u, float v) {           // gbuffer_encode.glsl:29-37
-  u = 2.f * u - 1.f; v = 2.f * v - 1.f;
-  f3 n = mk3(u, v, 1.0f - fabsf(u) - fabsf(v));
+  u = FS(FM(2.f, u), 1.f); v = FS(FM(2.f, v), 1.f);
+  f3 n = mk3(u, v, FS(FS(1.0f, fabsf(u)), fabsf(v)));
   if (n.z < 0.0f) {
-    float tx = (1.0f - fabsf(n.y)) * sign_nz(n.x);
-    float ty = (1.0f - fabsf(n.x)) * sign_nz(n.y);
+    float tx = FM(FS(1.0f, fabsf(n.y)), sign_nz(n.x));
+    float ty = FM(FS(1.0f, fabsf(n.x)), sign_nz(n.y));
     n.x = tx; n.y = ty;
   }
   return norm3(n);
 }
 
 __device__ __forceinline__ float linearize_depth2(float d, float n, float f) {   // :53-56
-  return n * f / (d * (f - n) - f);
+  return FM(n, f) / FS(FM(d, FS(f, n)), f);
 }
 
 __device__ __forceinline__ f3 reconstruct_view_vec(float u, float v, float d, const CamK& c) {  // :58-69
   float z = linearize_depth2(d, c.znear, c.zfar);
-  float xd = 2 * u - 1;
-  float yd = 2 * v - 1;
-  float x = -(xd) * (z * c.aspect * c.tg);
-  float y = -(yd) * (z * c.tg);
+  float xd = FS(FM(2.f, u), 1.f);
+  float yd = FS(FM(2.f, v), 1.f);
+  float x = FM(-(xd), FM(FM(z, c.aspect), c.tg));
+  float y = FM(-(yd), FM(z, c.tg));
   return mk3(x, y, z);
 }
 
 __device__ __forceinline__ f3 project_view_vec(f3 v, const CamK& c) {                          // :75-84
   float n = c.znear, f = c.zfar;
   float z = v.z;
-  float depth = f / (f - n) + f * n / (z * (f - n));
-  float pu = v.x / (-v.z * c.tg * c.aspect);
-  float pv = v.y / (-z * c.tg);
-  return mk3(0.5f * pu + 0.5f, 0.5f * pv + 0.5f, depth);
+  float depth = FA(f / FS(f, n), FM(f, n) / FM(z, FS(f, n)));
+  float pu = v.x / FM(FM(-v.z, c.tg), c.aspect);
+  float pv = v.y / FM(-z, c.tg);
+  return mk3(FA(FM(0.5f, pu), 0.5f), FA(FM(0.5f, pv), 0.5f), depth);
 }
 
 // ---- texel decode ----------------------------------------------------------------

@@ -1,0 +1,247 @@
+// gtao.cu — GTAO main (MIS with the SSR ray), 4x4 depth-aware filter, temporal accumulate.
+//
+// Replaces tasks "GTAO_main", "GTAO_filter", "GTAO_accumulate"
+// (reference src/gtao.cpp:84-148,:198-239,:286-347; shaders/gtao/{main,filter,accum}.comp).
+#include "brdf.cuh"
+
+namespace vkr {
+
+struct GtaoK {
+  Mat4 normal_mat;
+  CamK cam;
+  float angle_offset, weight_ratio;
+  uint32_t use_mis, two_directions, reflections_only;
+  int tw, th;  // tex_size = truncated dispatch extent (gtao.cpp:145, main.comp:54)
+};
+
+#define MAX_THIKNESS 0.1f  // main.comp:82
+
+// main.comp:84-108 — 16 bilinear depth taps along the slice direction.
+__device__ __forceinline__ float find_horizon(const Mip& depth, float su, float sv, f3 camera_start, float dirx, float diry,
+                                              int samples_count, f3 v, const CamK& cam) {
+  float h_cos = -1.0f;
+  float previous_z = camera_start.z;
+  for (int i = 1; i <= samples_count; i++) {
+    float s = (float)i / (float)samples_count;
+    float tu = FA(su, FM(s, dirx)), tv = FA(sv, FM(s, diry));
+    float sample_depth = sample_d24(depth, tu, tv);
+    f3 sample_pos = reconstruct_view_vec(tu, tv, sample_depth, cam);
+    if (sample_pos.z > FA(previous_z, MAX_THIKNESS)) break;
+    previous_z = sample_pos.z;
+    f3 sample_offset = sample_pos - camera_start;
+    float sample_cos = dot3(v, norm3(sample_offset));
+    if (sample_cos > h_cos) h_cos = sample_cos;
+  }
+  return h_cos;
+}
+
+// main.comp:276-278
+__device__ __forceinline__ float gtao_direction(int x, int y) { return (1.0f / 16.0f) * (float)((((x + y) & 3) << 2) + (x & 3)); }
+
+// slice integral shared by mis_gtao (:232-246) and gtao_camera_space (:199-214)
+__device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& k, float su, float sv, float frag_depth, f3 camera_pos,
+                                                 f3 w0, f3 camera_normal, float rx, float ry, float angle, f3* Lout, bool mis) {
+  float sdx = FM(rx, cosf(angle)), sdy = FM(ry, sinf(angle));
+  f3 sample_end_pos = reconstruct_view_vec(FA(su, sdx), FA(sv, sdy), frag_depth, k.cam);
+  if (Lout) *Lout = norm3(sample_end_pos - camera_pos);
+  f3 slice_normal = norm3(cross3(w0, -sample_end_pos));
+  f3 normal_projected = camera_normal - dot3(camera_normal, slice_normal) * slice_normal;
+  f3 X = -norm3(cross3(slice_normal, w0));
+  float n = FS(VKR_PI / 2.0f, acosf(dot3(norm3(normal_projected), X)));
+  float h_cos = find_horizon(depth, su, sv, camera_pos, sdx, sdy, 16, w0, k.cam);
+  float h = acosf(h_cos);
+  h = gmin(FA(n, gmin(FS(h, n), VKR_PI / 2.0f)), h);
+  const float lenp = mis ? FM(1.0f / VKR_PI, len3(normal_projected)) : len3(normal_projected);   // main.comp:246 vs :213
+  return FM(FM(lenp, 0.25f), gmax(FA(FA(-cosf(FS(FM(2.f, h), n)), cosf(n)), FM(FM(2.f, h), sinf(n))), 0.0f));
+}
+
+__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Mip depth, Mip normal, Mip material, Mip pdf, Mip raw, const float* __restrict__ srgb) {
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (px >= k.tw || py >= k.th) return;
+  const float su = ((float)px + 0.5f) / (float)k.tw, sv = ((float)py + 0.5f) / (float)k.th;
+  uint2* out = (uint2*)(raw.p + (size_t)py * raw.pitch) + px;
+  float ox = 0.f, oy = 1.0f / (2 * VKR_PI);
+
+  const float frag_depth = sample_d24(depth, su, sv);
+  if (k.use_mis > 0) {                                                     // mis_gtao, main.comp:219-274
+    if (frag_depth >= 1.f) { *out = make_uint2(pack_half2(0.f, 1.0f), 0u); return; }
+    f3 camera_pos = reconstruct_view_vec(su, sv, frag_depth, k.cam);
+    f3 w0 = -norm3(camera_pos);
+    f3 camera_normal = norm3(mul_m4(k.normal_mat, sample_gbuffer_normal(normal, su, sv), 0.f));
+    float rad = gmin(100.0f / len3(camera_pos), 16.0f);
+    float rx = rad / (float)depth.w, ry = rad / (float)depth.h;
+    float base_angle = FA(gtao_direction(px, py), k.angle_offset);
+    float angle = FM(2 * VKR_PI, base_angle);
+    f3 L;
+    float occlusion = slice_occlusion(depth, k, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true);
+
+    float roughness = sample_srgb8(material, su, sv, srgb).y;
+    float pdf_ggx = sampleGGXdirPDF(pdf, w0, camera_normal, L, FM(roughness, roughness));
+    float pdf_uniform = 1.0f / (2 * VKR_PI);
+    uint2 prev = *out;
+    float2 ao = unpack_rg16f(prev.x);                                       // imageLoad(gtao_out).xy
+    if (k.reflections_only != 0) {
+      float res = ao.x / ao.y;
+      ox = isnan(res) ? 1.f : res; oy = 1.f;
+    } else {
+      float alpha = 1 / FA(k.weight_ratio, 1.f);
+      float betta = FS(1.f, alpha);
+      float mis_weight1 = alpha / FA(FM(alpha, ao.y), FM(betta, pdf_uniform));
+      float mis_weight2 = betta / FA(FM(alpha, pdf_ggx), FM(betta, pdf_uniform));
+      float mis_ao = FA(FM(ao.x, mis_weight1), FM(occlusion, mis_weight2));
+      ox = isnan(mis_ao) ? occlusion / pdf_uniform : mis_ao; oy = 1.f;
+    }
+  } else {                                                                  // gtao_camera_space, main.comp:185-217
+    if (frag_depth >= 1.f) ox = 0.f;
+    else {
+      f3 camera_pos = reconstruct_view_vec(su, sv, frag_depth, k.cam);
+      f3 w0 = -norm3(camera_pos);
+      f3 camera_normal = norm3(mul_m4(k.normal_mat, sample_gbuffer_normal(normal, su, sv), 0.f));
+      float rad = gmin(100.0f / len3(camera_pos), 16.0f);
+      float rx = rad / (float)depth.w, ry = rad / (float)depth.h;
+      float base_angle = gtao_direction(px, py) + k.angle_offset;
+      int dirs = k.two_directions != 0 ? 2 : 1;
+      float sum = 0.f;
+      for (int d = 0; d < dirs; d++) {
+        float angle = 2 * VKR_PI * (base_angle + (float)d / (float)dirs);
+        sum += slice_occlusion(depth, k, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false);
+      }
+      ox = 2 * sum / (float)dirs;
+    }
+  }
+  *out = make_uint2(pack_half2(ox, oy), 0u);
+}
+
+// filter.comp:17-52 — 4x4 window at offsets -2..+1, weight on linear depth.
+__global__ void __launch_bounds__(256) gtao_filter_kernel(Mip depth, Mip raw, Mip filtered, int tw, int th, float znear, float zfar) {
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (px >= tw || py >= th) return;
+  float pixel_depth = fetch_d24(depth, px, py);
+  float linear_depth = linearize_depth2(pixel_depth, znear, zfar);
+  float weight_sum = 0, ao = 0;
+#pragma unroll
+  for (int x = 0; x < 4; x++) {
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      int sx = px + x - 2, sy = py + y - 2;
+      float sampled_depth = linearize_depth2(fetch_d24(depth, sx, sy), znear, zfar);
+      float weight = gmax(0.0f, FS(1.0f, FM(5.f, fabsf(FS(sampled_depth, linear_depth))) / fabsf(linear_depth)));
+      weight_sum = FA(weight_sum, weight);
+      float r = in_range(raw, sx, sy) ? unpack_rg16f(ld64(raw, sx, sy).x).x : 0.f;
+      ao = FA(ao, FM(weight, r));
+    }
+  }
+  ao /= weight_sum;
+  *((__half*)(filtered.p + (size_t)py * filtered.pitch) + px) = __float2half_rn(ao);
+}
+
+struct AccumK {
+  Mat4 inverse_camera, prev_inverse_camera, mvp;
+  CamK cam;
+  uint32_t clear_history;
+};
+
+__device__ __forceinline__ f3 reconstruct_world_pos(const Mip& depth, const Mat4& inv, float u, float v, const CamK& cam) {  // accum.comp:94-99
+  float d = sample_d24(depth, u, v);
+  f3 vc = reconstruct_view_vec(u, v, d, cam);
+  return mul_m4(inv, vc, 1.0f);
+}
+
+// accum.comp:29-92
+__global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k, Mip depth, Mip prev_depth, Mip filtered, Mip out, Mip velocity, Mip history) {
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (px >= out.w || py >= out.h) return;
+  const float tw = (float)out.w, th = (float)out.h;
+  const float su = ((float)px + 0.5f) / tw, sv = ((float)py + 0.5f) / th;
+  float2 vel = sample_rg16f(velocity, su, sv);
+  float pu = FA(su, vel.x), pv = FA(sv, vel.y);
+  bool reprojected = false;
+  float valid_samples = 1.0f;
+  if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
+    f3 v_world_prev = reconstruct_world_pos(prev_depth, k.prev_inverse_camera, pu, pv, k.cam);
+    float4 prev_ndc = mul_m4_4(k.mvp, v_world_prev, 1.0f);
+    float ndx = prev_ndc.x / prev_ndc.w, ndy = prev_ndc.y / prev_ndc.w, ndz = prev_ndc.z / prev_ndc.w;
+    float wu = FA(FM(0.5f, ndx), 0.5f), wv = FA(FM(0.5f, ndy), 0.5f);
+    float dx = FM(fabsf(FS(wu, su)), tw), dy = FM(fabsf(FS(wv, sv)), th);
+    float current_z = linearize_depth2(sample_d24(depth, su, sv), k.cam.znear, k.cam.zfar);
+    float prev_z = linearize_depth2(ndz, k.cam.znear, k.cam.zfar);
+    float depth_err = fabsf(FS(prev_z, current_z));
+    float vel_delta = gmax(FM(fabsf(vel.x), tw), FM(fabsf(vel.y), th));
+    float error = FA(FM(0.1f, vel_delta), depth_err);
+    valid_samples = gclamp(FS(1.f, error), 0.8f, 1.f);
+    reprojected = (gmax(dx, dy) <= 2.0f) && (depth_err < 0.2f);
+  }
+  float new_ao = __half2float(*((const __half*)(filtered.p + (size_t)py * filtered.pitch) + px));
+  float computed_ao = new_ao;
+  float samples_count = 1.f;
+  if (k.clear_history != 0) reprojected = false;
+  if (reprojected) {
+    float2 acc = sample_rg16f(history, pu, pv);
+    samples_count = FM(FM(255.f, acc.y), valid_samples);
+    computed_ao = FA(FM(acc.x, samples_count), new_ao) / FA(samples_count, 1.f);
+    samples_count = FA(samples_count, 1.f);
+    if (samples_count > 255.f) samples_count = 100.f;
+  }
+  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_half2(gclamp(computed_ao, 0.f, 1.f), samples_count / 255.f);
+}
+
+}  // namespace vkr
+using namespace vkr;
+
+extern "C" int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
+                             const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, void* stream) {
+  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth_lod >= depth->mip_count || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) ||
+      !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(pdf_lut, VKR_FORMAT_R32_SFLOAT) || !image_ok(raw, VKR_FORMAT_R16G16B16A16_SFLOAT)) {
+    set_error("gtao_main: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  GtaoK k;
+  k.normal_mat = make_mat(p->normal_mat);
+  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
+  k.angle_offset = p->angle_offset; k.weight_ratio = p->weight_ratio;
+  k.use_mis = p->use_mis; k.two_directions = p->two_directions; k.reflections_only = p->reflections_only;
+  k.tw = (int)(raw->width / 8) * 8; k.th = (int)(raw->height / 4) * 4;  // truncating dispatch, gtao.cpp:145
+  if (k.tw == 0 || k.th == 0) return VKR_OK;
+  const float* srgb = srgb_decode_table_device();
+  if (!srgb) { set_error("gtao_main: sRGB table upload failed"); return VKR_ERR_CUDA; }
+  dim3 grid((k.tw + 31) / 32, (k.th + 7) / 8);
+  gtao_main_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, depth_lod), make_mip(normal, 0), make_mip(material, 0),
+                                                           make_mip(pdf_lut, 0), make_mip(raw, 0), srgb);
+  return check_launch("gtao_main_kernel");
+}
+
+extern "C" int vkr_gtao_filter(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
+                               uint32_t depth_lod, void* stream) {
+  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth_lod >= depth->mip_count ||
+      !image_ok(raw, VKR_FORMAT_R16G16B16A16_SFLOAT) || !image_ok(filtered, VKR_FORMAT_R16_SFLOAT)) {
+    set_error("gtao_filter: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  int tw = (int)(filtered->width / 8) * 8, th = (int)(filtered->height / 4) * 4;  // gtao.cpp:237
+  if (tw == 0 || th == 0) return VKR_OK;
+  dim3 grid((tw + 31) / 32, (th + 7) / 8);
+  gtao_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(make_mip(depth, depth_lod), make_mip(raw, 0), make_mip(filtered, 0), tw, th, p->znear, p->zfar);
+  return check_launch("gtao_filter_kernel");
+}
+
+extern "C" int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth, const VkrImage* filtered,
+                                   const VkrImage* accumulated, const VkrImage* dvelocity, const VkrImage* history, uint32_t depth_lod, void* stream) {
+  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || !image_ok(prev_depth, VKR_FORMAT_D24_UNORM_S8_UINT) ||
+      depth_lod >= depth->mip_count || depth_lod >= prev_depth->mip_count || !image_ok(filtered, VKR_FORMAT_R16_SFLOAT) ||
+      !image_ok(accumulated, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(dvelocity, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(history, VKR_FORMAT_R16G16_SFLOAT)) {
+    set_error("gtao_accumulate: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  if (filtered->width != accumulated->width || filtered->height != accumulated->height) {
+    set_error("gtao_accumulate: filtered and accumulated sizes differ");
+    return VKR_ERR_SIZE_MISMATCH;
+  }
+  AccumK k;
+  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera); k.mvp = make_mat(p->mvp);
+  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  k.clear_history = p->clear_history;
+  dim3 grid((accumulated->width + 31) / 32, (accumulated->height + 7) / 8);
+  gtao_accumulate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, depth_lod), make_mip(prev_depth, depth_lod), make_mip(filtered, 0),
+                                                                 make_mip(accumulated, 0), make_mip(dvelocity, 0), make_mip(history, 0));
+  return check_launch("gtao_accumulate_kernel");
+}

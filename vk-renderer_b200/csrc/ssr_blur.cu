@@ -1,0 +1,171 @@
+// ssr_blur.cu — roughness-sized bilateral Gaussian blur of the resolved reflections plus the
+// temporal blend.  Replaces task "SSSR_blur" (reference src/advanced_ssr.cpp:371-438,
+// shaders/advanced_ssr/blur.comp:31-118).
+//
+// The reference shader fetches, for each of up to (2*11+1)^2 = 529 taps per pixel, one depth
+// texel, one bilinear normal (4 texels + octahedral decode + normalize) and one colour texel.
+// All three depend only on the tap POSITION, so a CTA of 16x16 pixels stages them once per
+// position for its tile + halo (halo = the tile's largest radius) in shared memory as two
+// float4 planes {n.xyz, depth} and {rgb, -}; the tap loop is then 2 LDS.128 + ~16 FP ops.
+// The bilateral weights are per tap, so the filter is not separable.
+// Warps iterate the window of their largest radius in lockstep (lanes outside their own
+// radius skip), which keeps the shared-memory reads conflict-free and preserves each pixel's
+// accumulation order (i = x offset outer, j = y offset inner, as in blur.comp:57-75).
+#include "common.cuh"
+
+namespace vkr {
+
+struct BlurK {
+  Mat4 inverse_camera, prev_inverse_camera;
+  CamK cam;
+  float max_roughness;
+  uint32_t accumulate, disable_blur;
+};
+
+#define BLUR_TILE 16
+#define BLUR_RMAX 11
+#define BLUR_SPAN (BLUR_TILE + 2 * BLUR_RMAX)
+
+__device__ __forceinline__ f3 world_pos_lod(const Mip& depth1, const Mat4& inv, float u, float v, const CamK& cam) {   // blur.comp:110-115
+  float d = sample_d24(depth1, u, v);
+  return mul_m4(inv, reconstruct_view_vec(u, v, d, cam), 1.0f);
+}
+
+__global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip normal_tex, Mip refl, Mip material_tex, Mip history, Mip velocity,
+                                                        Mip prev_depth1, Mip out, const float* __restrict__ srgb) {
+  __shared__ float4 s_nd[BLUR_SPAN * BLUR_SPAN];
+  __shared__ float4 s_col[BLUR_SPAN * BLUR_SPAN];
+  __shared__ int s_rmax;
+
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const int px = blockIdx.x * BLUR_TILE + tx, py = blockIdx.y * BLUR_TILE + ty;
+  const bool inside = px < out.w && py < out.h;
+  const float tsx = (float)out.w, tsy = (float)out.h;
+  const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;
+
+  // per-pixel radius (blur.comp:39-53)
+  float sigma = 0.35f;
+  int r = 0;
+  if (inside) {
+    float roughness = sample_srgb8(material_tex, su, sv, srgb).y;
+    roughness = gmix(0.0f, k.max_roughness, roughness);
+    sigma = gmix(0.4f, 4.f, roughness);
+    if (k.disable_blur != 0) sigma = 0.35f;
+    r = (int)floorf(FS(FM(3.f, sigma), 0.01f));
+    r = min(max(r, 0), BLUR_RMAX);
+  }
+  if (threadIdx.x == 0) s_rmax = 0;
+  __syncthreads();
+  int wr = __reduce_max_sync(0xFFFFFFFFu, r);
+  if ((threadIdx.x & 31) == 0) atomicMax(&s_rmax, wr);
+  __syncthreads();
+  const int R = s_rmax;
+  const int span = BLUR_TILE + 2 * R;
+
+  // stage {normal, depth} and colour for every tap position of the tile
+  const int ox = blockIdx.x * BLUR_TILE - R, oy = blockIdx.y * BLUR_TILE - R;
+  for (int t = threadIdx.x; t < span * span; t += 256) {
+    const int lx = t % span, ly = t / span;
+    const int qx = ox + lx, qy = oy + ly;
+    float4 nd = make_float4(0.f, 0.f, 0.f, 0.f), col = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (qx >= 0 && qy >= 0 && qx < out.w && qy < out.h) {          // outside: depth 0 -> bilateral weight 0, colour 0
+      f3 n = sample_gbuffer_normal(normal_tex, (float)qx / tsx, (float)qy / tsy);   // uv without +0.5 (blur.comp:60,:63)
+      nd = make_float4(n.x, n.y, n.z, fetch_d24(depth1, qx, qy));
+      f3 c = unpack_rgb8unorm(ld32(refl, qx, qy));
+      col = make_float4(c.x, c.y, c.z, 0.f);
+    }
+    s_nd[ly * BLUR_SPAN + lx] = nd;
+    s_col[ly * BLUR_SPAN + lx] = col;
+  }
+  __syncthreads();
+
+  const float center_depth = s_nd[(ty + R) * BLUR_SPAN + tx + R].w;            // texelFetch(DEPTH_TEX, pixel_pos, 1)
+  f3 center_normal = mk3(0.f, 0.f, 1.f);
+  if (inside) center_normal = sample_gbuffer_normal(normal_tex, su, sv);
+  const float g = 1.0f / FM(FM(2 * VKR_PI, sigma), sigma);
+  const float e = FM(FM(2.f, sigma), sigma);
+  const float ek = -1.4426950408889634f / e;     // exp(-d2/e) = exp2(d2 * ek)
+  const float bk = 1000.0f / center_depth;
+
+  float weight_sum = 0.f;
+  f3 color = mk3(0.f, 0.f, 0.f);
+  const int base = (ty + R) * BLUR_SPAN + tx + R;
+  for (int i = -wr; i <= wr; i++) {
+    const bool ix_ok = (i >= -r) && (i <= r);
+    for (int j = -wr; j <= wr; j++) {
+      if (ix_ok && j >= -r && j <= r) {
+        const float4 nd = s_nd[base + j * BLUR_SPAN + i];
+        const float4 c = s_col[base + j * BLUR_SPAN + i];
+        float bilateral_weight = gmax(1 - fabsf(center_depth - nd.w) * bk, 0.f);
+        float normal_weight = gmax(center_normal.x * nd.x + center_normal.y * nd.y + center_normal.z * nd.z, 0.f);
+        float w = g * exp2f((float)(i * i + j * j) * ek);
+        w *= bilateral_weight;
+        w *= normal_weight;
+        color.x += c.x * w; color.y += c.y * w; color.z += c.z * w;
+        weight_sum += w;
+      }
+    }
+  }
+  if (!inside) return;
+  const float inv = gmax(weight_sum, 0.001f);
+  color = mk3(color.x / inv, color.y / inv, color.z / inv);
+
+  // temporal blend (blur.comp:77-105)
+  bool reprojected = false;
+  float2 vel = sample_rg16f(velocity, su, sv);
+  float delta_len = sqrtf(FA(FM(vel.x, vel.x), FM(vel.y, vel.y)));
+  float pu = FA(su, vel.x), pv = FA(sv, vel.y);
+  if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
+    f3 v_world_cur = world_pos_lod(depth1, k.inverse_camera, su, sv, k.cam);
+    f3 v_world_prev = world_pos_lod(prev_depth1, k.prev_inverse_camera, pu, pv, k.cam);
+    f3 v_camera = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
+    float error = len3(v_world_cur - v_world_prev);
+    float pixel_dist = len3(v_world_cur - v_camera);
+    reprojected = (delta_len < 0.0001f) || (error < gclamp(FM(FM(0.1f, pixel_dist), delta_len), 0.01f, 0.1f));
+  }
+  if (k.accumulate == 0) reprojected = false;
+  if (reprojected) {
+    Tap t = make_tap(su, sv, history.w, history.h);            // history at screen_uv, not prev_uv (App. A.6 #3)
+    f3 a = unpack_rgb8unorm(ld32(history, t.x0, t.y0)), b = unpack_rgb8unorm(ld32(history, t.x1, t.y0));
+    f3 c = unpack_rgb8unorm(ld32(history, t.x0, t.y1)), d = unpack_rgb8unorm(ld32(history, t.x1, t.y1));
+    f3 hc = mk3(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy), bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy));
+    color = mix3(hc, color, 0.1f);
+  }
+  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_rgba8unorm(color.x, color.y, color.z, 0.f);
+}
+
+}  // namespace vkr
+using namespace vkr;
+
+extern "C" int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
+                             const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity, const VkrImage* prev_depth,
+                             const VkrImage* out_blurred, void* stream) {
+  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 || !image_ok(prev_depth, VKR_FORMAT_D24_UNORM_S8_UINT) ||
+      prev_depth->mip_count < 2 || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) || !image_ok(reflections, VKR_FORMAT_R8G8B8A8_UNORM) ||
+      !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(history, VKR_FORMAT_R8G8B8A8_UNORM) ||
+      !image_ok(dvelocity, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(out_blurred, VKR_FORMAT_R8G8B8A8_UNORM)) {
+    set_error("sssr_blur: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  if (reflections->width != out_blurred->width || reflections->height != out_blurred->height ||
+      history->width != out_blurred->width || history->height != out_blurred->height) {
+    set_error("sssr_blur: reflections / history / blurred sizes differ");
+    return VKR_ERR_SIZE_MISMATCH;
+  }
+  if (!(p->max_roughness >= 0.f && p->max_roughness <= 1.f)) {   // radius bound r <= 11 assumes sigma <= 4
+    set_error("sssr_blur: max_roughness outside [0,1]");
+    return VKR_ERR_UNSUPPORTED;
+  }
+  if (history->base == out_blurred->base) { set_error("sssr_blur: history and output alias"); return VKR_ERR_INVALID_ARGUMENT; }
+  BlurK k;
+  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera);
+  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  k.max_roughness = p->max_roughness; k.accumulate = p->accumulate; k.disable_blur = p->disable_blur;
+  const float* srgb = srgb_decode_table_device();
+  if (!srgb) { set_error("sssr_blur: sRGB table upload failed"); return VKR_ERR_CUDA; }
+  dim3 grid((out_blurred->width + BLUR_TILE - 1) / BLUR_TILE, (out_blurred->height + BLUR_TILE - 1) / BLUR_TILE);
+  sssr_blur_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, 1), make_mip(normal, 0), make_mip(reflections, 0), make_mip(material, 0),
+                                                           make_mip(history, 0), make_mip(dvelocity, 0), make_mip(prev_depth, 1),
+                                                           make_mip(out_blurred, 0), srgb);
+  return check_launch("sssr_blur_kernel");
+}

@@ -201,3 +201,144 @@ def depth_mips(depth, src_mip=1, stream=None):
 
 def hiz_build(depth, normal, velocity, out_normal, out_velocity, stream=None):
     check(lib.vkr_hiz_build(depth.ptr, normal.ptr, velocity.ptr, out_normal.ptr, out_velocity.ptr, stream_ptr(stream)))
+
+
+# ---- synthetic G-buffer producer (include/vkr_synth.h) -----------------------------------
+class SynthObject(C.Structure):
+    _fields_ = [("center", C.c_float * 3), ("half_extent", C.c_float * 3), ("kind", C.c_uint32),
+                ("albedo_srgb8", C.c_uint32), ("material_srgb8", C.c_uint32)]
+
+
+class SynthScene(C.Structure):
+    _fields_ = [("object_count", C.c_uint32), ("objects", SynthObject * 64), ("ground_albedo", C.c_uint32 * 2),
+                ("ground_material", C.c_uint32), ("wall_albedo", C.c_uint32), ("wall_material", C.c_uint32),
+                ("sky_albedo", C.c_uint32), ("wall_z", C.c_float), ("wall_height", C.c_float), ("wall_half_width", C.c_float)]
+
+
+class DrawTAAParams(C.Structure):
+    """reference src/scene_renderer.hpp:26-33"""
+    _fields_ = [_mat("mvp"), _mat("prev_mvp"), _mat("camera"), _mat("prev_camera"), ("jitter", C.c_float * 4),
+                ("fovy_aspect_znear_zfar", C.c_float * 4)]
+
+
+lib.vkr_synth_scene.restype = None
+lib.vkr_synth_scene.argtypes = [C.c_uint32, C.c_uint32, C.POINTER(SynthScene)]
+lib.vkr_synth_camera.restype = None
+lib.vkr_synth_camera.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.POINTER(DrawTAAParams)]
+lib.vkr_mat4_inverse.restype = None
+lib.vkr_mat4_inverse.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
+lib.vkr_mat4_transpose.restype = None
+lib.vkr_mat4_transpose.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_float)]
+_sig("vkr_synth_gbuffer", C.POINTER(SynthScene), C.POINTER(DrawTAAParams), IP, IP, IP, IP, IP, VP)
+_sig("vkr_synth_gbuffer_host", C.POINTER(SynthScene), C.POINTER(DrawTAAParams), IP, IP, IP, IP, IP, C.c_int)
+
+
+def synth_scene(seed=0, objects=64):
+    s = SynthScene()
+    lib.vkr_synth_scene(seed, objects, C.byref(s))
+    return s
+
+
+def synth_camera(view_seed, frame, width, height, jitter=True):
+    p = DrawTAAParams()
+    lib.vkr_synth_camera(view_seed, frame, width, height, 1 if jitter else 0, C.byref(p))
+    return p
+
+
+def mat_inverse(m16):
+    out = (C.c_float * 16)()
+    lib.vkr_mat4_inverse(m16, out)
+    return out
+
+
+def mat_transpose(m16):
+    out = (C.c_float * 16)()
+    lib.vkr_mat4_transpose(m16, out)
+    return out
+
+
+class Gbuffer:
+    """Image set of `struct Gbuffer` (reference src/scene_renderer.hpp:11-24, ctor src/scene_renderer.cpp:8-44)."""
+
+    def __init__(self, w, h, device="cuda", pinned=False):
+        self.w, self.h = w, h
+        mips = full_mip_count(w, h)
+        mk = lambda f, ww=w, hh=h, m=1: Image(ww, hh, f, m, device=device, pinned=pinned)  # noqa: E731
+        self.albedo = mk(R8G8B8A8_SRGB)
+        self.normal = mk(R16G16_UNORM)
+        self.material = mk(R8G8B8A8_SRGB)
+        self.velocity_vectors = mk(R16G16_SFLOAT)
+        self.depth = mk(D24_UNORM_S8_UINT, m=mips)
+        self.prev_depth = mk(D24_UNORM_S8_UINT, m=mips)
+        self.downsampled_normals = mk(R16G16_UNORM, w // 2, h // 2)
+        self.downsampled_velocity_vectors = mk(R16G16_SFLOAT, w // 2, h // 2)
+
+    def input_images(self):
+        return [self.albedo, self.normal, self.material, self.velocity_vectors, self.depth]
+
+
+def synth_gbuffer(scene, params, gb, stream=None, host_threads=0):
+    """Fill gb's input images for one frame: CUDA ray-caster for device images, host twin for CPU images."""
+    a = (gb.albedo.ptr, gb.normal.ptr, gb.material.ptr, gb.velocity_vectors.ptr, gb.depth.ptr)
+    if gb.depth.device.type == "cpu":
+        check(lib.vkr_synth_gbuffer_host(C.byref(scene), C.byref(params), *a, host_threads))
+    else:
+        check(lib.vkr_synth_gbuffer(C.byref(scene), C.byref(params), *a, stream_ptr(stream)))
+
+
+# ---- remaining pass entries ---------------------------------------------------------------
+PT = C.POINTER
+_sig("vkr_pdf_preintegrate", IP, VP)
+_sig("vkr_brdf_preintegrate", FP, IP, VP)
+_sig("vkr_sssr_trace", PT(TraceParams), IP, IP, IP, FP, IP, IP, IP, VP)
+_sig("vkr_sssr_filter", PT(TraceParams), IP, IP, IP, IP, IP, IP, VP)
+_sig("vkr_sssr_blur", PT(BlurParams), IP, IP, IP, IP, IP, IP, IP, IP, VP)
+_sig("vkr_gtao_main", PT(GtaoParams), IP, IP, IP, IP, IP, C.c_uint32, VP)
+_sig("vkr_gtao_filter", PT(GtaoParams), IP, IP, IP, C.c_uint32, VP)
+_sig("vkr_gtao_accumulate", PT(AccumParams), IP, IP, IP, IP, IP, IP, C.c_uint32, VP)
+_sig("vkr_deferred_shading", PT(ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, VP)
+_sig("vkr_taa_resolve", PT(TaaParams), IP, IP, IP, IP, IP, IP, VP)
+
+
+def pdf_preintegrate(out, stream=None):
+    check(lib.vkr_pdf_preintegrate(out.ptr, stream_ptr(stream)))
+
+
+def brdf_preintegrate(halton_dev, out, stream=None):
+    check(lib.vkr_brdf_preintegrate(C.c_void_p(halton_dev.data_ptr()), out.ptr, stream_ptr(stream)))
+
+
+def sssr_trace(p, depth, dnormal, material, halton_dev, pdf, rays, occlusion, stream=None):
+    check(lib.vkr_sssr_trace(C.byref(p), depth.ptr, dnormal.ptr, material.ptr, C.c_void_p(halton_dev.data_ptr()), pdf.ptr, rays.ptr,
+                             occlusion.ptr, stream_ptr(stream)))
+
+
+def sssr_filter(p, rays, depth, albedo, normal, material, out, stream=None):
+    check(lib.vkr_sssr_filter(C.byref(p), rays.ptr, depth.ptr, albedo.ptr, normal.ptr, material.ptr, out.ptr, stream_ptr(stream)))
+
+
+def sssr_blur(p, depth, normal, refl, material, history, dvel, prev_depth, out, stream=None):
+    check(lib.vkr_sssr_blur(C.byref(p), depth.ptr, normal.ptr, refl.ptr, material.ptr, history.ptr, dvel.ptr, prev_depth.ptr, out.ptr,
+                            stream_ptr(stream)))
+
+
+def gtao_main(p, depth, normal, material, pdf, raw, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_main(C.byref(p), depth.ptr, normal.ptr, material.ptr, pdf.ptr, raw.ptr, depth_lod, stream_ptr(stream)))
+
+
+def gtao_filter(p, depth, raw, filtered, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_filter(C.byref(p), depth.ptr, raw.ptr, filtered.ptr, depth_lod, stream_ptr(stream)))
+
+
+def gtao_accumulate(p, depth, prev_depth, filtered, accumulated, dvel, history, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_accumulate(C.byref(p), depth.ptr, prev_depth.ptr, filtered.ptr, accumulated.ptr, dvel.ptr, history.ptr, depth_lod,
+                                  stream_ptr(stream)))
+
+
+def deferred_shading(p, albedo, normal, material, depth, occlusion, brdf, reflections, out, stream=None):
+    check(lib.vkr_deferred_shading(C.byref(p), albedo.ptr, normal.ptr, material.ptr, depth.ptr, occlusion.ptr, brdf.ptr, reflections.ptr,
+                                   out.ptr, stream_ptr(stream)))
+
+
+def taa_resolve(p, history, prev_depth, depth, velocity, color, out, stream=None):
+    check(lib.vkr_taa_resolve(C.byref(p), history.ptr, prev_depth.ptr, depth.ptr, velocity.ptr, color.ptr, out.ptr, stream_ptr(stream)))
