@@ -142,6 +142,10 @@ uint32_t vkr_full_mip_count(uint32_t width, uint32_t height);
 /* reference src/advanced_ssr.cpp:8-34: 128 x vec4, .x = halton(i+1,2), .y = halton(i+1,3). Host memory. */
 void vkr_halton23_seq(uint32_t count, float* out_vec4);
 
+/* Test hook: exhaustive device check of the kernels' 3-instruction unorm decode against the IEEE
+ * division; returns the number of mismatching codes (0 expected), negative on a CUDA error. */
+long long vkr_selftest_decode(void);
+
 /* ---- Hi-Z: DownsamplePass (reference src/downsample_pass.cpp) ------------------- */
 /* Task "DownsampleGbuffer" (:63-90, shaders/advanced_ssr/downsample_gbuffer.frag):
  * depth mip0 -> depth mip1 (2x2 min), normal/velocity of the min-depth texel -> out_*. */

@@ -43,6 +43,13 @@ def test_halton_table_matches():
     np.testing.assert_array_equal(vkr.halton23_seq(128), oracle_lib.halton23_seq(128))
 
 
+def test_unorm_decode_is_exact(cuda):
+    """The 3-instruction k/D decode equals the IEEE division for every D24 / UNORM16 / UNORM8 code."""
+    import ctypes
+    vkr.lib.vkr_selftest_decode.restype = ctypes.c_longlong
+    assert vkr.lib.vkr_selftest_decode() == 0
+
+
 def test_lut_kernels(cuda, oracle_luts):
     import torch
     pdf_ref, brdf_ref = oracle_luts

@@ -55,9 +55,33 @@ const float* srgb_decode_table_device() {
   return g_srgb_dev[dev];
 }
 
+// exhaustive device check of the 3-instruction unorm decodes against the IEEE division
+__global__ void selftest_decode_kernel(unsigned long long* mismatches) {
+  unsigned k = blockIdx.x * blockDim.x + threadIdx.x;   // 2^24 threads
+  unsigned bad = 0;
+  bad += d24_to_float(k) != __fdiv_rn((float)k, 16777215.0f);
+  if (k < 65536u) bad += unorm16_to_float(k) != __fdiv_rn((float)k, 65535.0f);
+  if (k < 256u) bad += unorm8_to_float(k) != __fdiv_rn((float)k, 255.0f);
+  if (bad) atomicAdd(mismatches, (unsigned long long)bad);
+}
+
 }  // namespace vkr
 
 extern "C" {
+
+/* Test hook: number of inputs for which the fast unorm decode differs from __fdiv_rn (must be 0);
+ * negative on a CUDA error. */
+long long vkr_selftest_decode(void) {
+  unsigned long long* d = nullptr;
+  unsigned long long h = 0;
+  if (cudaMalloc(&d, sizeof(h)) != cudaSuccess) return -1;
+  cudaMemset(d, 0, sizeof(h));
+  vkr::selftest_decode_kernel<<<(1u << 24) / 256, 256>>>(d);
+  cudaError_t e = cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (e != cudaSuccess) { vkr::set_error("selftest_decode: %s", cudaGetErrorString(e)); return -1; }
+  return (long long)h;
+}
 
 const char* vkr_version(void) { return "vkr_b200 0.1 (sm_100a)"; }
 const char* vkr_last_error(void) { return vkr::g_err; }

@@ -133,9 +133,19 @@ __device__ __forceinline__ f3 project_view_vec(f3 v, const CamK& c) {           
 }
 
 // ---- texel decode ----------------------------------------------------------------
-__device__ __forceinline__ float d24_to_float(uint32_t k) { return __fdiv_rn((float)(k & 0xFFFFFFu), 16777215.0f); }
-__device__ __forceinline__ float unorm16_to_float(uint32_t k) { return __fdiv_rn((float)k, 65535.0f); }
-__device__ __forceinline__ float unorm8_to_float(uint32_t k) { return __fdiv_rn((float)k, 255.0f); }
+// Correctly rounded k / D for an integer-valued k and a constant D in 3 instructions instead of
+// the ~12 of the generic IEEE division (MUFU.RCP + Newton + FCHK + slow-path branch): with
+// r = RN(1/D), q = RN(k*r), the FMA residual e = k - q*D is exact and RN(q + e*r) is the correctly
+// rounded quotient (Markstein).  vkr_selftest_decode() checks all 2^24 + 2^16 + 2^8 inputs against
+// __fdiv_rn on the device (tests/test_parity_gpu.py::test_unorm_decode_is_exact).
+__device__ __forceinline__ float div_by_const(float k, float d, float r) {
+  float q = __fmul_rn(k, r);
+  float e = __fmaf_rn(-q, d, k);
+  return __fmaf_rn(e, r, q);
+}
+__device__ __forceinline__ float d24_to_float(uint32_t k) { return div_by_const((float)(k & 0xFFFFFFu), 16777215.0f, 1.0f / 16777215.0f); }
+__device__ __forceinline__ float unorm16_to_float(uint32_t k) { return div_by_const((float)k, 65535.0f, 1.0f / 65535.0f); }
+__device__ __forceinline__ float unorm8_to_float(uint32_t k) { return div_by_const((float)k, 255.0f, 1.0f / 255.0f); }
 
 __device__ __forceinline__ uint32_t ld32(const Mip& m, int x, int y) {
   return __ldg((const uint32_t*)(m.p + (size_t)y * m.pitch) + x);

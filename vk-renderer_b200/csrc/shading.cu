@@ -13,8 +13,25 @@ struct ShadeK {
   uint32_t show_ao;
 };
 
-// brdf.glsl:6-13,:31-38,:49-56
-__device__ __forceinline__ float pow5(float x) { return powf(x, 5.0f); }
+// Colour-only arithmetic (no discrete decision depends on it): FMA contraction, reciprocal-multiply and
+// the MUFU-based pow are allowed here; everything that SELECTS something (texel footprints, the
+// closest-depth pick) stays on the unfused helpers of common.cuh.
+struct c3 { float x, y, z; };
+__device__ __forceinline__ c3 C3(float x, float y, float z) { c3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ c3 C3(f3 v) { return C3(v.x, v.y, v.z); }
+__device__ __forceinline__ c3 operator+(c3 a, c3 b) { return C3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ c3 operator-(c3 a, c3 b) { return C3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ c3 operator*(c3 a, c3 b) { return C3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ c3 operator*(c3 a, float s) { return C3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ c3 operator*(float s, c3 a) { return C3(a.x * s, a.y * s, a.z * s); }
+
+__device__ __forceinline__ float srgb_encode_fast(float l) {       // linear -> sRGB OETF, MUFU lg2/ex2
+  if (!(l > 0.0f)) return 0.0f;
+  if (l >= 1.0f) return 1.0f;
+  if (l < 0.0031308f) return 12.92f * l;
+  return 1.055f * exp2f(__log2f(l) * (1.0f / 2.4f)) - 0.055f;
+}
+
 __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip depth0, Mip depth1,
                                                                Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex, Mip out,
                                                                const float* __restrict__ srgb) {
@@ -23,63 +40,92 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Mip alb
   const float su = ((float)px + 0.5f) / (float)out.w, sv = ((float)py + 0.5f) / (float)out.h;
 
   f3 N = sample_gbuffer_normal(normal_tex, su, sv);
-  float4 a4 = sample_srgb8(albedo_tex, su, sv, srgb);
-  f3 albedo = mk3(a4.x, a4.y, a4.z);
-  float4 material = sample_srgb8(material_tex, su, sv, srgb);
-  float depth = sample_d24(depth0, su, sv);
+  // albedo (rgb), material (.g roughness, .b metallic) share one footprint (same size, same uv)
+  c3 albedo;
+  float roughness, mat_b;
+  {
+    Tap t = make_tap(su, sv, albedo_tex.w, albedo_tex.h);
+    uint32_t a00 = ld32(albedo_tex, t.x0, t.y0), a10 = ld32(albedo_tex, t.x1, t.y0), a01 = ld32(albedo_tex, t.x0, t.y1), a11 = ld32(albedo_tex, t.x1, t.y1);
+    uint32_t m00 = ld32(material_tex, t.x0, t.y0), m10 = ld32(material_tex, t.x1, t.y0), m01 = ld32(material_tex, t.x0, t.y1), m11 = ld32(material_tex, t.x1, t.y1);
+#define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
+    albedo.x = bilerp(CH(a00, 0), CH(a10, 0), CH(a01, 0), CH(a11, 0), t.wx, t.wy);
+    albedo.y = bilerp(CH(a00, 8), CH(a10, 8), CH(a01, 8), CH(a11, 8), t.wx, t.wy);
+    albedo.z = bilerp(CH(a00, 16), CH(a10, 16), CH(a01, 16), CH(a11, 16), t.wx, t.wy);
+    roughness = bilerp(CH(m00, 8), CH(m10, 8), CH(m01, 8), CH(m11, 8), t.wx, t.wy);
+    mat_b = bilerp(CH(m00, 16), CH(m10, 16), CH(m01, 16), CH(m11, 16), t.wx, t.wy);
+#undef CH
+  }
+  const float depth = sample_d24(depth0, su, sv);
 
-  // sample_ocllusion_ssr, shader.frag:103-130: of the 2x2 half-res neighbourhood pick the
-  // texel whose mip-1 depth is closest, then sample AO / reflections with the same offset.
-  float dl0 = fabsf(sample_d24(depth1, su, sv, 0, 0) - depth), dl1 = fabsf(sample_d24(depth1, su, sv, 1, 0) - depth);
-  float dl2 = fabsf(sample_d24(depth1, su, sv, 0, 1) - depth), dl3 = fabsf(sample_d24(depth1, su, sv, 1, 1) - depth);
-  float min_delta = gmin(gmin(dl0, dl1), gmin(dl2, dl3));
+  // sample_ocllusion_ssr, shader.frag:103-130.  The four textureLodOffset(depth, uv, 1, off) footprints
+  // cover a 3x3 block of half-res texels: fetch and decode each once.
   int ox, oy;
-  if (min_delta == dl0) { ox = 0; oy = 0; }
-  else if (min_delta == dl1) { ox = 1; oy = 0; }
-  else if (min_delta == dl2) { ox = 0; oy = 1; }
-  else { ox = 1; oy = 1; }
-  float occlusion = sample_rg16f(occlusion_tex, su, sv, ox, oy).x;
-  f3 reflection;
+  {
+    Tap t = make_tap(su, sv, depth1.w, depth1.h);   // only wx, wy used; indices rebuilt below with clamping per offset
+    float x = __fsub_rn(__fmul_rn(su, (float)depth1.w), 0.5f), y = __fsub_rn(__fmul_rn(sv, (float)depth1.h), 0.5f);
+    const int ix = (int)floorf(x), iy = (int)floorf(y);
+    int cx[3], cy[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) { cx[i] = min(max(ix + i, 0), depth1.w - 1); cy[i] = min(max(iy + i, 0), depth1.h - 1); }
+    float d[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+#pragma unroll
+      for (int i = 0; i < 3; i++) d[j][i] = d24_to_float(ld32(depth1, cx[i], cy[j]));
+    float dl0 = fabsf(FS(bilerp(d[0][0], d[0][1], d[1][0], d[1][1], t.wx, t.wy), depth));
+    float dl1 = fabsf(FS(bilerp(d[0][1], d[0][2], d[1][1], d[1][2], t.wx, t.wy), depth));
+    float dl2 = fabsf(FS(bilerp(d[1][0], d[1][1], d[2][0], d[2][1], t.wx, t.wy), depth));
+    float dl3 = fabsf(FS(bilerp(d[1][1], d[1][2], d[2][1], d[2][2], t.wx, t.wy), depth));
+    float min_delta = gmin(gmin(dl0, dl1), gmin(dl2, dl3));
+    if (min_delta == dl0) { ox = 0; oy = 0; }
+    else if (min_delta == dl1) { ox = 1; oy = 0; }
+    else if (min_delta == dl2) { ox = 0; oy = 1; }
+    else { ox = 1; oy = 1; }
+  }
+  const float occlusion = sample_rg16f(occlusion_tex, su, sv, ox, oy).x;
+  c3 reflection;
   {
     Tap t = make_tap(su, sv, reflections_tex.w, reflections_tex.h, ox, oy);
     f3 a = unpack_rgb8unorm(ld32(reflections_tex, t.x0, t.y0)), b = unpack_rgb8unorm(ld32(reflections_tex, t.x1, t.y0));
     f3 c = unpack_rgb8unorm(ld32(reflections_tex, t.x0, t.y1)), d = unpack_rgb8unorm(ld32(reflections_tex, t.x1, t.y1));
-    reflection = mk3(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy), bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy));
+    reflection = C3(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy), bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy));
   }
 
   f3 camera_view_vec = reconstruct_view_vec(su, sv, depth, k.cam);
   f3 world_pos = mul_m4(k.inverse_camera, camera_view_vec, 1.f);
   f3 camera_pos = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
 
-  const float metallic = gmix(0.1f, 1.0f, material.z);
-  const float roughness = material.y;
+  const float metallic = gmix(0.1f, 1.0f, mat_b);
   const f3 V = norm3(camera_pos - world_pos);
-  f3 F0 = mix3(mk3(0.04f, 0.04f, 0.04f), albedo, metallic);
-
-  const f3 LIGHT_POS = mk3(-1.85867f, 5.81832f, -0.247114f);
+  const f3 LIGHT_POS = mk3(-1.85867f, 5.81832f, -0.247114f);                 // shader.frag:37
   f3 Lv = LIGHT_POS - world_pos;
   f3 L = norm3(Lv);
   f3 H = norm3(V + L);
-  float light_distance = len3(Lv);
-  float rad = FM(0.1f, gmin(100 / FM(light_distance, light_distance), 100.0f));
+  const float ld2 = dot3(Lv, Lv);                                          // light_distance^2
+  const float rad = 0.1f * fminf(__fdividef(100.f, ld2), 100.0f);          // LIGHT_RADIANCE * min(100/d^2, 100)
 
-  float NdotL = gmax(dot3(N, L), 0.f);
-  float NdotV = gmax(dot3(N, V), 0.f);
-  float NDF = DistributionGGX(N, H, roughness);
-  float G = brdfG2(NdotV, NdotL, FM(roughness, roughness));
-  float fs = pow5(gclamp(FS(1.0f, gmax(dot3(H, V), 0.0f)), 0.0f, 1.0f));
-  f3 one = mk3(1.f, 1.f, 1.f);
-  f3 F = F0 + (one - F0) * fs;
-  f3 kD = (one - F) * FS(1.f, metallic);
-  f3 specular = (FM(NDF, G) * F) / FA(FM(FM(4.0f, NdotV), NdotL), 0.0001f);
-  float biased_rougness = gmix(k.min_r, k.max_r, roughness);
-  float2 ssr_brdf = sample_rg16f(brdf_tex, biased_rougness, NdotV);
+  const float NdotL = fmaxf(dot3(N, L), 0.f), NdotV = fmaxf(dot3(N, V), 0.f);
+  // --- colour from here on ---
+  const c3 one = C3(1.f, 1.f, 1.f);
+  const c3 F0 = C3(0.04f, 0.04f, 0.04f) * (1.0f - metallic) + albedo * metallic;
+  const float NDF = DistributionGGX(N, H, roughness);
+  const float G = brdfG2(NdotV, NdotL, roughness * roughness);
+  float fc = fminf(fmaxf(1.0f - fmaxf(dot3(H, V), 0.0f), 0.0f), 1.0f);
+  float fc2 = fc * fc;
+  const float fs = fc2 * fc2 * fc;                                          // pow(x, 5)
+  const c3 F = F0 + (one - F0) * fs;
+  const c3 kD = (one - F) * (1.f - metallic);
+  const float inv_den = __frcp_rn(4.0f * NdotV * NdotL + 0.0001f);
+  const c3 specular = F * (NDF * G * inv_den);
+  const float biased_rougness = gmix(k.min_r, k.max_r, roughness);
+  const float2 ssr_brdf = sample_rg16f(brdf_tex, biased_rougness, NdotV);
 
-  f3 Lo = ((kD * albedo) / VKR_PI + specular) * rad * NdotL;
-  Lo = Lo + reflection * (F0 * ssr_brdf.x + mk3(ssr_brdf.y, ssr_brdf.y, ssr_brdf.y));
-  f3 color = occlusion * (0.6f * albedo + Lo);
-  if (k.show_ao != 0) color = mk3(occlusion, occlusion, occlusion);
-  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_rgba8unorm(srgb_encode(color.x), srgb_encode(color.y), srgb_encode(color.z), 0.f);
+  c3 Lo = (kD * albedo * (1.0f / VKR_PI) + specular) * (rad * NdotL);
+  Lo = Lo + reflection * (F0 * ssr_brdf.x + C3(ssr_brdf.y, ssr_brdf.y, ssr_brdf.y));
+  c3 color = occlusion * (0.6f * albedo + Lo);
+  if (k.show_ao != 0) color = C3(occlusion, occlusion, occlusion);
+  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) =
+      pack_rgba8unorm(srgb_encode_fast(color.x), srgb_encode_fast(color.y), srgb_encode_fast(color.z), 0.f);
 }
 
 }  // namespace vkr

@@ -12,58 +12,100 @@ struct FilterK {
   uint32_t render_flags;
 };
 
+// Everything process_pixel() (filter.comp:110-149) derives from the TAP position alone — the ray, its
+// reconstructed hit, the radiance fetched at the hit, V, L, H, N.L, N.V and the Fresnel factor — is
+// computed once per position of a (32+2) x (8+2) tile and staged in shared memory; a pixel's five taps
+// then only combine those with its own F0 / roughness / centre depth.  (The reference evaluates the
+// whole of process_pixel five times per pixel.)  Out-of-range positions are processed like the
+// reference does: texelFetch returns zeros and the arithmetic runs on them.
+struct TapRec {
+  float fs, tl, tv, ndv;      // (1 - H.V)^5 ; (1-NdotL^2)/NdotL^2 ; (1-NdotV^2)/NdotV^2 ; NdotV
+  float r, g, b, depth;       // radiance at the hit ; mip-1 depth of the tap pixel
+};
+
+#define FT_W 32
+#define FT_H 8
+
 __global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k, Mip rays, Mip depth1, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip out,
                                                           const float* __restrict__ srgb) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
-  if (px >= out.w || py >= out.h) return;
+  __shared__ float4 s_a[(FT_W + 2) * (FT_H + 2)];
+  __shared__ float4 s_b[(FT_W + 2) * (FT_H + 2)];
   const float tsx = (float)out.w, tsy = (float)out.h;
-  const float su = (float)px / tsx, sv = (float)py / tsy;                                     // :39
+  const int bx = blockIdx.x * FT_W - 1, by = blockIdx.y * FT_H - 1;
 
-  float4 material = sample_srgb8(material_tex, su, sv, srgb);
-  const float metallic = material.z, roughness = material.y;
-  float4 a4 = sample_srgb8(albedo_tex, su, sv, srgb);
-  f3 F0 = mix3(mk3(0.04f, 0.04f, 0.04f), mk3(a4.x, a4.y, a4.z), metallic);
-  f3 color_sum = mk3(0, 0, 0), weight_sum = mk3(0, 0, 0);
-  const float center_depth = fetch_d24(depth1, px, py);                                       // :75
-  const float alpha2 = FM(roughness, roughness);
-  const int taps = (k.render_flags & VKR_SSR_NORMALIZE_REFLECTIONS) ? 5 : 1;
-  const int offx[5] = {0, -1, 0, 1, 0}, offy[5] = {0, 0, 1, 0, -1};                            // :63-69
-
-  for (int i = 0; i < taps; i++) {                                                              // process_pixel, :110-149
-    const int qx = px + offx[i], qy = py + offy[i];
+  for (int t = threadIdx.x; t < (FT_W + 2) * (FT_H + 2); t += 256) {
+    const int lx = t % (FT_W + 2), ly = t / (FT_W + 2);
+    const int qx = bx + lx, qy = by + ly;
     float4 tr = make_float4(0.f, 0.f, 0.f, 0.f);
     if (in_range(rays, qx, qy)) {
       uint2 r = ld64(rays, qx, qy);
       tr = make_float4(unorm16_to_float(r.x & 0xFFFFu), unorm16_to_float(r.x >> 16), unorm16_to_float(r.y & 0xFFFFu), unorm16_to_float(r.y >> 16));
     }
-    const float pu = (float)qx / tsx, pv = (float)qy / tsy;
+    const float pu = (float)qx / tsx, pv = (float)qy / tsy;                                      // :117 (no +0.5)
     const float pixel_depth = fetch_d24(depth1, qx, qy);
     f3 view_vec = reconstruct_view_vec(pu, pv, pixel_depth, k.cam);
     f3 Nn = mul_m4(k.normal_mat, sample_gbuffer_normal(normal_tex, pu, pv), 0.f);
     f3 hit_vec = reconstruct_view_vec(tr.x, tr.y, tr.z, k.cam);
-    f3 radiance = mk3(0, 0, 0);
-    if (tr.w != 1.0f) { float4 c = sample_srgb8(albedo_tex, tr.x, tr.y, srgb); radiance = mk3(c.x, c.y, c.z); }
+    float4 rad = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tr.w != 1.0f) rad = sample_srgb8(albedo_tex, tr.x, tr.y, srgb);                          // is_valid_ray, :93-95,:128
     f3 V = -norm3(view_vec);
     f3 L = norm3(hit_vec - view_vec);
-    // ray_weight, :97-108
     f3 H = norm3(V + L);
-    float fs = powf(gclamp(FS(1.0f, gmax(dot3(H, V), 0.0f)), 0.0f, 1.0f), 5.0f);
-    f3 one = mk3(1.f, 1.f, 1.f);
-    f3 F = F0 + (one - F0) * fs;
-    float NdotL = gmax(dot3(Nn, L), 0.f);
-    float NdotV = gmax(dot3(Nn, V), 0.f);
-    float G2 = brdfG2(NdotL, NdotV, alpha2);
-    float G1 = brdfG1(NdotV, alpha2);      // argument order as written in the reference
-    f3 weight = (F * G2) / G1;
-    float bilateral_weight = 1.0f;
-    if (k.render_flags & VKR_SSR_BILATERAL_FILTER) bilateral_weight = gmax(FS(1.f, FM(1000.f, fabsf(FS(center_depth, pixel_depth))) / center_depth), 0.f);
-    weight = weight * bilateral_weight;
-    color_sum = color_sum + weight * radiance;
-    weight_sum = weight_sum + weight;
+    float fc = gclamp(FS(1.0f, gmax(dot3(H, V), 0.0f)), 0.0f, 1.0f);
+    float fc2 = fc * fc;
+    float NdotL = gmax(dot3(Nn, L), 0.f), NdotV = gmax(dot3(Nn, V), 0.f);
+    float l2 = NdotL * NdotL, v2 = NdotV * NdotV;
+    s_a[t] = make_float4(fc2 * fc2 * fc, (1.f - l2) / l2, (1.f - v2) / v2, NdotV);
+    s_b[t] = make_float4(rad.x, rad.y, rad.z, pixel_depth);
   }
-  if (gmax(weight_sum.x, gmax(weight_sum.y, weight_sum.z)) < 0.001f) weight_sum = mk3(1, 1, 1);
-  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) =
-      pack_rgba8unorm(color_sum.x / weight_sum.x, color_sum.y / weight_sum.y, color_sum.z / weight_sum.z, 0.f);
+  __syncthreads();
+
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int px = blockIdx.x * FT_W + tx, py = blockIdx.y * FT_H + ty;
+  if (px >= out.w || py >= out.h) return;
+  const float su = (float)px / tsx, sv = (float)py / tsy;                                       // :39
+
+  float roughness, metallic;
+  float F0x, F0y, F0z;
+  {
+    Tap t = make_tap(su, sv, albedo_tex.w, albedo_tex.h);
+    uint32_t a00 = ld32(albedo_tex, t.x0, t.y0), a10 = ld32(albedo_tex, t.x1, t.y0), a01 = ld32(albedo_tex, t.x0, t.y1), a11 = ld32(albedo_tex, t.x1, t.y1);
+    uint32_t m00 = ld32(material_tex, t.x0, t.y0), m10 = ld32(material_tex, t.x1, t.y0), m01 = ld32(material_tex, t.x0, t.y1), m11 = ld32(material_tex, t.x1, t.y1);
+#define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
+    float ax = bilerp(CH(a00, 0), CH(a10, 0), CH(a01, 0), CH(a11, 0), t.wx, t.wy);
+    float ay = bilerp(CH(a00, 8), CH(a10, 8), CH(a01, 8), CH(a11, 8), t.wx, t.wy);
+    float az = bilerp(CH(a00, 16), CH(a10, 16), CH(a01, 16), CH(a11, 16), t.wx, t.wy);
+    roughness = bilerp(CH(m00, 8), CH(m10, 8), CH(m01, 8), CH(m11, 8), t.wx, t.wy);
+    metallic = bilerp(CH(m00, 16), CH(m10, 16), CH(m01, 16), CH(m11, 16), t.wx, t.wy);
+#undef CH
+    F0x = gmix(0.04f, ax, metallic); F0y = gmix(0.04f, ay, metallic); F0z = gmix(0.04f, az, metallic);   // F0_approximation
+  }
+  const float alpha2 = roughness * roughness;
+  // brdfG1(NdotV, alpha2) with the reference's swapped arguments (App. A.6 #4): the "NdotV" slot holds alpha2
+  const float a4 = alpha2 * alpha2;
+  const float tg_c = (1.f - a4) / a4;
+  const int c = (ty + 1) * (FT_W + 2) + tx + 1;
+  const float center_depth = s_b[c].w;                                                          // :75
+  const float bk = 1000.f / center_depth;
+  const bool bilateral = (k.render_flags & VKR_SSR_BILATERAL_FILTER) != 0;
+  const int taps = (k.render_flags & VKR_SSR_NORMALIZE_REFLECTIONS) ? 5 : 1;
+  const int offs[5] = {0, -1, FT_W + 2, 1, -(FT_W + 2)};                                         // :63-69: (0,0) (-1,0) (0,1) (1,0) (0,-1)
+
+  float csx = 0.f, csy = 0.f, csz = 0.f, wsx = 0.f, wsy = 0.f, wsz = 0.f;
+  for (int i = 0; i < taps; i++) {
+    const float4 A = s_a[c + offs[i]], B = s_b[c + offs[i]];
+    // ray_weight (:97-108): F * G2 / G1
+    const float L1 = sqrtf(1.f + alpha2 * A.y), L2 = sqrtf(1.f + alpha2 * A.z);
+    const float g = (1.f + sqrtf(1.f + A.w * tg_c)) / (L1 + L2);                                // (2/(L1+L2)) / (2/(1+sqrt(..)))
+    float bw = 1.0f;
+    if (bilateral) bw = gmax(1.f - fabsf(center_depth - B.w) * bk, 0.f);
+    const float gb = g * bw;
+    const float wx = (F0x + (1.f - F0x) * A.x) * gb, wy = (F0y + (1.f - F0y) * A.x) * gb, wz = (F0z + (1.f - F0z) * A.x) * gb;
+    csx += wx * B.x; csy += wy * B.y; csz += wz * B.z;
+    wsx += wx; wsy += wy; wsz += wz;
+  }
+  if (gmax(wsx, gmax(wsy, wsz)) < 0.001f) { wsx = 1.f; wsy = 1.f; wsz = 1.f; }
+  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_rgba8unorm(csx / wsx, csy / wsy, csz / wsz, 0.f);
 }
 
 }  // namespace vkr
@@ -87,7 +129,7 @@ extern "C" int vkr_sssr_filter(const VkrTraceParams* p, const VkrImage* rays, co
   k.render_flags = p->render_flags;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_filter: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_reflections->width + 31) / 32, (out_reflections->height + 7) / 8);
+  dim3 grid((out_reflections->width + FT_W - 1) / FT_W, (out_reflections->height + FT_H - 1) / FT_H);
   sssr_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(rays, 0), make_mip(depth, 1), make_mip(albedo, 0), make_mip(normal, 0),
                                                              make_mip(material, 0), make_mip(out_reflections, 0), srgb);
   return check_launch("sssr_filter_kernel");
