@@ -1,0 +1,61 @@
+/* vkr_host.h — C API of the headless host (libvkr_host.so).
+ *
+ * The host is C++: a rendergraph shim plus the reference's pass classes (vk-renderer_b200/host/),
+ * driven in the reference's frame order.  VkrApp is that frame loop without the window:
+ *   create      = reference src/main.cpp:255-309  (RenderGraph, Gbuffer, DownsamplePass, GTAO(w,h,0,1),
+ *                 AdvancedSSR, TAA, LUT pre-integration, DeferedShadingPass, color_out_tex,
+ *                 clear_depth(prev_depth, 1.0))
+ *   render_frame = reference src/main.cpp:329-421 (update_params, downsample_pass.run, ssr.run,
+ *                 gtao.add_main/filter/accumulate, shading_pass.draw, taa_pass.run, submit, the five remaps)
+ * The G-buffer rasterisation (scene_renderer.draw_taa) is the INPUT of the path: it is uploaded from
+ * host memory (upload_gbuffer) or produced on the device by the synthetic ray-caster (synth_gbuffer).
+ * This C API exists so Python (bench.py, tests) can drive the C++ host; a C++ user links the
+ * classes in vk-renderer_b200/host/passes.hpp directly.
+ * All calls return 0 on success, negative VkrStatus otherwise (vkr_host_last_error() has the text).
+ */
+#ifndef VKR_HOST_H_INCLUDED
+#define VKR_HOST_H_INCLUDED
+#include "vkr_passes.h"
+#include "vkr_synth.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct VkrApp VkrApp;
+
+const char* vkr_host_last_error(void);
+
+/* stream: a cudaStream_t to run on (e.g. the caller's), or NULL for a stream owned by the app. */
+VkrApp* vkr_app_create(int device, uint32_t width, uint32_t height, void* stream);
+void vkr_app_destroy(VkrApp* app);
+
+/* Asynchronous host->device copy of one frame's G-buffer (albedo, normal, material, velocity, depth
+ * mip 0), each laid out as vkr_image_layout() describes (mip 0 only: row_pitch[0] * height bytes).
+ * Pinned host memory makes the copies truly asynchronous. */
+int vkr_app_upload_gbuffer(VkrApp* app, const void* albedo, const void* normal, const void* material, const void* velocity, const void* depth);
+/* Device-side producer for the same five images. */
+int vkr_app_synth_gbuffer(VkrApp* app, const VkrSynthScene* scene, const VkrDrawTAAParams* params);
+
+/* One frame of the chain on the current G-buffer.  gtao_angle_jitter replaces the reference's
+ * rand()/RAND_MAX - 0.5 (src/gtao.cpp:111).  Asynchronous. */
+int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao_angle_jitter);
+
+/* Descriptor of a named image AS OF THE LAST RENDERED FRAME (the ping-pong remaps are undone in the
+ * lookup): albedo normal material velocity depth prev_depth dn dv rays raw filtered accumulated_ao
+ * reflections blurred color taa pdf brdf. */
+int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out);
+/* Asynchronous device->host copy of the whole allocation of a named image (all mips). */
+int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes);
+int vkr_app_sync(VkrApp* app);
+void* vkr_app_stream(VkrApp* app);
+/* Names of the tasks replayed by the last submit, '\n'-separated (for tests). */
+const char* vkr_app_last_tasks(VkrApp* app);
+/* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the
+ * whole DownsamplePass instead of the per-task calls. */
+int vkr_app_set_option(VkrApp* app, const char* name, float value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

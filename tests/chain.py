@@ -18,9 +18,14 @@ import vkr
 ANGLE_TABLE = [60., 300., 180., 240., 120., 0., 300., 60., 180., 120., 240., 0.]  # src/gtao.cpp:109
 
 
-def angle_offset(frame, seed=0):
+def angle_jitter(frame, seed=0):
+    """Stand-in for rand()/RAND_MAX - 0.5 of src/gtao.cpp:111, reproducible."""
     u = np.random.default_rng(1000003 * seed + frame).random()
-    return float(np.float32(ANGLE_TABLE[frame % 12] / 360.0) + np.float32(u) - np.float32(0.5))
+    return float(np.float32(np.float32(u) - np.float32(0.5)))
+
+
+def angle_offset(frame, seed=0):
+    return float(np.float32(np.float32(ANGLE_TABLE[frame % 12]) / np.float32(360.0)) + np.float32(angle_jitter(frame, seed)))
 
 
 class OracleBackend:

@@ -1,0 +1,221 @@
+// app.cpp — the reference's frame loop without the window (see include/vkr_host.h), and its C API.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <map>
+#include <string>
+
+#include "../../include/vkr_host.h"
+#include "passes.hpp"
+
+using namespace rendergraph;
+
+static thread_local char g_host_err[512] = "";
+static void host_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_host_err, sizeof(g_host_err), fmt, ap);
+  va_end(ap);
+}
+
+struct VkrApp {
+  uint32_t width, height;
+  RenderGraph render_graph;
+  Gbuffer gbuffer;
+  DownsamplePass downsample_pass;
+  GTAO gtao;
+  AdvancedSSR ssr;
+  TAA taa_pass;
+  DeferedShadingPass shading_pass;
+  ImageResourceId shadows_tex, color_out_tex;
+  std::string task_names;
+  uint64_t frames = 0;
+
+  VkrApp(int device, uint32_t w, uint32_t h, void* stream)
+      : width{w}, height{h}, render_graph{device, stream}, gbuffer{render_graph, w, h}, downsample_pass{},
+        gtao{render_graph, w, h, /*USE_RAY_QUERY*/ false, /*half_res*/ true},                   // main.cpp:265
+        ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph} {
+    ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
+    ssr.preintegrate_brdf(render_graph);
+    gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
+    shadows_tex = render_graph.create_image(sh);
+    gpu::ImageInfo co; co.format = VKR_FORMAT_R8G8B8A8_SRGB; co.width = w; co.height = h;        // main.cpp:289-291
+    color_out_tex = render_graph.create_image(co);
+    render_graph.submit();                                                                        // main.cpp:304 — LUTs are built here
+    // clear_depth(render_graph, gbuffer.prev_depth) -> 1.0 on every mip (main.cpp:306, util_passes.cpp:93)
+    // memset 0xFF also sets the stencil byte, which every kernel masks off (depth = low 24 bits).
+    const VkrImage& pd = render_graph.image(gbuffer.prev_depth);
+    VkrImage tmp;
+    const uint64_t total = vkr_image_layout(pd.width, pd.height, pd.format, pd.mip_count, &tmp);
+    if (cudaMemsetAsync(pd.base, 0xFF, total, (cudaStream_t)render_graph.stream()) != cudaSuccess)
+      throw std::runtime_error("clear_depth(prev_depth) failed");
+  }
+
+  void render_frame(const DrawTAAParams& draw_params, float angle_jitter) {
+    const float fovy = draw_params.fovy_aspect_znear_zfar.x, aspect = draw_params.fovy_aspect_znear_zfar.y;
+    const float znear = draw_params.fovy_aspect_znear_zfar.z, zfar = draw_params.fovy_aspect_znear_zfar.w;
+    glm::mat4 shadow_mvp;                                                                         // unused by the shader
+    shading_pass.update_params(draw_params.camera, shadow_mvp, fovy, aspect, znear, zfar);        // main.cpp:339
+
+    downsample_pass.run(render_graph, gbuffer.normal, gbuffer.velocity_vectors, gbuffer.depth, gbuffer.downsampled_normals,
+                        gbuffer.downsampled_velocity_vectors);                                     // main.cpp:347
+
+    auto normal_mat = glm::transpose(glm::inverse(draw_params.camera));                           // main.cpp:368
+    GTAOParams gtao_params{normal_mat, fovy, aspect, znear, zfar};
+    AdvancedSSRParams assr_params{normal_mat, fovy, aspect, znear, zfar};
+
+    ssr.run(render_graph, assr_params, draw_params, gbuffer, gtao.raw);                           // main.cpp:375
+    gtao.angle_jitter = angle_jitter;
+    gtao.add_main_pass(render_graph, gtao_params, gbuffer.depth, gbuffer.normal, gbuffer.material, ssr.get_preintegrated_pdf());  // :384
+    gtao.add_filter_pass(render_graph, gtao_params, gbuffer.depth);                               // :387
+    gtao.add_accumulate_pass(render_graph, draw_params, gbuffer);                                 // :388
+    shading_pass.draw(render_graph, gbuffer, shadows_tex, gtao.accumulated_ao, ssr.get_preintegrated_brdf(), ssr.get_blurred(), color_out_tex);  // :390
+    taa_pass.run(render_graph, gbuffer, color_out_tex, draw_params);                              // :391
+    render_graph.submit();                                                                        // :402
+    task_names.clear();
+    for (auto& n : render_graph.last_task_names()) { task_names += n; task_names += '\n'; }
+
+    render_graph.remap(gbuffer.depth, gbuffer.prev_depth);                                        // main.cpp:416-420
+    render_graph.remap(gtao.output, gtao.prev_frame);
+    taa_pass.remap_targets(render_graph);
+    ssr.remap_images(render_graph);
+    gtao.remap(render_graph);
+    frames++;
+  }
+
+  // Image by name as of the last rendered frame: after the remaps the frame's depth is in the
+  // prev_depth slot, its TAA target in the history slot, etc.
+  bool lookup(const std::string& name, ImageResourceId& id) {
+    const bool r = frames > 0;   // remapped at least once
+    if (name == "albedo") id = gbuffer.albedo;
+    else if (name == "normal") id = gbuffer.normal;
+    else if (name == "material") id = gbuffer.material;
+    else if (name == "velocity") id = gbuffer.velocity_vectors;
+    else if (name == "depth") id = r ? gbuffer.prev_depth : gbuffer.depth;
+    else if (name == "prev_depth") id = r ? gbuffer.depth : gbuffer.prev_depth;
+    else if (name == "dn") id = gbuffer.downsampled_normals;
+    else if (name == "dv") id = gbuffer.downsampled_velocity_vectors;
+    else if (name == "rays") id = ssr.get_rays();
+    else if (name == "raw") id = gtao.raw;
+    else if (name == "filtered") id = gtao.filtered;
+    else if (name == "accumulated_ao") id = r ? gtao.accumulated_history : gtao.accumulated_ao;
+    else if (name == "reflections") id = ssr.get_ouput();
+    else if (name == "blurred") id = r ? ssr.get_blurred_history() : ssr.get_blurred();
+    else if (name == "color") id = color_out_tex;
+    else if (name == "taa") id = r ? taa_pass.get_history() : taa_pass.get_output();
+    else if (name == "pdf") id = ssr.get_preintegrated_pdf();
+    else if (name == "brdf") id = ssr.get_preintegrated_brdf();
+    else return false;
+    return true;
+  }
+};
+
+extern "C" {
+
+const char* vkr_host_last_error(void) { return g_host_err; }
+
+#define VKR_TRY(...)                                                         \
+  try { __VA_ARGS__; return VKR_OK; }                                        \
+  catch (const std::exception& e) { host_error("%s", e.what()); return VKR_ERR_CUDA; }
+
+VkrApp* vkr_app_create(int device, uint32_t width, uint32_t height, void* stream) {
+  try {
+    if (width < 16 || height < 16) { host_error("vkr_app_create: extent too small"); return nullptr; }
+    return new VkrApp(device, width, height, stream);
+  } catch (const std::exception& e) {
+    host_error("%s", e.what());
+    return nullptr;
+  }
+}
+
+void vkr_app_destroy(VkrApp* app) { delete app; }
+
+int vkr_app_upload_gbuffer(VkrApp* app, const void* albedo, const void* normal, const void* material, const void* velocity, const void* depth) {
+  if (!app || !albedo || !normal || !material || !velocity || !depth) { host_error("upload_gbuffer: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    cudaStream_t st = (cudaStream_t)app->render_graph.stream();
+    const void* src[5] = {albedo, normal, material, velocity, depth};
+    ImageResourceId ids[5] = {app->gbuffer.albedo, app->gbuffer.normal, app->gbuffer.material, app->gbuffer.velocity_vectors, app->gbuffer.depth};
+    for (int i = 0; i < 5; i++) {
+      const VkrImage& im = app->render_graph.image(ids[i]);
+      size_t bytes = (size_t)im.row_pitch[0] * im.height;
+      if (cudaMemcpyAsync(im.base, src[i], bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) throw std::runtime_error("upload_gbuffer: cudaMemcpyAsync failed");
+    }
+  })
+}
+
+int vkr_app_synth_gbuffer(VkrApp* app, const VkrSynthScene* scene, const VkrDrawTAAParams* params) {
+  if (!app || !scene || !params) { host_error("synth_gbuffer: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    auto& g = app->render_graph;
+    int rc = vkr_synth_gbuffer(scene, params, &g.image(app->gbuffer.albedo), &g.image(app->gbuffer.normal), &g.image(app->gbuffer.material),
+                               &g.image(app->gbuffer.velocity_vectors), &g.image(app->gbuffer.depth), g.stream());
+    vkr_check(rc, "GbufferPass(synthetic)");
+  })
+}
+
+int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* p, float gtao_angle_jitter) {
+  if (!app || !p) { host_error("render_frame: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    DrawTAAParams d;
+    d.mvp = glm::mat4(p->mvp); d.prev_mvp = glm::mat4(p->prev_mvp); d.camera = glm::mat4(p->camera); d.prev_camera = glm::mat4(p->prev_camera);
+    d.jitter = {p->jitter[0], p->jitter[1], p->jitter[2], p->jitter[3]};
+    d.fovy_aspect_znear_zfar = {p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]};
+    app->render_frame(d, gtao_angle_jitter);
+  })
+}
+
+int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out) {
+  if (!app || !name || !out) { host_error("get_image: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  ImageResourceId id;
+  if (!app->lookup(name, id)) { host_error("get_image: unknown image '%s'", name); return VKR_ERR_INVALID_ARGUMENT; }
+  *out = app->render_graph.image(id);
+  return VKR_OK;
+}
+
+int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity) {
+  VkrImage im;
+  int rc = vkr_app_get_image(app, name, &im);
+  if (rc) return rc;
+  VkrImage tmp;
+  uint64_t total = vkr_image_layout(im.width, im.height, im.format, im.mip_count, &tmp);
+  if (!host_dst || capacity < total) { host_error("readback: destination too small (%llu < %llu)", (unsigned long long)capacity, (unsigned long long)total); return VKR_ERR_INVALID_ARGUMENT; }
+  if (cudaMemcpyAsync(host_dst, im.base, total, cudaMemcpyDeviceToHost, (cudaStream_t)app->render_graph.stream()) != cudaSuccess) {
+    host_error("readback: cudaMemcpyAsync failed");
+    return VKR_ERR_CUDA;
+  }
+  return VKR_OK;
+}
+
+int vkr_app_sync(VkrApp* app) {
+  if (!app) return VKR_ERR_INVALID_ARGUMENT;
+  VKR_TRY(app->render_graph.wait_idle())
+}
+
+void* vkr_app_stream(VkrApp* app) { return app ? app->render_graph.stream() : nullptr; }
+const char* vkr_app_last_tasks(VkrApp* app) { return app ? app->task_names.c_str() : ""; }
+
+int vkr_app_set_option(VkrApp* app, const char* name, float v) {
+  if (!app || !name) return VKR_ERR_INVALID_ARGUMENT;
+  std::string n = name;
+  if (n == "fused_hiz") app->downsample_pass.fused = v != 0.f;
+  else if (n == "gtao.mis") app->gtao.mis_gtao = v != 0.f;
+  else if (n == "gtao.two_directions") app->gtao.two_directions = v != 0.f;
+  else if (n == "gtao.only_reflections") app->gtao.only_reflections = v != 0.f;
+  else if (n == "gtao.clear_history") app->gtao.clear_history = v != 0.f;
+  else if (n == "gtao.weight_ratio") app->gtao.weight_ratio = v;
+  else if (n == "ssr.max_roughness") app->ssr.settings.max_rougness = v;
+  else if (n == "ssr.normalize") app->ssr.settings.normalize_reflections = v != 0.f;
+  else if (n == "ssr.accumulate") app->ssr.settings.accumulate_reflections = v != 0.f;
+  else if (n == "ssr.bilateral") app->ssr.settings.bilateral_filter = v != 0.f;
+  else if (n == "ssr.use_blur") app->ssr.settings.use_blur = v != 0.f;
+  else if (n == "ssr.max_accumulated_rays") app->ssr.settings.max_accumulated_rays = (int)v;
+  else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
+  else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;
+  else if (n == "shading.max_roughness") app->shading_pass.min_max_roughness.y = v;
+  else { host_error("set_option: unknown option '%s'", name); return VKR_ERR_INVALID_ARGUMENT; }
+  return VKR_OK;
+}
+
+}  // extern "C"

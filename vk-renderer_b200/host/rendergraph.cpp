@@ -1,0 +1,104 @@
+// rendergraph.cpp — see rendergraph.hpp.
+#include "rendergraph.hpp"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+
+namespace rendergraph {
+
+static void cuda_check(cudaError_t e, const char* what) {
+  if (e != cudaSuccess) throw std::runtime_error(std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+void vkr_check(int status, const char* what) {
+  if (status != 0) throw std::runtime_error(std::string(what) + ": " + vkr_last_error());
+}
+
+RenderGraph::RenderGraph(int device, void* external_stream) : device_{device} {
+  cuda_check(cudaSetDevice(device_), "cudaSetDevice");
+  if (external_stream) {
+    stream_ = external_stream;
+    owns_stream_ = false;
+  } else {
+    cudaStream_t s;
+    cuda_check(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "cudaStreamCreate");
+    stream_ = s;
+  }
+}
+
+RenderGraph::~RenderGraph() {
+  cudaSetDevice(device_);
+  if (stream_) {
+    cudaStreamSynchronize((cudaStream_t)stream_);
+    if (owns_stream_) cudaStreamDestroy((cudaStream_t)stream_);
+  }
+  for (auto& s : slots) cudaFree(s.desc.base);
+}
+
+ImageResourceId RenderGraph::create_image(const gpu::ImageInfo& info) {
+  Slot s{};
+  s.bytes = vkr_image_layout(info.width, info.height, info.format, info.mip_levels, &s.desc);
+  if (s.bytes == 0) throw std::runtime_error("create_image: unsupported format / extent / mip count");
+  cuda_check(cudaSetDevice(device_), "cudaSetDevice");
+  cuda_check(cudaMalloc(&s.desc.base, s.bytes), "cudaMalloc(image)");
+  cuda_check(cudaMemsetAsync(s.desc.base, 0, s.bytes, (cudaStream_t)stream_), "cudaMemset(image)");
+  slots.push_back(s);
+  ImageResourceId id;
+  id.index = (uint32_t)slots.size() - 1;
+  return id;
+}
+
+const VkrImage& RenderGraph::image(ImageResourceId id) const {
+  if (id.get_index() >= slots.size()) throw std::runtime_error("Invalid image resource id");
+  return slots[id.get_index()].desc;
+}
+
+gpu::ImageInfo RenderGraph::get_descriptor(ImageResourceId id) const {
+  const VkrImage& d = image(id);
+  gpu::ImageInfo info;
+  info.format = d.format; info.width = d.width; info.height = d.height; info.mip_levels = d.mip_count;
+  return info;
+}
+
+void RenderGraph::remap(ImageResourceId src, ImageResourceId dst) {
+  image(src); image(dst);
+  std::swap(slots[src.get_index()], slots[dst.get_index()]);
+}
+
+void RenderGraph::submit() {
+  cuda_check(cudaSetDevice(device_), "cudaSetDevice");
+  RenderResources resources{*this};
+  gpu::CmdContext cmd{stream_};
+  last_names.clear();
+  std::vector<std::unique_ptr<BaseTask>> run;
+  run.swap(tasks);  // a task may not enqueue tasks for this submit
+  for (auto& t : run) {
+    last_names.push_back(t->name);
+    t->write_commands(resources, cmd);
+  }
+}
+
+void RenderGraph::wait_idle() { cuda_check(cudaStreamSynchronize((cudaStream_t)stream_), "cudaStreamSynchronize"); }
+
+ImageViewId RenderGraphBuilder::make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count) {
+  const VkrImage& d = graph.image(id);
+  if (base_mip + mip_count > d.mip_count || mip_count == 0) throw std::runtime_error("Image subresource out of range");  // rendergraph.cpp:390-392
+  gpu::ImageViewRange r;
+  r.base_mip = base_mip; r.mips_count = mip_count;
+  return ImageViewId{id, r};
+}
+
+ImageViewId RenderGraphBuilder::use_color_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
+ImageViewId RenderGraphBuilder::use_depth_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
+ImageViewId RenderGraphBuilder::use_storage_image(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
+ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t, uint32_t) {
+  return make_view(id, base_mip, mip_count);
+}
+ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id) { return make_view(id, 0, graph.image(id).mip_count); }
+gpu::ImageInfo RenderGraphBuilder::get_image_info(ImageResourceId id) { return graph.get_descriptor(id); }
+
+const VkrImage* RenderResources::get_image(const ImageViewId& ref) const { return &graph.image(ref.get_id()); }
+const VkrImage* RenderResources::get_image(ImageResourceId id) const { return &graph.image(id); }
+
+}  // namespace rendergraph

@@ -1,0 +1,167 @@
+// rendergraph.hpp — headless re-creation of the interface the reference passes bind through
+// (reference src/rendergraph/rendergraph.hpp:17-158, src/rendergraph/resources.hpp:15-118,
+// src/gpu/resource_info.hpp:11-45).  Same shape — create_image / get_descriptor / add_task<T>(name,
+// setup_cb, exec_cb) / submit / remap, ImageResourceId slots that must be re-resolved every frame —
+// but the Vulkan machinery behind it (barrier derivation, VkEvents, descriptor pools, swapchain) is
+// replaced by CUDA stream order: submit() replays the task list in FIFO order onto one stream.
+// Images are linear device buffers (VkrImage); the graph owns them, passes hold only ids.
+#pragma once
+#include <cstdint>
+#include <functional>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/vkr_passes.h"
+
+namespace gpu {
+
+// reference src/gpu/resource_info.hpp:11-45 (type / aspect dropped: every view here is 2D)
+struct ImageViewRange {
+  uint32_t base_mip = 0;
+  uint32_t mips_count = 1;
+  uint32_t base_layer = 0;
+  uint32_t layers_count = 1;
+};
+
+// reference gpu::ImageInfo as the passes use it: {format, aspect, width, height, depth, mips, layers}
+struct ImageInfo {
+  uint32_t format = 0;  // VkrFormat (= VkFormat value)
+  uint32_t width = 0, height = 0;
+  uint32_t mip_levels = 1;
+  uint32_t array_layers = 1;
+  struct Extent2D { uint32_t width, height; };
+  Extent2D extent2D() const { return {width, height}; }
+};
+
+// Stands in for gpu::CmdContext (reference src/gpu/cmd_buffers.hpp:162-247): the only thing a task
+// body needs to issue work is the stream of the frame being recorded.
+struct CmdContext {
+  void* stream = nullptr;  // cudaStream_t
+};
+
+}  // namespace gpu
+
+namespace rendergraph {
+
+struct GraphResources;
+
+struct ImageResourceId {
+  ImageResourceId() {}
+  uint32_t get_index() const { return index; }
+  bool operator==(const ImageResourceId& id) const { return index == id.index; }
+
+ private:
+  uint32_t index = ~0u;
+  friend struct GraphResources;
+  friend struct RenderGraph;
+};
+
+struct ImageViewId {
+  ImageViewId() {}
+  ImageViewId(ImageResourceId id, gpu::ImageViewRange view) : res_id{id}, range{view} {}
+  ImageResourceId get_id() const { return res_id; }
+  const gpu::ImageViewRange& get_range() const { return range; }
+  operator ImageResourceId() const { return res_id; }
+
+ private:
+  ImageResourceId res_id;
+  gpu::ImageViewRange range;
+};
+
+struct RenderGraph;
+
+// reference rendergraph.hpp:17-55.  Usage declarations keep their names; they only validate the
+// subresource range (reference rendergraph.cpp:390-392 "Image subresource out of range") because
+// hazards are resolved by stream order.
+struct RenderGraphBuilder {
+  explicit RenderGraphBuilder(RenderGraph& g) : graph{g} {}
+  ImageViewId use_color_attachment(ImageResourceId id, uint32_t mip, uint32_t layer);
+  ImageViewId use_depth_attachment(ImageResourceId id, uint32_t mip, uint32_t layer);
+  ImageViewId use_storage_image(ImageResourceId id, uint32_t mip, uint32_t layer);
+  ImageViewId sample_image(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t base_layer, uint32_t layer_count);
+  ImageViewId sample_image(ImageResourceId id);  // whole image
+  gpu::ImageInfo get_image_info(ImageResourceId id);
+
+ private:
+  RenderGraph& graph;
+  ImageViewId make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count);
+};
+
+// reference rendergraph.hpp:57-83: resolves ids to memory at replay time (after any remap).
+struct RenderResources {
+  explicit RenderResources(RenderGraph& g) : graph{g} {}
+  // The image behind a view, as the C ABI wants it (whole image; the pass passes the mip window on).
+  const VkrImage* get_image(const ImageViewId& ref) const;
+  const VkrImage* get_image(ImageResourceId id) const;
+
+ private:
+  RenderGraph& graph;
+};
+
+struct BaseTask {
+  explicit BaseTask(const std::string& task_name) : name{task_name} {}
+  virtual void write_commands(RenderResources&, gpu::CmdContext&) = 0;
+  virtual ~BaseTask() {}
+  std::string name;
+};
+
+template <typename TaskData>
+using TaskRunCB = std::function<void(TaskData&, RenderResources&, gpu::CmdContext&)>;
+template <typename TaskData>
+using TaskCreateCB = std::function<void(TaskData&, RenderGraphBuilder&)>;
+
+template <typename TaskData>
+struct Task : BaseTask {
+  explicit Task(const std::string& name) : BaseTask{name} {}
+  TaskData data;
+  TaskRunCB<TaskData> callback;
+  void write_commands(RenderResources& resources, gpu::CmdContext& cmd) override { callback(data, resources, cmd); }
+};
+
+struct RenderGraph {
+  // external_stream: run on the caller's cudaStream_t instead of a stream owned by the graph
+  explicit RenderGraph(int device = 0, void* external_stream = nullptr);
+  ~RenderGraph();
+  RenderGraph(const RenderGraph&) = delete;
+  RenderGraph& operator=(const RenderGraph&) = delete;
+
+  template <typename TaskData>
+  void add_task(const std::string& name, TaskCreateCB<TaskData> create_cb, TaskRunCB<TaskData> run_cb) {  // reference :116-128
+    RenderGraphBuilder builder{*this};
+    std::unique_ptr<Task<TaskData>> ptr{new Task<TaskData>{name}};
+    create_cb(ptr->data, builder);
+    ptr->callback = run_cb;
+    tasks.push_back(std::move(ptr));
+  }
+
+  // Replays the recorded tasks in order on the graph's stream and clears the list (reference
+  // rendergraph.cpp:271-337 minus barriers / present).  Asynchronous; wait_idle() joins.
+  void submit();
+  void wait_idle();
+
+  ImageResourceId create_image(const gpu::ImageInfo& info);  // zero-initialised device memory
+  gpu::ImageInfo get_descriptor(ImageResourceId id) const;
+  void remap(ImageResourceId src, ImageResourceId dst);      // reference resources.cpp:89-91: swap slot contents
+
+  const VkrImage& image(ImageResourceId id) const;
+  void* stream() const { return stream_; }
+  const std::vector<std::string>& last_task_names() const { return last_names; }
+
+ private:
+  struct Slot { VkrImage desc; uint64_t bytes; };
+  std::vector<Slot> slots;
+  std::vector<std::unique_ptr<BaseTask>> tasks;
+  std::vector<std::string> last_names;
+  void* stream_ = nullptr;
+  bool owns_stream_ = true;
+  int device_ = 0;
+  friend struct RenderGraphBuilder;
+  friend struct RenderResources;
+};
+
+// VKCHECK analogue (reference src/gpu/common.hpp:9): non-zero C-ABI status -> std::runtime_error
+void vkr_check(int status, const char* what);
+
+}  // namespace rendergraph

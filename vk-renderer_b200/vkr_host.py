@@ -1,0 +1,107 @@
+"""ctypes binding of libvkr_host.so — the headless C++ host (rendergraph shim + the reference's
+pass classes + frame loop, include/vkr_host.h).  This is the public API a user of the repo calls:
+upload (or synthesise) a G-buffer, render_frame(), read the TAA target back.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import torch
+
+import vkr
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libvkr_host.so")
+if not os.path.exists(LIB_PATH):
+    raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+lib = C.CDLL(LIB_PATH)
+
+lib.vkr_host_last_error.restype = C.c_char_p
+lib.vkr_app_create.restype = C.c_void_p
+lib.vkr_app_create.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p]
+lib.vkr_app_destroy.restype = None
+lib.vkr_app_destroy.argtypes = [C.c_void_p]
+lib.vkr_app_upload_gbuffer.restype = C.c_int
+lib.vkr_app_upload_gbuffer.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+lib.vkr_app_synth_gbuffer.restype = C.c_int
+lib.vkr_app_synth_gbuffer.argtypes = [C.c_void_p, C.POINTER(vkr.SynthScene), C.POINTER(vkr.DrawTAAParams)]
+lib.vkr_app_render_frame.restype = C.c_int
+lib.vkr_app_render_frame.argtypes = [C.c_void_p, C.POINTER(vkr.DrawTAAParams), C.c_float]
+lib.vkr_app_get_image.restype = C.c_int
+lib.vkr_app_get_image.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(vkr.VkrImage)]
+lib.vkr_app_readback.restype = C.c_int
+lib.vkr_app_readback.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64]
+lib.vkr_app_sync.restype = C.c_int
+lib.vkr_app_sync.argtypes = [C.c_void_p]
+lib.vkr_app_stream.restype = C.c_void_p
+lib.vkr_app_stream.argtypes = [C.c_void_p]
+lib.vkr_app_last_tasks.restype = C.c_char_p
+lib.vkr_app_last_tasks.argtypes = [C.c_void_p]
+lib.vkr_app_set_option.restype = C.c_int
+lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise HostError(f"vkr_host status {rc}: {lib.vkr_host_last_error().decode()}")
+
+
+class App:
+    """Headless frame loop (reference src/main.cpp:255-421) on one device."""
+
+    def __init__(self, width, height, device=0, stream=None):
+        self.width, self.height, self.device = width, height, device
+        sp = None if stream is None else C.c_void_p(stream.cuda_stream)
+        self.h = lib.vkr_app_create(device, width, height, sp)
+        if not self.h:
+            raise HostError(lib.vkr_host_last_error().decode())
+
+    def close(self):
+        if self.h:
+            lib.vkr_app_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload_gbuffer(self, gb):
+        """gb: vkr.Gbuffer on the CPU (pinned for asynchronous copies)."""
+        ims = gb.input_images()
+        _check(lib.vkr_app_upload_gbuffer(self.h, *[C.c_void_p(i.buf.data_ptr()) for i in ims]))
+
+    def synth_gbuffer(self, scene, params):
+        _check(lib.vkr_app_synth_gbuffer(self.h, C.byref(scene), C.byref(params)))
+
+    def render_frame(self, params, angle_jitter=0.0):
+        _check(lib.vkr_app_render_frame(self.h, C.byref(params), angle_jitter))
+
+    def sync(self):
+        _check(lib.vkr_app_sync(self.h))
+
+    def set_option(self, name, value):
+        _check(lib.vkr_app_set_option(self.h, name.encode(), float(value)))
+
+    def last_tasks(self):
+        return lib.vkr_app_last_tasks(self.h).decode().split()
+
+    def image_desc(self, name):
+        d = vkr.VkrImage()
+        _check(lib.vkr_app_get_image(self.h, name.encode(), C.byref(d)))
+        return d
+
+    def readback(self, name, host_image=None, sync=True):
+        """Copy a named image (all mips) into a CPU vkr.Image (allocated if not given)."""
+        d = self.image_desc(name)
+        if host_image is None:
+            host_image = vkr.Image(d.width, d.height, d.format, d.mip_count, device="cpu")
+        _check(lib.vkr_app_readback(self.h, name.encode(), C.c_void_p(host_image.buf.data_ptr()), host_image.nbytes))
+        if sync:
+            self.sync()
+        return host_image
