@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""bench.py — full image-space chain (Hi-Z, SSR trace/filter/blur, GTAO main/filter/accumulate, deferred lighting, TAA)
+on the 3840x2160 synthetic TAA sequence (BASELINE.json configs[2]); metric Gpix/s (ms/frame in ms_per_step).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo: C++ host -> C ABI -> sm_100a kernels
+    python bench.py --impl reference --gpus N --steps K ...  # the CPU oracle (restated reference shaders) on the host cores
+
+A step = one frame of the chain.  N > 1 (torchrun): every rank renders its own independent sequence (sequences
+shard, frames of one sequence do not: SURVEY §8e) -> weak scaling, no data-path collective.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [os.path.join(ROOT, "vk-renderer_b200")]
+
+# algorithmic bytes per full-res pixel of every task (the fused Hi-Z task = 9 + 1.67)
+ALG_BYTES = {"DownsampleGbuffer+DownsampleDepth": 10.67, "DownsampleGbuffer": 9.0, "DownsampleDepth": 1.67, "SSSR_trace": 10.33,
+             "SSSR_filter": 16.0, "SSSR_blur": 14.0, "GTAO_main": 13.0, "GTAO_filter": 3.5, "GTAO_accumulate": 5.5,
+             "DeferedShading": 23.0, "TAA": 32.0}
+KERNELS_PER_FRAME = 10  # hiz tile + hiz tail, trace, filter, blur, gtao main/filter/accumulate, shading, taa
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--width", type=int, default=3840)
+    ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+
+    def run(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap", nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+                     nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                     nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake"}
+            while not self.stop_flag:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                time.sleep(0.002)
+        except Exception as e:  # NVML missing: report that instead of inventing numbers
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def result(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "samples": len(s), "reasons": sorted(self.reasons)}
+
+
+BAND = (0.375, 0.625)   # the CPU legs compute this band of output rows of every pass (a quarter of the frame)
+
+
+def cpu_chain_rate(width, height, frames, warm, threads=0):
+    """Oracle chain on the host cores (the checker doubling as CPU baseline).  Every pass computes the BAND of rows of
+    the real frame (the Hi-Z pyramid is built in full); returns (Gpix/s over the band pixels, ms per band-frame, threads, band rows)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import chain
+    import vkr
+    b = chain.OracleBackend(rows=BAND)
+    if threads:
+        b.o.lib.orc_set_threads(threads)
+    nthreads = b.o.lib.orc_get_max_threads()
+    full = chain.OracleBackend()
+    ch = chain.Chain(width, height, full, lut_size=1024)     # LUT pre-integration is init-time work, not timed
+    ch.b = b
+    scene = vkr.synth_scene(0, 64)
+    t = 0.0
+    for f in range(warm + frames):
+        P = ch.begin_frame(scene)                            # G-buffer production is the input, not timed
+        t0 = time.perf_counter()
+        ch.passes(P)
+        dt = time.perf_counter() - t0
+        ch.end_frame()
+        if f >= warm:
+            t += dt
+    band_rows = int(BAND[1] * height) - int(BAND[0] * height)
+    return width * band_rows * frames / t / 1e9, 1e3 * t / frames, nthreads, band_rows
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    gpix, ms, threads, band_rows = cpu_chain_rate(args.width, args.height, args.steps, args.warmup)
+    sample = (f"each step = rows [{int(BAND[0]*args.height)}, {int(BAND[1]*args.height)}) of one {args.width}x{args.height} frame through every pass "
+              f"({band_rows} of {args.height} rows; Hi-Z built in full), OpenMP over rows")
+    line = {"impl": "reference", "metric": "chain_throughput", "value": gpix, "unit": "Gpix/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {args.width}x{args.height} TAA sequence", "sample": sample},
+            "cpu_baseline": {"value": gpix, "unit": "Gpix/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": gpix, "unit": "Gpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference's GLSL cannot run here (no Vulkan / glslc): this is the CPU restatement of its shaders (oracle/)"}
+    print(json.dumps(line))
+
+
+def run_ours(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import vkr
+    import vkr_host
+
+    w, h, K, W = args.width, args.height, args.steps, args.warmup
+    npix = w * h
+    stream = torch.cuda.Stream()
+    app = vkr_host.App(w, h, device=local, stream=stream)
+    scene = vkr.synth_scene(rank, 64)                     # every rank renders its own sequence
+    nres = min(64, K + W)                                 # distinct frames of the sequence kept resident (wraps after 64)
+    seq_params = [vkr.synth_camera(rank, f, w, h, True) for f in range(nres)]
+    jit = [float(((f * 2654435761) % 1000) / 1000.0 - 0.5) for f in range(nres)]   # stands in for rand()/RAND_MAX - 0.5
+    resident = []
+    with torch.cuda.stream(stream):
+        for f in range(nres):
+            gb = vkr.Gbuffer(w, h, device=f"cuda:{local}")
+            vkr.synth_gbuffer(scene, seq_params[f], gb, stream=stream)
+            resident.append(gb)
+    stream.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident throughput: value ------------------------------------------------------------------------
+    def step_resident(i):
+        f = i % nres
+        app.bind_gbuffer(resident[f])
+        app.render_frame(seq_params[f], jit[f])
+
+    for i in range(W):
+        step_resident(i)
+    app.task_timing(True)
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(W, W + K):
+        step_resident(i)
+    e1.record(stream)
+    stream.synchronize()
+    sampler.stop_flag = True
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    tasks = app.task_times()
+    app.task_timing(False)
+    sampler.join(timeout=1.0)
+    ms_step = ms_total / K
+    value = world * npix * K / (ms_total * 1e-3) / 1e9
+
+    # ---- end to end through the host API with host buffers: e2e -----------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        nh = min(nres, 8 if K + W > 8 else K + W)          # pinned host frames (the H2D cost does not depend on content)
+        host_frames = [vkr.Gbuffer(w, h, device="cpu", pinned=True) for f in range(nh)]
+        for f in range(nh):
+            for d, s in zip(host_frames[f].input_images(), resident[f].input_images()):
+                d.buf.copy_(s.buf)
+        out_desc = app.image_desc("taa")
+        out_host = vkr.Image(out_desc.width, out_desc.height, out_desc.format, 1, device="cpu", pinned=True)
+        h2d = sum(int(i.desc.row_pitch[0]) * i.height for i in host_frames[0].input_images())
+        d2h = out_host.nbytes
+
+        def step_e2e(i):
+            f = i % nh
+            app.upload_gbuffer(host_frames[f])
+            app.render_frame(seq_params[f], jit[f])
+            app.readback("taa", out_host, sync=False)
+
+        for i in range(W):
+            step_e2e(i)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(stream)
+        for i in range(W, W + K):
+            step_e2e(i)
+        a1.record(stream)
+        stream.synchronize()
+        barrier()
+        ms_e2e = max_over_ranks(a0.elapsed_time(a1))
+        e2e = {"value": world * npix * K / (ms_e2e * 1e-3) / 1e9, "unit": "Gpix/s", "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "note": "pinned host G-buffer -> vkr_app_upload_gbuffer -> render_frame -> vkr_app_readback(taa), one stream"}
+
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    dom = max(tasks.items(), key=lambda kv: kv[1][0])
+    dname, (dms, dcount) = dom
+    avg_ms = dms / max(dcount, 1)
+    achieved = ALG_BYTES[dname] * npix / (avg_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(f"{w}x{h}", {}).get(dname)
+    chain_alg = 128.0 * npix
+    line = {"metric": "chain_throughput", "value": value, "unit": "Gpix/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {w}x{h} TAA sequence with synthetic velocity (BASELINE configs[2])",
+                       "frames_resident": nres, "l2": "inputs larger than L2 (one frame touches > 1 GB at 4K)",
+                       "parallelism": f"{world} independent sequence(s), one per GPU"},
+            "roofline": {"bound": "hbm", "kernel": dname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                         "chain": {"alg_bytes_per_frame": chain_alg, "achieved": chain_alg / (ms_step * 1e-3) / 1e9,
+                                   "frac": chain_alg / (ms_step * 1e-3) / 1e9 / peak},
+                         "per_task_ms": {k: v[0] / max(v[1], 1) for k, v in tasks.items()}},
+            "gpu_launches": KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+    if e2e:
+        line["e2e"] = e2e
+    if world == 1 and not args.no_cpu_baseline:
+        gpix, ms, threads, band_rows = cpu_chain_rate(w, h, 3, 1)
+        line["cpu_baseline"] = {"value": gpix, "unit": "Gpix/s", "cores": threads, "kind": "port", "ms_per_sample_frame": ms,
+                                "sample": f"rows [{int(BAND[0]*h)}, {int(BAND[1]*h)}) of 3 frames of the same {w}x{h} sequence through every pass after 1 warm-up "
+                                          f"({band_rows} of {h} rows; Hi-Z in full)"}
+    print(json.dumps(line))
+
+
+def main():
+    args = parse()
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world)
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -37,6 +37,19 @@ int vkr_app_upload_gbuffer(VkrApp* app, const void* albedo, const void* normal, 
 /* Device-side producer for the same five images. */
 int vkr_app_synth_gbuffer(VkrApp* app, const VkrSynthScene* scene, const VkrDrawTAAParams* params);
 
+/* Bind caller-owned DEVICE images as the frame's G-buffer instead of copying (inputs already resident
+ * in HBM).  Each must match the app's image (extent, format, mip count — depth carries its whole mip
+ * chain, which DownsamplePass fills in place).  The app borrows them: after the depth<->prev_depth
+ * remap the previous frame's depth image keeps serving as prev_depth, so keep it alive for one more frame. */
+int vkr_app_bind_gbuffer(VkrApp* app, const VkrImage* albedo, const VkrImage* normal, const VkrImage* material, const VkrImage* velocity,
+                         const VkrImage* depth);
+
+/* Per-task device timing (cudaEvents around every task the rendergraph replays).  task_timing(1) resets
+ * and enables; task_times() waits for the stream and returns the number of distinct tasks, their names
+ * ('\n'-separated), accumulated milliseconds and launch counts. */
+int vkr_app_task_timing(VkrApp* app, int enable);
+int vkr_app_task_times(VkrApp* app, char* names_out, uint64_t names_capacity, double* ms_out, uint64_t* count_out, uint32_t max_tasks);
+
 /* One frame of the chain on the current G-buffer.  gtao_angle_jitter replaces the reference's
  * rand()/RAND_MAX - 0.5 (src/gtao.cpp:111).  Asynchronous. */
 int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao_angle_jitter);

@@ -166,6 +166,36 @@ int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* p, float gtao_angl
   })
 }
 
+int vkr_app_bind_gbuffer(VkrApp* app, const VkrImage* albedo, const VkrImage* normal, const VkrImage* material, const VkrImage* velocity, const VkrImage* depth) {
+  if (!app || !albedo || !normal || !material || !velocity || !depth) { host_error("bind_gbuffer: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    auto& g = app->render_graph;
+    g.rebind_image(app->gbuffer.albedo, *albedo);
+    g.rebind_image(app->gbuffer.normal, *normal);
+    g.rebind_image(app->gbuffer.material, *material);
+    g.rebind_image(app->gbuffer.velocity_vectors, *velocity);
+    g.rebind_image(app->gbuffer.depth, *depth);
+  })
+}
+
+int vkr_app_task_timing(VkrApp* app, int enable) {
+  if (!app) return VKR_ERR_INVALID_ARGUMENT;
+  VKR_TRY({ app->render_graph.reset_task_times(); app->render_graph.enable_task_timing(enable != 0); })
+}
+
+int vkr_app_task_times(VkrApp* app, char* names_out, uint64_t names_capacity, double* ms_out, uint64_t* count_out, uint32_t max_tasks) {
+  if (!app || !names_out || !ms_out || !count_out) return VKR_ERR_INVALID_ARGUMENT;
+  try {
+    const auto& t = app->render_graph.collect_task_times();
+    std::string names;
+    uint32_t n = 0;
+    for (; n < t.size() && n < max_tasks; n++) { names += t[n].name; names += '\n'; ms_out[n] = t[n].ms; count_out[n] = t[n].count; }
+    if (names.size() + 1 > names_capacity) { host_error("task_times: names buffer too small"); return VKR_ERR_INVALID_ARGUMENT; }
+    std::memcpy(names_out, names.c_str(), names.size() + 1);
+    return (int)n;
+  } catch (const std::exception& e) { host_error("%s", e.what()); return VKR_ERR_CUDA; }
+}
+
 int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out) {
   if (!app || !name || !out) { host_error("get_image: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
   ImageResourceId id;

@@ -33,8 +33,40 @@ RenderGraph::~RenderGraph() {
     cudaStreamSynchronize((cudaStream_t)stream_);
     if (owns_stream_) cudaStreamDestroy((cudaStream_t)stream_);
   }
-  for (auto& s : slots) cudaFree(s.desc.base);
+  for (void* p : allocations) cudaFree(p);
+  for (auto& p : pending_) { cudaEventDestroy((cudaEvent_t)p.start); cudaEventDestroy((cudaEvent_t)p.stop); }
+  for (void* e : event_pool_) cudaEventDestroy((cudaEvent_t)e);
 }
+
+void* RenderGraph::get_event() {
+  if (!event_pool_.empty()) { void* e = event_pool_.back(); event_pool_.pop_back(); return e; }
+  cudaEvent_t e;
+  cuda_check(cudaEventCreate(&e), "cudaEventCreate");
+  return e;
+}
+
+void RenderGraph::rebind_image(ImageResourceId id, const VkrImage& external) {
+  const VkrImage& cur = image(id);
+  if (!external.base || external.width != cur.width || external.height != cur.height || external.format != cur.format || external.mip_count != cur.mip_count)
+    throw std::runtime_error("rebind_image: external image does not match the slot's descriptor");
+  slots[id.get_index()].desc = external;
+}
+
+const std::vector<RenderGraph::TaskTime>& RenderGraph::collect_task_times() {
+  wait_idle();
+  for (auto& p : pending_) {
+    float ms = 0.f;
+    cuda_check(cudaEventElapsedTime(&ms, (cudaEvent_t)p.start, (cudaEvent_t)p.stop), "cudaEventElapsedTime");
+    auto it = std::find_if(totals_.begin(), totals_.end(), [&](const TaskTime& t) { return t.name == p.name; });
+    if (it == totals_.end()) { totals_.push_back(TaskTime{p.name, 0.0, 0}); it = totals_.end() - 1; }
+    it->ms += ms; it->count += 1;
+    event_pool_.push_back(p.start); event_pool_.push_back(p.stop);
+  }
+  pending_.clear();
+  return totals_;
+}
+
+void RenderGraph::reset_task_times() { collect_task_times(); totals_.clear(); }
 
 ImageResourceId RenderGraph::create_image(const gpu::ImageInfo& info) {
   Slot s{};
@@ -44,6 +76,7 @@ ImageResourceId RenderGraph::create_image(const gpu::ImageInfo& info) {
   cuda_check(cudaMalloc(&s.desc.base, s.bytes), "cudaMalloc(image)");
   cuda_check(cudaMemsetAsync(s.desc.base, 0, s.bytes, (cudaStream_t)stream_), "cudaMemset(image)");
   slots.push_back(s);
+  allocations.push_back(s.desc.base);
   ImageResourceId id;
   id.index = (uint32_t)slots.size() - 1;
   return id;
@@ -75,7 +108,15 @@ void RenderGraph::submit() {
   run.swap(tasks);  // a task may not enqueue tasks for this submit
   for (auto& t : run) {
     last_names.push_back(t->name);
-    t->write_commands(resources, cmd);
+    if (timing_) {
+      Pending p{t->name, get_event(), get_event()};
+      cuda_check(cudaEventRecord((cudaEvent_t)p.start, (cudaStream_t)stream_), "cudaEventRecord");
+      t->write_commands(resources, cmd);
+      cuda_check(cudaEventRecord((cudaEvent_t)p.stop, (cudaStream_t)stream_), "cudaEventRecord");
+      pending_.push_back(p);
+    } else {
+      t->write_commands(resources, cmd);
+    }
   }
 }
 

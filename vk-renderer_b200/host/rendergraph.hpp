@@ -145,6 +145,17 @@ struct RenderGraph {
   gpu::ImageInfo get_descriptor(ImageResourceId id) const;
   void remap(ImageResourceId src, ImageResourceId dst);      // reference resources.cpp:89-91: swap slot contents
 
+  // Point a slot at caller-owned device memory (same extent / format / mips): lets a resident input
+  // set be bound without a copy.  The graph never frees borrowed memory; its own allocation stays alive.
+  void rebind_image(ImageResourceId id, const VkrImage& external);
+
+  // Per-task device timing: cudaEvents recorded around every task replayed by submit().
+  void enable_task_timing(bool on) { timing_ = on; }
+  struct TaskTime { std::string name; double ms = 0; uint64_t count = 0; };
+  // Waits for the stream, folds the pending event pairs into the totals and returns them.
+  const std::vector<TaskTime>& collect_task_times();
+  void reset_task_times();
+
   const VkrImage& image(ImageResourceId id) const;
   void* stream() const { return stream_; }
   const std::vector<std::string>& last_task_names() const { return last_names; }
@@ -152,6 +163,13 @@ struct RenderGraph {
  private:
   struct Slot { VkrImage desc; uint64_t bytes; };
   std::vector<Slot> slots;
+  std::vector<void*> allocations;   // everything create_image() allocated (slots may be rebound / swapped)
+  bool timing_ = false;
+  struct Pending { std::string name; void* start; void* stop; };
+  std::vector<Pending> pending_;
+  std::vector<void*> event_pool_;
+  std::vector<TaskTime> totals_;
+  void* get_event();
   std::vector<std::unique_ptr<BaseTask>> tasks;
   std::vector<std::string> last_names;
   void* stream_ = nullptr;

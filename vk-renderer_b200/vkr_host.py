@@ -41,6 +41,14 @@ lib.vkr_app_set_option.restype = C.c_int
 lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 
 
+lib.vkr_app_bind_gbuffer.restype = C.c_int
+lib.vkr_app_bind_gbuffer.argtypes = [C.c_void_p] + [C.POINTER(vkr.VkrImage)] * 5
+lib.vkr_app_task_timing.restype = C.c_int
+lib.vkr_app_task_timing.argtypes = [C.c_void_p, C.c_int]
+lib.vkr_app_task_times.restype = C.c_int
+lib.vkr_app_task_times.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_uint32]
+
+
 class HostError(RuntimeError):
     pass
 
@@ -75,6 +83,23 @@ class App:
         """gb: vkr.Gbuffer on the CPU (pinned for asynchronous copies)."""
         ims = gb.input_images()
         _check(lib.vkr_app_upload_gbuffer(self.h, *[C.c_void_p(i.buf.data_ptr()) for i in ims]))
+
+    def bind_gbuffer(self, gb):
+        """gb: vkr.Gbuffer on this device; its five input images become the frame's G-buffer (no copy)."""
+        _check(lib.vkr_app_bind_gbuffer(self.h, *[i.ptr for i in gb.input_images()]))
+
+    def task_timing(self, enable=True):
+        _check(lib.vkr_app_task_timing(self.h, 1 if enable else 0))
+
+    def task_times(self):
+        """{task name: (total ms, launches)} since task_timing(True)."""
+        names = C.create_string_buffer(4096)
+        ms, cnt = (C.c_double * 64)(), (C.c_uint64 * 64)()
+        n = lib.vkr_app_task_times(self.h, names, 4096, ms, cnt, 64)
+        if n < 0:
+            _check(n)
+        keys = names.value.decode().split("\n")[:n]
+        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(keys)}
 
     def synth_gbuffer(self, scene, params):
         _check(lib.vkr_app_synth_gbuffer(self.h, C.byref(scene), C.byref(params)))
