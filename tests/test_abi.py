@@ -1,0 +1,61 @@
+"""The C-ABI libraries load on a machine without a GPU and export every symbol include/*.h declares; compute entries
+refuse to run without a device instead of falling back (no compute calls here)."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "vk-renderer_b200")
+DECL = re.compile(r"^\s*(?:const\s+)?[A-Za-z_][\w\s\*]*?\b(vkr_\w+)\s*\(", re.M)
+
+
+def declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(DECL.findall(text)))
+
+
+@pytest.mark.parametrize("header,libname", [("vkr_passes.h", "libvkr_b200.so"), ("vkr_synth.h", "libvkr_b200.so"), ("vkr_host.h", "libvkr_host.so"),
+                                            ("vkr_multi.h", "libvkr_b200.so")])
+def test_every_declared_symbol_is_exported(header, libname):
+    if not os.path.exists(os.path.join(ROOT, "include", header)):
+        pytest.skip(f"{header} not present")
+    names = declared(header)
+    assert len(names) >= 3, names
+    lib = C.CDLL(os.path.join(PKG, libname))
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+
+
+def test_headers_compile_as_plain_c(tmp_path):
+    """The boundary is C: no C++ or torch types in the signatures."""
+    import subprocess
+    src = tmp_path / "abi.c"
+    hdrs = [h for h in sorted(os.listdir(os.path.join(ROOT, "include"))) if h.endswith(".h")]
+    src.write_text("".join(f'#include "{h}"\n' for h in hdrs) + "int main(void){return (int)sizeof(VkrImage) - 176;}\n")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), "-c", str(src), "-o", str(tmp_path / "abi.o")], check=True)
+
+
+def test_version_and_layout_helpers_work_without_a_gpu():
+    import vkr
+    assert vkr.lib.vkr_full_mip_count(3840, 2160) == 12 and vkr.lib.vkr_full_mip_count(256, 256) == 9    # scene_renderer.cpp:13
+    img = vkr.VkrImage()
+    vkr.lib.vkr_image_layout.restype = C.c_uint64
+    n = vkr.lib.vkr_image_layout(250, 130, vkr.D24_UNORM_S8_UINT, 8, C.byref(img))
+    assert n > 0 and img.row_pitch[0] == 1008 and all(img.mip_offset[i] % 256 == 0 for i in range(8))
+    assert vkr.lib.vkr_format_texel_size(vkr.R16G16B16A16_SFLOAT) == 8
+
+
+def test_compute_entry_fails_loudly_without_a_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    import vkr
+    d = vkr.Image(64, 64, vkr.D24_UNORM_S8_UINT, 7, device="cpu")
+    n = vkr.Image(64, 64, vkr.R16G16_UNORM, device="cpu")
+    v = vkr.Image(64, 64, vkr.R16G16_SFLOAT, device="cpu")
+    on = vkr.Image(32, 32, vkr.R16G16_UNORM, device="cpu")
+    ov = vkr.Image(32, 32, vkr.R16G16_SFLOAT, device="cpu")
+    assert vkr.lib.vkr_hiz_build(d.ptr, n.ptr, v.ptr, on.ptr, ov.ptr, None) == -3      # VKR_ERR_CUDA: no CPU fallback

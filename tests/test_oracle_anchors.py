@@ -1,0 +1,226 @@
+"""Analytic anchors that pin the CPU oracle (SURVEY §8c ii-vi; anchor i lives in test_hiz.py).
+
+The reference has no golden vectors and cannot run here, so the oracle is "parity unpinned" against
+upstream; these tests pin it against closed-form answers of the shader math it restates.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import chain
+import oracle_lib as orc
+import vkr
+
+FOVY, ZN, ZF = np.float32(np.pi / 3), np.float32(0.05), np.float32(80.0)
+
+
+def f32(*v):
+    return np.array(v, dtype=np.float32)
+
+
+def cam4(aspect):
+    return f32(FOVY, aspect, ZN, ZF)
+
+
+def depth_of_z(z):
+    """gbuffer_encode.glsl:71-73: d = f/(f-n) + f*n/(z*(f-n)), z negative in front of the camera."""
+    f, n = float(ZF), float(ZN)
+    return f / (f - n) + f * n / (z * (f - n))
+
+
+def reconstruct_np(u, v, d, aspect):
+    """gbuffer_encode.glsl:53-69 in float64 (the analytic side of the anchors)."""
+    f, n, tg = float(ZF), float(ZN), np.tan(float(FOVY) / 2)
+    z = n * f / (d * (f - n) - f)
+    return np.stack([-(2 * u - 1) * z * aspect * tg, -(2 * v - 1) * z * tg, z], axis=-1)
+
+
+# ---- (ii) shared encode/decode helpers -------------------------------------------------------------
+def test_normal_octahedral_roundtrip():
+    rng = np.random.default_rng(0)
+    v = rng.normal(size=(2000, 3)).astype(np.float32)
+    v /= np.linalg.norm(v, axis=1, keepdims=True)
+    worst = 0.0
+    for n in v:
+        e, back = f32(0, 0), f32(0, 0, 0)
+        orc.lib.orc_probe_encode_normal(orc.fptr(np.ascontiguousarray(n)), orc.fptr(e))
+        assert 0.0 <= e[0] <= 1.0 and 0.0 <= e[1] <= 1.0
+        orc.lib.orc_probe_decode_normal(orc.fptr(e), orc.fptr(back))
+        worst = max(worst, float(np.abs(back - n).max()))
+    assert worst < 1e-5, worst
+
+
+def test_project_inverts_reconstruct():
+    rng = np.random.default_rng(1)
+    aspect = np.float32(16 / 9)
+    c = cam4(aspect)
+    for _ in range(500):
+        uv = rng.random(2).astype(np.float32)
+        d = np.float32(depth_of_z(-rng.uniform(0.2, 60.0)))
+        p, back = f32(0, 0, 0), f32(0, 0, 0)
+        orc.lib.orc_probe_reconstruct(orc.fptr(uv), C.c_float(d), orc.fptr(c), orc.fptr(p))
+        ref = reconstruct_np(float(uv[0]), float(uv[1]), float(d), float(aspect))
+        np.testing.assert_allclose(p, ref, rtol=2e-4, atol=1e-5)
+        orc.lib.orc_probe_project(orc.fptr(p), orc.fptr(c), orc.fptr(back))
+        np.testing.assert_allclose(back[:2], uv, atol=2e-6)
+        assert abs(float(back[2]) - float(d)) < 2e-6
+
+
+def test_srgb_and_half_codecs():
+    assert orc.lib.orc_probe_srgb_decode(0) == 0.0 and orc.lib.orc_probe_srgb_decode(255) == 1.0
+    for k in range(256):
+        lin = orc.lib.orc_probe_srgb_decode(k)
+        c = k / 255.0
+        ref = c / 12.92 if c <= 0.04045 else ((c + 0.055) / 1.055) ** 2.4
+        assert abs(lin - ref) < 1e-6
+        assert abs(orc.lib.orc_probe_srgb_encode(C.c_float(lin)) * 255.0 - k) < 1e-3
+    for v in (0.0, 1.0, 0.1, 65504.0, 1e-5, -2.5):
+        assert orc.lib.orc_probe_half_roundtrip(C.c_float(v)) == float(np.float32(np.float16(v)))
+
+
+# ---- helpers: a hand-built G-buffer with identity camera --------------------------------------------
+def ident16():
+    return (C.c_float * 16)(*np.eye(4, dtype=np.float32).reshape(16))
+
+
+def flat_gbuffer(w, h, z, albedo_code=188, rough_code=128):
+    """Fronto-parallel plane at view z (camera = identity, so view normal = world normal = +z)."""
+    gb = vkr.Gbuffer(w, h, device="cpu")
+    k = int(round(depth_of_z(z) * 0xFFFFFF))
+    for img in (gb.depth, gb.prev_depth):
+        for lod in range(img.mips):
+            mw, mh = img.mip_size(lod)
+            img.upload(np.full((mh, mw), k, dtype=np.uint32), lod)
+    gb.normal.upload(np.full((h, w, 2), 32768, dtype=np.uint16))           # oct(0,0,1) = (0.5, 0.5)
+    gb.albedo.upload(np.full((h, w, 4), albedo_code, dtype=np.uint8))
+    mat = np.zeros((h, w, 4), dtype=np.uint8)
+    mat[..., 1] = rough_code
+    gb.material.upload(mat)
+    gb.velocity_vectors.upload(np.zeros((h, w, 2), dtype=np.float16))
+    return gb, k
+
+
+# ---- (iii) GTAO on an unoccluded plane ---------------------------------------------------------------
+def test_gtao_unoccluded_plane_is_one_at_the_view_axis():
+    """Plane facing the camera: every horizon sample lies in the plane, so at the view axis h = pi/2, n = 0 and
+    gtao_camera_space (main.comp:185-217) gives 2 * 0.25 * (-cos(pi) + cos 0 + 0) = 1.  Sky pixels give 0."""
+    w, h = 2048, 1024                         # half-res pixel pitch = 2.3 mrad, so the 4x4 centre block is on-axis to < 5 mrad
+    gb, _ = flat_gbuffer(w, h, -5.0)
+    d = gb.depth.download(1)
+    d[:8, :] = 0xFFFFFF                       # a strip of sky
+    gb.depth.upload(d, 1)
+    raw = vkr.Image(w // 2, h // 2, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    pdf = vkr.Image(16, 16, vkr.R32_SFLOAT, device="cpu")
+    p = vkr.GtaoParams()
+    C.memmove(p.normal_mat, ident16(), 64)
+    p.fovy, p.aspect, p.znear, p.zfar = FOVY, w / h, ZN, ZF
+    p.angle_offset, p.weight_ratio, p.use_mis, p.two_directions, p.reflections_only = 0.125, 1.0, 0, 0, 0
+    orc.ok(orc.lib.orc_gtao_main(C.byref(p), gb.depth.ptr, gb.normal.ptr, gb.material.ptr, pdf.ptr, raw.ptr, 1, 0, 0))
+    ao = raw.download()[..., 0].astype(np.float32)
+    cy, cx = h // 4, w // 4
+    centre = ao[cy - 2:cy + 2, cx - 2:cx + 2]
+    # off the axis by an angle t the single-sided slice integral is 1 +- (pi/2) t to first order
+    assert np.abs(centre - 1.0).max() < 1.2e-2 and abs(float(centre.mean()) - 1.0) < 4e-3, centre
+    assert (ao[:3, :] == 0).all()
+    body = ao[8:, :]
+    assert np.isfinite(body).all() and body.min() >= 0.0          # single-sided slices: no closed form off the axis
+
+
+# ---- (iv) BRDF LUT limits ------------------------------------------------------------------------------
+def test_brdf_lut_mirror_limit():
+    """preintegrate_ssr.comp: as roughness -> 0 and N.V -> 1 the split sum A + B -> 1 and B -> 0 (F = F0)."""
+    b = chain.OracleBackend()
+    lut = vkr.Image(256, 256, vkr.R16G16_SFLOAT, device="cpu")
+    b.brdf_lut(b.halton(), lut)
+    t = lut.download().astype(np.float32)
+    a, bb = t[255, 0, 0], t[255, 0, 1]
+    assert abs(a + bb - 1.0) < 2e-2 and bb < 1e-3, (a, bb)
+    assert (t[..., 0] >= 0).all() and (t[..., 0] + t[..., 1] <= 1.02).all()
+    # grazing angle on a smooth surface: Fresnel term dominates
+    assert t[0, 0, 1] > 0.5 * (t[0, 0, 0] + t[0, 0, 1])
+
+
+# ---- (v) TAA converges geometrically on a static input ---------------------------------------------------
+def test_taa_static_input_converges_like_0p9_pow_k():
+    w, h = 64, 32
+    gb, _ = flat_gbuffer(w, h, -3.0)
+    color = vkr.Image(w, h, vkr.R8G8B8A8_SRGB, device="cpu").upload(np.full((h, w, 4), 188, dtype=np.uint8))
+    c = orc.lib.orc_probe_srgb_decode(188)
+    hist = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    tgt = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    p = vkr.TaaParams()
+    C.memmove(p.inverse_camera, ident16(), 64)
+    C.memmove(p.prev_inverse_camera, ident16(), 64)
+    p.fovy_aspect_znear_zfar[:] = [FOVY, w / h, ZN, ZF]
+    for k in range(12):
+        orc.ok(orc.lib.orc_taa_resolve(C.byref(p), hist.ptr, gb.prev_depth.ptr, gb.depth.ptr, gb.velocity_vectors.ptr, color.ptr, tgt.ptr, 0, 0))
+        out = tgt.download().astype(np.float32)[..., :3]
+        expect = c * (1.0 - 0.9 ** (k + 1))
+        assert np.abs(out - expect).max() < 2e-3 * (k + 1) ** 0.5, (k, out[0, 0], expect)   # fp16 storage each frame
+        hist, tgt = tgt, hist
+
+
+# ---- (vi) SSR on a mirror floor under a wall --------------------------------------------------------------
+def test_ssr_mirror_floor_hits_the_reflected_ray():
+    """Ground plane with roughness 0 (VNDF collapses to the geometric normal) in front of the back wall: for every
+    valid hit, the reconstructed hit point must lie on the mirror-reflected ray of the pixel's view vector."""
+    w, h = 512, 288
+    scene = vkr.synth_scene(0, 0)                          # ground + wall only
+    scene.ground_material = 0                              # roughness code 0, metallic 0
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=16)
+    P = oc.begin_frame(scene, jitter=False)
+    steps = oc.steps(P)
+    steps[0][1]()                                          # Hi-Z
+    steps[1][1]()                                          # SSSR_trace
+    rays = oc.rays.download().astype(np.float64) / 65535.0
+    valid = oc.rays.download()[..., 3] != 65535
+    h2, w2 = valid.shape
+    aspect = w / h
+    d1 = oc.gb.depth.download(1).astype(np.float64) / 0xFFFFFF
+    nrm = oc.gb.downsampled_normals.download().astype(np.float64) / 65535.0
+    ys, xs = np.nonzero(valid)
+    assert len(ys) > 0.02 * w2 * h2, "the synthetic floor should reflect the wall in a sizeable region"
+    u, v = (xs + 0.5) / w2, (ys + 0.5) / h2
+    Pv = reconstruct_np(u, v, d1[ys, xs], aspect)
+    # view-space normal of the pixel: decode the oct normal (gbuffer_encode.glsl:29-37), rotate by normal_mat
+    e = nrm[ys, xs] * 2 - 1
+    n = np.stack([e[:, 0], e[:, 1], 1 - np.abs(e[:, 0]) - np.abs(e[:, 1])], axis=-1)
+    neg = n[:, 2] < 0
+    nx = (1 - np.abs(n[:, 1])) * np.where(n[:, 0] >= 0, 1, -1)
+    ny = (1 - np.abs(n[:, 0])) * np.where(n[:, 1] >= 0, 1, -1)
+    n[neg, 0], n[neg, 1] = nx[neg], ny[neg]
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    M = np.array(list(P["trace"].normal_mat), dtype=np.float64).reshape(4, 4).T[:3, :3]
+    nv = n @ M.T
+    nv /= np.linalg.norm(nv, axis=1, keepdims=True)
+    R = Pv - 2 * np.sum(nv * Pv, axis=1, keepdims=True) * nv
+    R /= np.linalg.norm(R, axis=1, keepdims=True)
+    hit = rays[ys, xs]
+    Hv = reconstruct_np(hit[:, 0], hit[:, 1], hit[:, 2], aspect)
+    # screen-space test: the hit texel must sit on the projection of the mirror ray (a straight line through the pixel)
+    def project_np(p):
+        tg = np.tan(float(FOVY) / 2)
+        return np.stack([0.5 * (p[:, 0] / (-p[:, 2] * tg * aspect)) + 0.5, 0.5 * (p[:, 1] / (-p[:, 2] * tg)) + 0.5], axis=-1)
+    a, b = project_np(Pv) * [w2, h2], project_np(Pv + R) * [w2, h2]
+    t = (b - a) / np.maximum(np.linalg.norm(b - a, axis=1, keepdims=True), 1e-12)
+    q = hit[:, :2] * [w2, h2] - a
+    perp = np.abs(q[:, 0] * t[:, 1] - q[:, 1] * t[:, 0])           # half-res texels off the line
+    along = q[:, 0] * t[:, 0] + q[:, 1] * t[:, 1]
+    floor = n[:, 1] > 0.99                                         # only the floor is a mirror here
+    assert floor.sum() > 0.5 * len(ys)
+    assert np.quantile(perp[floor], 0.999) < 1.0, np.quantile(perp[floor], [0.5, 0.9, 0.99, 1.0])
+    assert (along[floor] > 1.5).all()                              # forward along the ray, past the 2-texel self-hit guard
+    # and in 3D: the reconstructed hit lies on the mirror ray to within the angle one texel subtends at that distance
+    D = Hv - Pv
+    dist = np.linalg.norm(D, axis=1)
+    cosang = np.sum(D * R, axis=1) / np.maximum(dist, 1e-9)
+    ang = np.degrees(np.arccos(np.clip(cosang[floor], -1, 1)))
+    assert np.quantile(ang, 0.5) < 0.5 and ang.max() < 5.0, np.quantile(ang, [0.5, 0.9, 0.99, 1.0])
+    # and the hit must be on real geometry: depth buffer at the hit uv agrees with the ray depth (trace.comp:111-118)
+    hx = np.clip((hit[floor, 0] * w2).astype(int), 0, w2 - 1)
+    hy = np.clip((hit[floor, 1] * h2).astype(int), 0, h2 - 1)
+    f, nn = float(ZF), float(ZN)
+    lin = lambda d: nn * f / (d * (f - nn) - f)  # noqa: E731
+    dz = lin(hit[floor, 2]) - lin(d1[hy, hx])
+    assert np.quantile(np.abs(dz), 0.99) < 0.35
