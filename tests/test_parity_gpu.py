@@ -128,10 +128,16 @@ def test_free_running_chain(cuda, w, h, frames):
     for r in report:
         if r["image"] in ("depth", "dn", "dv") and r["mismatches"]:
             failures.append(r)
-    first = {r["image"]: r for r in report if r["frame"] == 1}
-    last = {r["image"]: r for r in report if r["frame"] == frames - 1}
+    # per frame: the stated tolerance of every image (tests/parity.py); a reprojection accept/reject that flips on a
+    # handful of texels is inside it (<= 1e-4 of texels) and decays with 0.9^k afterwards.
+    # no drift: the last frame is not worse than the worst earlier frame by more than 3 dB, and stays above the floor.
+    for r in report:
+        if r["frame"] >= 1 and r["image"] in parity.TOLERANCES and r["image"] not in ("depth", "dn", "dv", "rays", "raw"):
+            if not parity.TOLERANCES[r["image"]](r):
+                failures.append(r)
     for o in ("accumulated_ao", "blurred", "color", "taa"):
-        floor = {"accumulated_ao": 45.0, "blurred": 35.0, "color": 40.0, "taa": 40.0}[o]
-        if last[o]["psnr"] < floor or min(last[o]["psnr"], 100.0) < min(first[o]["psnr"], 100.0) - 6.0:
-            failures.append(dict(drift=o, first=first[o]["psnr"], last=last[o]["psnr"]))
+        series = [min(r["psnr"], 120.0) for r in report if r["image"] == o and r["frame"] >= 1]
+        floor = {"accumulated_ao": 60.0, "blurred": 45.0, "color": 50.0, "taa": 50.0}[o]
+        if series[-1] < floor or series[-1] < min(series[:-1]) - 3.0:
+            failures.append(dict(drift=o, series=series))
     assert not failures, failures

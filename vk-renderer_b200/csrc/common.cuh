@@ -47,6 +47,10 @@ struct CamK {  // camera constants; tg = tanf(fovy/2) evaluated once on the host
 };
 CamK make_cam(float fovy, float aspect, float znear, float zfar);
 
+struct Dim { float w, h, rw, rh; };   // extent and RN(1/extent): pixel-centre uv without a division (see pixel_uv)
+inline Dim make_dim(uint32_t w, uint32_t h) { Dim d; d.w = (float)w; d.h = (float)h; d.rw = 1.0f / d.w; d.rh = 1.0f / d.h; return d; }
+inline bool same_extent(const VkrImage* a, const VkrImage* b) { return a->width == b->width && a->height == b->height; }
+
 struct Mat4 { float m[16]; };  // column-major
 inline Mat4 make_mat(const float* p) { Mat4 r; for (int i = 0; i < 16; i++) r.m[i] = p[i]; return r; }
 
@@ -223,6 +227,96 @@ __device__ __forceinline__ float4 sample_srgb8(const Mip& m, float u, float v, c
 }
 __device__ __forceinline__ f3 unpack_rgb8unorm(uint32_t k) {
   return mk3(unorm8_to_float(k & 255u), unorm8_to_float((k >> 8) & 255u), unorm8_to_float((k >> 16) & 255u));
+}
+
+// ---- value-only fast paths -------------------------------------------------------
+// Precision policy: a quantity needs the unfused, IEEE-divided evaluation above only if a DISCONTINUOUS
+// choice hangs on it (a texelFetch cell index, an argmin between near-tied candidates, a radius floor).
+// Bilinear results are continuous in their coordinates and thresholds on continuous quantities flip on a
+// ~1e-7 fraction of pixels, so everything below may use FMA contraction, weight-form bilinear (4 FMA per
+// channel instead of 12 unfused ops), MUFU reciprocal / rsqrt.  Deviation from the oracle stays ~1e-6
+// relative, three orders of magnitude inside the stated output tolerances (tests/parity.py).
+
+// (px + 0.5) / W and px / W, correctly rounded in 3 instructions (checked exhaustively for every
+// W <= 16384, px < W against the IEEE division: tests/test_abi.py::test_pixel_uv_division_is_exact).
+__device__ __forceinline__ float pixel_uv(int p, float dim, float rdim) { return div_by_const((float)p + 0.5f, dim, rdim); }
+__device__ __forceinline__ float texel_uv(int p, float dim, float rdim) { return div_by_const((float)p, dim, rdim); }
+
+struct TapW { int x0, x1, y0, y1; float w00, w10, w01, w11; };
+__device__ __forceinline__ TapW make_tapw(const Tap& t) {
+  TapW r;
+  r.x0 = t.x0; r.x1 = t.x1; r.y0 = t.y0; r.y1 = t.y1;
+  r.w11 = t.wx * t.wy; r.w10 = t.wx - r.w11; r.w01 = t.wy - r.w11; r.w00 = (1.0f - t.wx) - r.w01;
+  return r;
+}
+__device__ __forceinline__ TapW make_tapw(float u, float v, int w, int h, int ox = 0, int oy = 0) { return make_tapw(make_tap(u, v, w, h, ox, oy)); }
+__device__ __forceinline__ float wsum(float a, float b, float c, float d, const TapW& w) {
+  return fmaf(d, w.w11, fmaf(c, w.w01, fmaf(b, w.w10, a * w.w00)));
+}
+// A footprint whose weights are within 2^-10 of a corner (a same-size image sampled at its own pixel
+// centres: |w - {0,1}| <= px * 2^-23) collapses to that texel; the dropped term is < 2.5e-4 of the
+// neighbour difference.  Only used for colour-like values, never for depth.
+__device__ __forceinline__ bool tap_is_texel(const Tap& t, int& x, int& y) {
+  const float e = 0.0009765625f;
+  bool okx = (t.wx < e) || (t.wx > 1.0f - e), oky = (t.wy < e) || (t.wy > 1.0f - e);
+  x = (t.wx < 0.5f) ? t.x0 : t.x1;
+  y = (t.wy < 0.5f) ? t.y0 : t.y1;
+  return okx && oky;
+}
+
+// single-MUFU reciprocal / square root / division (2 ulp): the IEEE forms cost 8-12 instructions plus a slow-path call
+__device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float div_fast(float a, float b) { return a * rcp_fast(b); }
+__device__ __forceinline__ float dot3f(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ f3 norm3f(f3 a) { float s = rsqrtf(dot3f(a, a)); return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float len3f(f3 a) { return sqrt_fast(dot3f(a, a)); }
+__device__ __forceinline__ f3 sub3f(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 mul_m4f(const Mat4& M, f3 v) {   // M * (v, 1), xyz
+  return mk3(fmaf(M.m[8], v.z, fmaf(M.m[4], v.y, fmaf(M.m[0], v.x, M.m[12]))), fmaf(M.m[9], v.z, fmaf(M.m[5], v.y, fmaf(M.m[1], v.x, M.m[13]))),
+             fmaf(M.m[10], v.z, fmaf(M.m[6], v.y, fmaf(M.m[2], v.x, M.m[14]))));
+}
+__device__ __forceinline__ f3 mul_m3f(const Mat4& M, f3 v) {   // M * (v, 0), xyz
+  return mk3(fmaf(M.m[8], v.z, fmaf(M.m[4], v.y, M.m[0] * v.x)), fmaf(M.m[9], v.z, fmaf(M.m[5], v.y, M.m[1] * v.x)),
+             fmaf(M.m[10], v.z, fmaf(M.m[6], v.y, M.m[2] * v.x)));
+}
+struct CamF { float aspect_tg, tg, nf, fmn, zfar; };   // hoisted products for the fast reconstruct
+__device__ __forceinline__ CamF make_camf(const CamK& c) {
+  CamF r; r.aspect_tg = c.aspect * c.tg; r.tg = c.tg; r.nf = FM(c.znear, c.zfar); r.fmn = FS(c.zfar, c.znear); r.zfar = c.zfar; return r;
+}
+// d*(f-n) - f cancels catastrophically for far depths (|den| ~ 0.1 against terms of 80): a fused or reordered
+// evaluation moves z by up to ~1e-2 view units there, which is the size of the reprojection thresholds (0.01 .. 0.2)
+// downstream.  So the denominator keeps the oracle's unfused rounding; only the final division is approximate (2 ulp).
+__device__ __forceinline__ float linearize_fast(float d, const CamF& c) { return c.nf * rcp_fast(FS(FM(d, c.fmn), c.zfar)); }
+__device__ __forceinline__ f3 reconstruct_fast(float u, float v, float d, const CamF& c) {
+  float z = linearize_fast(d, c);
+  return mk3((1.0f - 2.f * u) * (z * c.aspect_tg), (1.0f - 2.f * v) * (z * c.tg), z);
+}
+__device__ __forceinline__ f3 decode_normal_fast(float u, float v) {
+  u = fmaf(2.f, u, -1.f); v = fmaf(2.f, v, -1.f);
+  f3 n = mk3(u, v, 1.0f - fabsf(u) - fabsf(v));
+  if (n.z < 0.0f) {
+    float tx = (1.0f - fabsf(n.y)) * sign_nz(n.x), ty = (1.0f - fabsf(n.x)) * sign_nz(n.y);
+    n.x = tx; n.y = ty;
+  }
+  return norm3f(n);
+}
+__device__ __forceinline__ float2 wsum2(float2 a, float2 b, float2 c, float2 d, const TapW& w) {
+  return make_float2(wsum(a.x, b.x, c.x, d.x, w), wsum(a.y, b.y, c.y, d.y, w));
+}
+__device__ __forceinline__ float2 sample_rg16f_fast(const Mip& m, const TapW& t) {
+  return wsum2(unpack_rg16f(ld32(m, t.x0, t.y0)), unpack_rg16f(ld32(m, t.x1, t.y0)), unpack_rg16f(ld32(m, t.x0, t.y1)), unpack_rg16f(ld32(m, t.x1, t.y1)), t);
+}
+__device__ __forceinline__ float2 sample_rg16unorm_fast(const Mip& m, const TapW& t) {
+  return wsum2(unpack_rg16unorm(ld32(m, t.x0, t.y0)), unpack_rg16unorm(ld32(m, t.x1, t.y0)), unpack_rg16unorm(ld32(m, t.x0, t.y1)),
+               unpack_rg16unorm(ld32(m, t.x1, t.y1)), t);
+}
+// Bilinear oct-normal at uv, or the single texel when the footprint is degenerate (same-size image, own pixel centre).
+__device__ __forceinline__ f3 sample_gbuffer_normal_fast(const Mip& m, float u, float v) {
+  Tap t = make_tap(u, v, m.w, m.h);
+  int x, y;
+  float2 e = tap_is_texel(t, x, y) ? unpack_rg16unorm(ld32(m, x, y)) : sample_rg16unorm_fast(m, make_tapw(t));
+  return decode_normal_fast(e.x, e.y);
 }
 
 // ---- texel encode ----------------------------------------------------------------

@@ -32,36 +32,56 @@ __device__ __forceinline__ float srgb_encode_fast(float l) {       // linear -> 
   return 1.055f * exp2f(__log2f(l) * (1.0f / 2.4f)) - 0.055f;
 }
 
-__global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip depth0, Mip depth1,
+// SAME: albedo / normal / material have the output's extent, so their bilinear footprint at the pixel's own
+// centre is the texel itself (common.cuh tap_is_texel).
+template <bool SAME>
+__global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Dim dim, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip depth0, Mip depth1,
                                                                Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex, Mip out,
                                                                const float* __restrict__ srgb) {
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
-  const float su = ((float)px + 0.5f) / (float)out.w, sv = ((float)py + 0.5f) / (float)out.h;
+  const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
+#define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
 
-  f3 N = sample_gbuffer_normal(normal_tex, su, sv);
-  // albedo (rgb), material (.g roughness, .b metallic) share one footprint (same size, same uv)
+  f3 N;
   c3 albedo;
   float roughness, mat_b;
-  {
-    Tap t = make_tap(su, sv, albedo_tex.w, albedo_tex.h);
+  if (SAME) {
+    float2 e = unpack_rg16unorm(ld32(normal_tex, px, py));
+    N = decode_normal_fast(e.x, e.y);
+    const uint32_t a = ld32(albedo_tex, px, py), m = ld32(material_tex, px, py);
+    albedo = C3(CH(a, 0), CH(a, 8), CH(a, 16));
+    roughness = CH(m, 8); mat_b = CH(m, 16);
+    if (((m >> 8) & 255u) == 0u) {
+      // roughness == 0 is a singular point of the BRDF (alpha2 * x / 0 is NaN for alpha2 == 0 but +inf for any
+      // alpha2 > 0): a sky / cleared texel beside geometry gets a ~1e-5-weight bleed from its neighbours in the
+      // reference's bilinear fetch, which decides between the two.  Evaluate the real footprint for these texels.
+      const Tap t = make_tap(su, sv, material_tex.w, material_tex.h);
+      roughness = bilerp(CH(ld32(material_tex, t.x0, t.y0), 8), CH(ld32(material_tex, t.x1, t.y0), 8), CH(ld32(material_tex, t.x0, t.y1), 8),
+                         CH(ld32(material_tex, t.x1, t.y1), 8), t.wx, t.wy);
+    }
+  } else {
+    N = sample_gbuffer_normal_fast(normal_tex, su, sv);
+    // albedo (rgb), material (.g roughness, .b metallic) share one footprint (same size, same uv)
+    const TapW t = make_tapw(su, sv, albedo_tex.w, albedo_tex.h);
     uint32_t a00 = ld32(albedo_tex, t.x0, t.y0), a10 = ld32(albedo_tex, t.x1, t.y0), a01 = ld32(albedo_tex, t.x0, t.y1), a11 = ld32(albedo_tex, t.x1, t.y1);
     uint32_t m00 = ld32(material_tex, t.x0, t.y0), m10 = ld32(material_tex, t.x1, t.y0), m01 = ld32(material_tex, t.x0, t.y1), m11 = ld32(material_tex, t.x1, t.y1);
-#define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
-    albedo.x = bilerp(CH(a00, 0), CH(a10, 0), CH(a01, 0), CH(a11, 0), t.wx, t.wy);
-    albedo.y = bilerp(CH(a00, 8), CH(a10, 8), CH(a01, 8), CH(a11, 8), t.wx, t.wy);
-    albedo.z = bilerp(CH(a00, 16), CH(a10, 16), CH(a01, 16), CH(a11, 16), t.wx, t.wy);
-    roughness = bilerp(CH(m00, 8), CH(m10, 8), CH(m01, 8), CH(m11, 8), t.wx, t.wy);
-    mat_b = bilerp(CH(m00, 16), CH(m10, 16), CH(m01, 16), CH(m11, 16), t.wx, t.wy);
-#undef CH
+    albedo.x = wsum(CH(a00, 0), CH(a10, 0), CH(a01, 0), CH(a11, 0), t);
+    albedo.y = wsum(CH(a00, 8), CH(a10, 8), CH(a01, 8), CH(a11, 8), t);
+    albedo.z = wsum(CH(a00, 16), CH(a10, 16), CH(a01, 16), CH(a11, 16), t);
+    roughness = wsum(CH(m00, 8), CH(m10, 8), CH(m01, 8), CH(m11, 8), t);
+    mat_b = wsum(CH(m00, 16), CH(m10, 16), CH(m01, 16), CH(m11, 16), t);
   }
+#undef CH
+  // Exact (unfused) from here to the pick: on planar surfaces the four deltas are near-ties and the argmin
+  // decides which half-res texel feeds AO / reflections.
   const float depth = sample_d24(depth0, su, sv);
 
   // sample_ocllusion_ssr, shader.frag:103-130.  The four textureLodOffset(depth, uv, 1, off) footprints
   // cover a 3x3 block of half-res texels: fetch and decode each once.
   int ox, oy;
+  Tap t1 = make_tap(su, sv, depth1.w, depth1.h);
   {
-    Tap t = make_tap(su, sv, depth1.w, depth1.h);   // only wx, wy used; indices rebuilt below with clamping per offset
     float x = __fsub_rn(__fmul_rn(su, (float)depth1.w), 0.5f), y = __fsub_rn(__fmul_rn(sv, (float)depth1.h), 0.5f);
     const int ix = (int)floorf(x), iy = (int)floorf(y);
     int cx[3], cy[3];
@@ -72,53 +92,65 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Mip alb
     for (int j = 0; j < 3; j++)
 #pragma unroll
       for (int i = 0; i < 3; i++) d[j][i] = d24_to_float(ld32(depth1, cx[i], cy[j]));
-    float dl0 = fabsf(FS(bilerp(d[0][0], d[0][1], d[1][0], d[1][1], t.wx, t.wy), depth));
-    float dl1 = fabsf(FS(bilerp(d[0][1], d[0][2], d[1][1], d[1][2], t.wx, t.wy), depth));
-    float dl2 = fabsf(FS(bilerp(d[1][0], d[1][1], d[2][0], d[2][1], t.wx, t.wy), depth));
-    float dl3 = fabsf(FS(bilerp(d[1][1], d[1][2], d[2][1], d[2][2], t.wx, t.wy), depth));
+    float dl0 = fabsf(FS(bilerp(d[0][0], d[0][1], d[1][0], d[1][1], t1.wx, t1.wy), depth));
+    float dl1 = fabsf(FS(bilerp(d[0][1], d[0][2], d[1][1], d[1][2], t1.wx, t1.wy), depth));
+    float dl2 = fabsf(FS(bilerp(d[1][0], d[1][1], d[2][0], d[2][1], t1.wx, t1.wy), depth));
+    float dl3 = fabsf(FS(bilerp(d[1][1], d[1][2], d[2][1], d[2][2], t1.wx, t1.wy), depth));
     float min_delta = gmin(gmin(dl0, dl1), gmin(dl2, dl3));
     if (min_delta == dl0) { ox = 0; oy = 0; }
     else if (min_delta == dl1) { ox = 1; oy = 0; }
     else if (min_delta == dl2) { ox = 0; oy = 1; }
     else { ox = 1; oy = 1; }
   }
-  const float occlusion = sample_rg16f(occlusion_tex, su, sv, ox, oy).x;
+  // --- value-only from here on ---
+  float occlusion;
   c3 reflection;
   {
-    Tap t = make_tap(su, sv, reflections_tex.w, reflections_tex.h, ox, oy);
-    f3 a = unpack_rgb8unorm(ld32(reflections_tex, t.x0, t.y0)), b = unpack_rgb8unorm(ld32(reflections_tex, t.x1, t.y0));
-    f3 c = unpack_rgb8unorm(ld32(reflections_tex, t.x0, t.y1)), d = unpack_rgb8unorm(ld32(reflections_tex, t.x1, t.y1));
-    reflection = C3(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy), bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy));
+    // occlusion and reflections have the extent of depth mip 1 in the reference (W/2 x H/2): one footprint serves both
+    const bool shared_fp = occlusion_tex.w == reflections_tex.w && occlusion_tex.h == reflections_tex.h;
+    const TapW t = make_tapw(su, sv, occlusion_tex.w, occlusion_tex.h, ox, oy);
+    occlusion = wsum(unpack_rg16f(ld32(occlusion_tex, t.x0, t.y0)).x, unpack_rg16f(ld32(occlusion_tex, t.x1, t.y0)).x,
+                     unpack_rg16f(ld32(occlusion_tex, t.x0, t.y1)).x, unpack_rg16f(ld32(occlusion_tex, t.x1, t.y1)).x, t);
+    const TapW tr = shared_fp ? t : make_tapw(su, sv, reflections_tex.w, reflections_tex.h, ox, oy);
+    f3 a = unpack_rgb8unorm(ld32(reflections_tex, tr.x0, tr.y0)), b = unpack_rgb8unorm(ld32(reflections_tex, tr.x1, tr.y0));
+    f3 c = unpack_rgb8unorm(ld32(reflections_tex, tr.x0, tr.y1)), d = unpack_rgb8unorm(ld32(reflections_tex, tr.x1, tr.y1));
+    reflection = C3(wsum(a.x, b.x, c.x, d.x, tr), wsum(a.y, b.y, c.y, d.y, tr), wsum(a.z, b.z, c.z, d.z, tr));
   }
 
-  f3 camera_view_vec = reconstruct_view_vec(su, sv, depth, k.cam);
-  f3 world_pos = mul_m4(k.inverse_camera, camera_view_vec, 1.f);
-  f3 camera_pos = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
+  const CamF cam = make_camf(k.cam);
+  const f3 world_pos = mul_m4f(k.inverse_camera, reconstruct_fast(su, sv, depth, cam));
+  const f3 camera_pos = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
 
-  const float metallic = gmix(0.1f, 1.0f, mat_b);
-  const f3 V = norm3(camera_pos - world_pos);
+  const float metallic = fmaf(0.9f, mat_b, 0.1f);                           // mix(0.1, 1.0, material.b)
+  const f3 V = norm3f(sub3f(camera_pos, world_pos));
   const f3 LIGHT_POS = mk3(-1.85867f, 5.81832f, -0.247114f);                 // shader.frag:37
-  f3 Lv = LIGHT_POS - world_pos;
-  f3 L = norm3(Lv);
-  f3 H = norm3(V + L);
-  const float ld2 = dot3(Lv, Lv);                                          // light_distance^2
-  const float rad = 0.1f * fminf(__fdividef(100.f, ld2), 100.0f);          // LIGHT_RADIANCE * min(100/d^2, 100)
+  const f3 Lv = sub3f(LIGHT_POS, world_pos);
+  const float ld2 = dot3f(Lv, Lv);                                          // light_distance^2
+  const float ild = rsqrtf(ld2);
+  const f3 L = mk3(Lv.x * ild, Lv.y * ild, Lv.z * ild);
+  const f3 H = norm3f(mk3(V.x + L.x, V.y + L.y, V.z + L.z));
+  const float rad = 0.1f * fminf(div_fast(100.f, ld2), 100.0f);          // LIGHT_RADIANCE * min(100/d^2, 100)
 
-  const float NdotL = fmaxf(dot3(N, L), 0.f), NdotV = fmaxf(dot3(N, V), 0.f);
-  // --- colour from here on ---
+  const float NdotL = fmaxf(dot3f(N, L), 0.f), NdotV = fmaxf(dot3f(N, V), 0.f);
   const c3 one = C3(1.f, 1.f, 1.f);
   const c3 F0 = C3(0.04f, 0.04f, 0.04f) * (1.0f - metallic) + albedo * metallic;
-  const float NDF = DistributionGGX(N, H, roughness);
-  const float G = brdfG2(NdotV, NdotL, roughness * roughness);
-  float fc = fminf(fmaxf(1.0f - fmaxf(dot3(H, V), 0.0f), 0.0f), 1.0f);
+  // DistributionGGX(N, H, roughness), brdf.glsl:31-38
+  const float NoH = dot3f(N, H), a2 = roughness * roughness, NoH2 = NoH * NoH;
+  const float den = fmaf(NoH2, a2, 1.f - NoH2);
+  const float NDF = (NoH2 > 0 ? a2 : 0.f) * rcp_fast(VKR_PI * den * den);
+  // brdfG2(NdotV, NdotL, roughness^2), brdf.glsl:49-56:  2 / (sqrt(1 + a(1-v^2)/v^2) + sqrt(1 + a(1-l^2)/l^2))
+  const float v2 = NdotV * NdotV, l2 = NdotL * NdotL;
+  const float L1 = sqrt_fast(1.f + div_fast(a2 * (1.f - v2), v2)), L2 = sqrt_fast(1.f + div_fast(a2 * (1.f - l2), l2));
+  const float G = div_fast(2.0f, L1 + L2);
+  float fc = fminf(fmaxf(1.0f - fmaxf(dot3f(H, V), 0.0f), 0.0f), 1.0f);
   float fc2 = fc * fc;
   const float fs = fc2 * fc2 * fc;                                          // pow(x, 5)
   const c3 F = F0 + (one - F0) * fs;
   const c3 kD = (one - F) * (1.f - metallic);
-  const float inv_den = __frcp_rn(4.0f * NdotV * NdotL + 0.0001f);
+  const float inv_den = rcp_fast(4.0f * NdotV * NdotL + 0.0001f);
   const c3 specular = F * (NDF * G * inv_den);
-  const float biased_rougness = gmix(k.min_r, k.max_r, roughness);
-  const float2 ssr_brdf = sample_rg16f(brdf_tex, biased_rougness, NdotV);
+  const float biased_rougness = fmaf(roughness, k.max_r - k.min_r, k.min_r);   // mix(min, max, roughness)
+  const float2 ssr_brdf = sample_rg16f_fast(brdf_tex, make_tapw(biased_rougness, NdotV, brdf_tex.w, brdf_tex.h));
 
   c3 Lo = (kD * albedo * (1.0f / VKR_PI) + specular) * (rad * NdotL);
   Lo = Lo + reflection * (F0 * ssr_brdf.x + C3(ssr_brdf.y, ssr_brdf.y, ssr_brdf.y));
@@ -147,7 +179,11 @@ extern "C" int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* a
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("deferred_shading: sRGB table upload failed"); return VKR_ERR_CUDA; }
   dim3 grid((out_color->width + 31) / 32, (out_color->height + 7) / 8);
-  deferred_shading_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(albedo, 0), make_mip(normal, 0), make_mip(material, 0), make_mip(depth, 0),
+  const Dim dim = make_dim(out_color->width, out_color->height);
+  const bool same = same_extent(albedo, out_color) && same_extent(normal, out_color) && same_extent(material, out_color) &&
+                    out_color->width <= 8192 && out_color->height <= 8192;
+  auto kern = same ? deferred_shading_kernel<true> : deferred_shading_kernel<false>;
+  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(albedo, 0), make_mip(normal, 0), make_mip(material, 0), make_mip(depth, 0),
                                                                   make_mip(depth, 1), make_mip(occlusion, 0), make_mip(brdf_lut, 0),
                                                                   make_mip(reflections, 0), make_mip(out_color, 0), srgb);
   return check_launch("deferred_shading_kernel");

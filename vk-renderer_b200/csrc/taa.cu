@@ -21,60 +21,85 @@ __device__ __forceinline__ f3 bilerp3(f3 a, f3 b, f3 c, f3 d, float wx, float wy
 
 __device__ __forceinline__ int clampi(int v, int hi) { return min(max(v, 0), hi); }
 
-// resolve.comp:72-77
-__device__ __forceinline__ f3 world_pos(const Mip& depth, const Mat4& inv, float u, float v, const CamK& cam) {
+// resolve.comp:72-77.  The depth footprint keeps the exact unfused bilinear (a silhouette texel with weight ~1e-4
+// moves the reconstructed point by metres at far depths); the rest of the reconstruction is value-only.
+__device__ __forceinline__ f3 world_pos(const Mip& depth, const Mat4& inv, float u, float v, const CamF& cam) {
   float d = sample_d24(depth, u, v);
-  return mul_m4(inv, reconstruct_view_vec(u, v, d, cam), 1.0f);
+  return mul_m4f(inv, reconstruct_fast(u, v, d, cam));
 }
 
-__global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k, Mip history, Mip prev_depth, Mip depth, Mip velocity, Mip color, Mip out,
+__device__ __forceinline__ f3 srgb_texel(const Mip& m, int x, int y, const float* __restrict__ srgb) {
+  uint32_t k = ld32(m, x, y);
+  return mk3(__ldg(srgb + (k & 255u)), __ldg(srgb + ((k >> 8) & 255u)), __ldg(srgb + ((k >> 16) & 255u)));
+}
+
+__device__ __forceinline__ f3 wsum3(f3 a, f3 b, f3 c, f3 d, const TapW& w) {
+  return mk3(wsum(a.x, b.x, c.x, d.x, w), wsum(a.y, b.y, c.y, d.y, w), wsum(a.z, b.z, c.z, d.z, w));
+}
+
+// SAME: colour and velocity have the output's extent, so their bilinear footprint at the pixel's own centre is the
+// texel itself (common.cuh tap_is_texel); otherwise the general footprint is evaluated.
+template <bool SAME>
+__global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k, Dim dim, Mip history, Mip prev_depth, Mip depth, Mip velocity, Mip color, Mip out,
                                                           const float* __restrict__ srgb) {
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
-  const float su = ((float)px + 0.5f) / (float)out.w, sv = ((float)py + 0.5f) / (float)out.h;
+  const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
+  const CamF cam = make_camf(k.cam);
 
-  float4 cc = sample_srgb8(color, su, sv, srgb);
-  f3 current_color = mk3(cc.x, cc.y, cc.z);
-  float2 vel = sample_rg16f(velocity, su, sv);
-  float delta_len = sqrtf(FA(FM(vel.x, vel.x), FM(vel.y, vel.y)));
+  f3 current_color;
+  float2 vel;
+  if (SAME) {
+    current_color = srgb_texel(color, px, py, srgb);
+    vel = unpack_rg16f(ld32(velocity, px, py));
+  } else {
+    float4 cc = sample_srgb8(color, su, sv, srgb);
+    current_color = mk3(cc.x, cc.y, cc.z);
+    vel = sample_rg16f(velocity, su, sv);
+  }
+  const float delta_len = sqrt_fast(fmaf(vel.x, vel.x, vel.y * vel.y));
   bool reprojected = false;
-  f3 out_color = mk3(0.f, 0.f, 0.f);
-  float pu = su + vel.x, pv = sv + vel.y;
+  f3 out_color = current_color;
+  const float pu = su + vel.x, pv = sv + vel.y;
 
   if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
-    // The five bilinear footprints (centre + 4 textureOffset neighbours, :41-45) share a
-    // plus-shaped set of 12 texels; fetch each once.
+    // The five bilinear footprints (centre + 4 textureOffset neighbours, :41-45) share a plus-shaped set of 12
+    // texels and one pair of weights; fetch each texel once.
     const int W = history.w, H = history.h;
     float x = __fsub_rn(__fmul_rn(pu, (float)W), 0.5f), y = __fsub_rn(__fmul_rn(pv, (float)H), 0.5f);
     float fx = floorf(x), fy = floorf(y);
-    float wx = __fsub_rn(x, fx), wy = __fsub_rn(y, fy);
+    Tap tw; tw.wx = x - fx; tw.wy = y - fy; tw.x0 = tw.x1 = tw.y0 = tw.y1 = 0;
+    const TapW w = make_tapw(tw);
     int ix = (int)fx, iy = (int)fy;
     int xs[4] = {clampi(ix - 1, W - 1), clampi(ix, W - 1), clampi(ix + 1, W - 1), clampi(ix + 2, W - 1)};
-    int ys[4] = {clampi(iy - 1, H - 1), clampi(iy, H - 1), clampi(iy + 1, H - 1), clampi(iy + 2, H - 1)};
+    const unsigned char* rows[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) rows[j] = history.p + (size_t)clampi(iy - 1 + j, H - 1) * history.pitch;
     f3 t[4][4];
 #pragma unroll
     for (int j = 0; j < 4; j++)
 #pragma unroll
       for (int i = 0; i < 4; i++)
-        if (!((i == 0 || i == 3) && (j == 0 || j == 3))) t[j][i] = unpack_rgb16f(ld64(history, xs[i], ys[j]));
-    f3 hist = bilerp3(t[1][1], t[1][2], t[2][1], t[2][2], wx, wy);
-    f3 c0 = bilerp3(t[1][2], t[1][3], t[2][2], t[2][3], wx, wy);   // offset (+1, 0)
-    f3 c1 = bilerp3(t[2][1], t[2][2], t[3][1], t[3][2], wx, wy);   // offset (0, +1)
-    f3 c2 = bilerp3(t[1][0], t[1][1], t[2][0], t[2][1], wx, wy);   // offset (-1, 0)
-    f3 c3 = bilerp3(t[0][1], t[0][2], t[1][1], t[1][2], wx, wy);   // offset (0, -1)
-    f3 cmin = mk3(gmin(c0.x, gmin(c1.x, gmin(c2.x, c3.x))), gmin(c0.y, gmin(c1.y, gmin(c2.y, c3.y))), gmin(c0.z, gmin(c1.z, gmin(c2.z, c3.z))));
-    f3 cmax = mk3(gmax(c0.x, gmax(c1.x, gmax(c2.x, c3.x))), gmax(c0.y, gmax(c1.y, gmax(c2.y, c3.y))), gmax(c0.z, gmax(c1.z, gmax(c2.z, c3.z))));
-    hist = mk3(gclamp(hist.x, cmin.x, cmax.x), gclamp(hist.y, cmin.y, cmax.y), gclamp(hist.z, cmin.z, cmax.z));
-    out_color = mix3(hist, current_color, 0.1f);
+        if (!((i == 0 || i == 3) && (j == 0 || j == 3))) t[j][i] = unpack_rgb16f(__ldg((const uint2*)rows[j] + xs[i]));
+    f3 hist = wsum3(t[1][1], t[1][2], t[2][1], t[2][2], w);
+    f3 c0 = wsum3(t[1][2], t[1][3], t[2][2], t[2][3], w);   // offset (+1, 0)
+    f3 c1 = wsum3(t[2][1], t[2][2], t[3][1], t[3][2], w);   // offset (0, +1)
+    f3 c2 = wsum3(t[1][0], t[1][1], t[2][0], t[2][1], w);   // offset (-1, 0)
+    f3 c3 = wsum3(t[0][1], t[0][2], t[1][1], t[1][2], w);   // offset (0, -1)
+    // min/max/clamp as single FMNMX (differs from the GLSL select form only when a history texel is NaN)
+    f3 cmin = mk3(fminf(fminf(c0.x, c1.x), fminf(c2.x, c3.x)), fminf(fminf(c0.y, c1.y), fminf(c2.y, c3.y)), fminf(fminf(c0.z, c1.z), fminf(c2.z, c3.z)));
+    f3 cmax = mk3(fmaxf(fmaxf(c0.x, c1.x), fmaxf(c2.x, c3.x)), fmaxf(fmaxf(c0.y, c1.y), fmaxf(c2.y, c3.y)), fmaxf(fmaxf(c0.z, c1.z), fmaxf(c2.z, c3.z)));
+    hist = mk3(fminf(fmaxf(hist.x, cmin.x), cmax.x), fminf(fmaxf(hist.y, cmin.y), cmax.y), fminf(fmaxf(hist.z, cmin.z), cmax.z));
 
-    f3 v_world_cur = world_pos(depth, k.inverse_camera, su, sv, k.cam);
-    f3 v_world_prev = world_pos(prev_depth, k.prev_inverse_camera, pu, pv, k.cam);
+    f3 v_world_cur = world_pos(depth, k.inverse_camera, su, sv, cam);
+    f3 v_world_prev = world_pos(prev_depth, k.prev_inverse_camera, pu, pv, cam);
     f3 v_camera = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
-    float error = len3(v_world_cur - v_world_prev);
-    float pixel_dist = len3(v_world_cur - v_camera);
-    reprojected = (delta_len < 0.005f) || (error < gclamp(FM(FM(0.1f, pixel_dist), delta_len), 0.01f, 0.2f));
+    float error = len3f(sub3f(v_world_cur, v_world_prev));
+    float pixel_dist = len3f(sub3f(v_world_cur, v_camera));
+    reprojected = (delta_len < 0.005f) || (error < gclamp(0.1f * pixel_dist * delta_len, 0.01f, 0.2f));
+    if (reprojected) out_color = mk3(fmaf(0.1f, current_color.x - hist.x, hist.x), fmaf(0.1f, current_color.y - hist.y, hist.y),
+                                     fmaf(0.1f, current_color.z - hist.z, hist.z));   // mix(history, current, 0.1)
   }
-  if (!reprojected) out_color = current_color;
   *((uint2*)(out.p + (size_t)py * out.pitch) + px) = make_uint2(pack_half2(out_color.x, out_color.y), pack_half2(out_color.z, 0.f));
 }
 
@@ -96,7 +121,10 @@ extern "C" int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, c
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("taa_resolve: sRGB table upload failed"); return VKR_ERR_CUDA; }
   dim3 grid((out_target->width + 31) / 32, (out_target->height + 7) / 8);
-  taa_resolve_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(history, 0), make_mip(prev_depth, 0), make_mip(depth, 0),
-                                                             make_mip(velocity, 0), make_mip(color, 0), make_mip(out_target, 0), srgb);
+  const Dim dim = make_dim(out_target->width, out_target->height);
+  const bool same = same_extent(color, out_target) && same_extent(velocity, out_target) && out_target->width <= 8192 && out_target->height <= 8192;
+  auto kern = same ? taa_resolve_kernel<true> : taa_resolve_kernel<false>;
+  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(history, 0), make_mip(prev_depth, 0), make_mip(depth, 0),
+                                               make_mip(velocity, 0), make_mip(color, 0), make_mip(out_target, 0), srgb);
   return check_launch("taa_resolve_kernel");
 }
