@@ -112,27 +112,41 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Mip depth, Mip 
   *out = make_uint2(pack_half2(ox, oy), 0u);
 }
 
-// filter.comp:17-52 — 4x4 window at offsets -2..+1, weight on linear depth.
+// filter.comp:17-52 — 4x4 window at offsets -2..+1, weight on linear depth.  A 32x8 tile stages the linearised
+// depth and raw.r of its 35x11 footprint once in shared memory (the shader linearises each of the 16 taps again).
+#define GF_W 32
+#define GF_H 8
+#define GF_SW (GF_W + 3)
+#define GF_SH (GF_H + 3)
 __global__ void __launch_bounds__(256) gtao_filter_kernel(Mip depth, Mip raw, Mip filtered, int tw, int th, float znear, float zfar) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+  __shared__ float s_z[GF_SH][GF_SW + 1];
+  __shared__ float s_r[GF_SH][GF_SW + 1];
+  const int bx = blockIdx.x * GF_W - 2, by = blockIdx.y * GF_H - 2;
+  const float nf = FM(znear, zfar), fmn = FS(zfar, znear);
+  for (int t = threadIdx.x; t < GF_SW * GF_SH; t += 256) {
+    const int ly = t / GF_SW, lx = t - ly * GF_SW;
+    const int sx = bx + lx, sy = by + ly;
+    const float d = fetch_d24(depth, sx, sy);                                // out of range = 0 (App. A.3)
+    s_z[ly][lx] = nf * rcp_fast(FS(FM(d, fmn), zfar));                       // linearize_depth2, exact denominator
+    s_r[ly][lx] = in_range(raw, sx, sy) ? __half2float(__ushort_as_half((unsigned short)(__ldg((const uint32_t*)(raw.p + (size_t)sy * raw.pitch) + 2 * sx) & 0xFFFFu))) : 0.f;
+  }
+  __syncthreads();
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int px = blockIdx.x * GF_W + tx, py = blockIdx.y * GF_H + ty;
   if (px >= tw || py >= th) return;
-  float pixel_depth = fetch_d24(depth, px, py);
-  float linear_depth = linearize_depth2(pixel_depth, znear, zfar);
+  const float linear_depth = s_z[ty + 2][tx + 2];
+  const float k5 = 5.f * rcp_fast(fabsf(linear_depth));
   float weight_sum = 0, ao = 0;
 #pragma unroll
   for (int x = 0; x < 4; x++) {
 #pragma unroll
     for (int y = 0; y < 4; y++) {
-      int sx = px + x - 2, sy = py + y - 2;
-      float sampled_depth = linearize_depth2(fetch_d24(depth, sx, sy), znear, zfar);
-      float weight = gmax(0.0f, FS(1.0f, FM(5.f, fabsf(FS(sampled_depth, linear_depth))) / fabsf(linear_depth)));
-      weight_sum = FA(weight_sum, weight);
-      float r = in_range(raw, sx, sy) ? unpack_rg16f(ld64(raw, sx, sy).x).x : 0.f;
-      ao = FA(ao, FM(weight, r));
+      const float weight = fmaxf(0.0f, fmaf(-k5, fabsf(s_z[ty + y][tx + x] - linear_depth), 1.0f));
+      weight_sum += weight;
+      ao = fmaf(weight, s_r[ty + y][tx + x], ao);
     }
   }
-  ao /= weight_sum;
-  *((__half*)(filtered.p + (size_t)py * filtered.pitch) + px) = __float2half_rn(ao);
+  *((__half*)(filtered.p + (size_t)py * filtered.pitch) + px) = __float2half_rn(ao * rcp_fast(weight_sum));
 }
 
 struct AccumK {
@@ -141,48 +155,50 @@ struct AccumK {
   uint32_t clear_history;
 };
 
-__device__ __forceinline__ f3 reconstruct_world_pos(const Mip& depth, const Mat4& inv, float u, float v, const CamK& cam) {  // accum.comp:94-99
-  float d = sample_d24(depth, u, v);
-  f3 vc = reconstruct_view_vec(u, v, d, cam);
-  return mul_m4(inv, vc, 1.0f);
-}
-
-// accum.comp:29-92
-__global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k, Mip depth, Mip prev_depth, Mip filtered, Mip out, Mip velocity, Mip history) {
+// accum.comp:29-99.  Depth footprints keep the exact unfused bilinear and the exact z denominator (far depths amplify a
+// 1-ulp difference to ~1e-3 view units, and depth_err is thresholded); everything else is value-only.
+template <bool SAME>
+__global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k, Dim dim, Mip depth, Mip prev_depth, Mip filtered, Mip out, Mip velocity, Mip history) {
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
-  const float tw = (float)out.w, th = (float)out.h;
-  const float su = ((float)px + 0.5f) / tw, sv = ((float)py + 0.5f) / th;
-  float2 vel = sample_rg16f(velocity, su, sv);
-  float pu = FA(su, vel.x), pv = FA(sv, vel.y);
+  const float tw = dim.w, th = dim.h;
+  const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
+  const CamF cam = make_camf(k.cam);
+  const float2 vel = SAME ? unpack_rg16f(ld32(velocity, px, py)) : sample_rg16f(velocity, su, sv);
+  const float pu = su + vel.x, pv = sv + vel.y;
   bool reprojected = false;
   float valid_samples = 1.0f;
   if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
-    f3 v_world_prev = reconstruct_world_pos(prev_depth, k.prev_inverse_camera, pu, pv, k.cam);
-    float4 prev_ndc = mul_m4_4(k.mvp, v_world_prev, 1.0f);
-    float ndx = prev_ndc.x / prev_ndc.w, ndy = prev_ndc.y / prev_ndc.w, ndz = prev_ndc.z / prev_ndc.w;
-    float wu = FA(FM(0.5f, ndx), 0.5f), wv = FA(FM(0.5f, ndy), 0.5f);
-    float dx = FM(fabsf(FS(wu, su)), tw), dy = FM(fabsf(FS(wv, sv)), th);
-    float current_z = linearize_depth2(sample_d24(depth, su, sv), k.cam.znear, k.cam.zfar);
-    float prev_z = linearize_depth2(ndz, k.cam.znear, k.cam.zfar);
-    float depth_err = fabsf(FS(prev_z, current_z));
-    float vel_delta = gmax(FM(fabsf(vel.x), tw), FM(fabsf(vel.y), th));
-    float error = FA(FM(0.1f, vel_delta), depth_err);
-    valid_samples = gclamp(FS(1.f, error), 0.8f, 1.f);
-    reprojected = (gmax(dx, dy) <= 2.0f) && (depth_err < 0.2f);
+    const f3 v_world_prev = mul_m4f(k.prev_inverse_camera, reconstruct_fast(pu, pv, sample_d24(prev_depth, pu, pv), cam));
+    const Mat4& M = k.mvp;
+    const float cx = fmaf(M.m[8], v_world_prev.z, fmaf(M.m[4], v_world_prev.y, fmaf(M.m[0], v_world_prev.x, M.m[12])));
+    const float cy = fmaf(M.m[9], v_world_prev.z, fmaf(M.m[5], v_world_prev.y, fmaf(M.m[1], v_world_prev.x, M.m[13])));
+    const float cz = fmaf(M.m[10], v_world_prev.z, fmaf(M.m[6], v_world_prev.y, fmaf(M.m[2], v_world_prev.x, M.m[14])));
+    const float cw = fmaf(M.m[11], v_world_prev.z, fmaf(M.m[7], v_world_prev.y, fmaf(M.m[3], v_world_prev.x, M.m[15])));
+    const float iw = rcp_fast(cw);
+    const float wu = fmaf(0.5f * iw, cx, 0.5f), wv = fmaf(0.5f * iw, cy, 0.5f);
+    const float ndz = cz / cw;                                              // feeds the ill-conditioned linearisation: IEEE
+    const float dx = fabsf(wu - su) * tw, dy = fabsf(wv - sv) * th;
+    const float current_z = linearize_fast(sample_d24(depth, su, sv), cam);
+    const float prev_z = linearize_fast(ndz, cam);
+    const float depth_err = fabsf(prev_z - current_z);
+    const float vel_delta = fmaxf(fabsf(vel.x) * tw, fabsf(vel.y) * th);
+    const float error = fmaf(0.1f, vel_delta, depth_err);
+    valid_samples = fminf(fmaxf(1.f - error, 0.8f), 1.f);
+    reprojected = (fmaxf(dx, dy) <= 2.0f) && (depth_err < 0.2f);
   }
-  float new_ao = __half2float(*((const __half*)(filtered.p + (size_t)py * filtered.pitch) + px));
+  const float new_ao = __half2float(*((const __half*)(filtered.p + (size_t)py * filtered.pitch) + px));
   float computed_ao = new_ao;
   float samples_count = 1.f;
   if (k.clear_history != 0) reprojected = false;
   if (reprojected) {
-    float2 acc = sample_rg16f(history, pu, pv);
-    samples_count = FM(FM(255.f, acc.y), valid_samples);
-    computed_ao = FA(FM(acc.x, samples_count), new_ao) / FA(samples_count, 1.f);
-    samples_count = FA(samples_count, 1.f);
+    const float2 acc = sample_rg16f_fast(history, make_tapw(pu, pv, history.w, history.h));
+    samples_count = 255.f * acc.y * valid_samples;
+    computed_ao = fmaf(acc.x, samples_count, new_ao) * rcp_fast(samples_count + 1.f);
+    samples_count = samples_count + 1.f;
     if (samples_count > 255.f) samples_count = 100.f;
   }
-  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_half2(gclamp(computed_ao, 0.f, 1.f), samples_count / 255.f);
+  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_half2(gclamp(computed_ao, 0.f, 1.f), samples_count * (1.0f / 255.f));
 }
 
 }  // namespace vkr
@@ -241,7 +257,10 @@ extern "C" int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* dept
   k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
   k.clear_history = p->clear_history;
   dim3 grid((accumulated->width + 31) / 32, (accumulated->height + 7) / 8);
-  gtao_accumulate_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, depth_lod), make_mip(prev_depth, depth_lod), make_mip(filtered, 0),
+  const Dim dim = make_dim(accumulated->width, accumulated->height);
+  const bool same = same_extent(dvelocity, accumulated) && accumulated->width <= 8192 && accumulated->height <= 8192;
+  auto kern = same ? gtao_accumulate_kernel<true> : gtao_accumulate_kernel<false>;
+  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(depth, depth_lod), make_mip(prev_depth, depth_lod), make_mip(filtered, 0),
                                                                  make_mip(accumulated, 0), make_mip(dvelocity, 0), make_mip(history, 0));
   return check_launch("gtao_accumulate_kernel");
 }
