@@ -26,12 +26,13 @@ struct BlurK {
 #define BLUR_RMAX 11
 #define BLUR_SPAN (BLUR_TILE + 2 * BLUR_RMAX)
 
-__device__ __forceinline__ f3 world_pos_lod(const Mip& depth1, const Mat4& inv, float u, float v, const CamK& cam) {   // blur.comp:110-115
-  float d = sample_d24(depth1, u, v);
-  return mul_m4(inv, reconstruct_view_vec(u, v, d, cam), 1.0f);
+// blur.comp:110-115 — exact depth footprint and z denominator (thresholded downstream), value-only otherwise
+__device__ __forceinline__ f3 world_pos_lod(const Mip& depth1, const Mat4& inv, float u, float v, const CamF& cam) {
+  return mul_m4f(inv, reconstruct_fast(u, v, sample_d24(depth1, u, v), cam));
 }
 
-__global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip normal_tex, Mip refl, Mip material_tex, Mip history, Mip velocity,
+template <bool SAME>
+__global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Dim dim, Mip depth1, Mip normal_tex, Mip refl, Mip material_tex, Mip history, Mip velocity,
                                                         Mip prev_depth1, Mip out, const float* __restrict__ srgb) {
   __shared__ float4 s_nd[BLUR_SPAN * BLUR_SPAN];
   __shared__ float4 s_col[BLUR_SPAN * BLUR_SPAN];
@@ -40,10 +41,9 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   const int px = blockIdx.x * BLUR_TILE + tx, py = blockIdx.y * BLUR_TILE + ty;
   const bool inside = px < out.w && py < out.h;
-  const float tsx = (float)out.w, tsy = (float)out.h;
-  const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;
+  const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
 
-  // per-pixel radius (blur.comp:39-53)
+  // per-pixel radius (blur.comp:39-53).  floor() makes this the one discontinuous quantity of the pass: unfused.
   float sigma = 0.35f;
   int r = 0;
   if (inside) {
@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip
   }
   if (threadIdx.x == 0) s_rmax = 0;
   __syncthreads();
-  int wr = __reduce_max_sync(0xFFFFFFFFu, r);
+  const int wr = __reduce_max_sync(0xFFFFFFFFu, r);
   if ((threadIdx.x & 31) == 0) atomicMax(&s_rmax, wr);
   __syncthreads();
   const int R = s_rmax;
@@ -65,13 +65,14 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip
   // stage {normal, depth} and colour for every tap position of the tile
   const int ox = blockIdx.x * BLUR_TILE - R, oy = blockIdx.y * BLUR_TILE - R;
   for (int t = threadIdx.x; t < span * span; t += 256) {
-    const int lx = t % span, ly = t / span;
+    const int ly = t / span, lx = t - ly * span;
     const int qx = ox + lx, qy = oy + ly;
     float4 nd = make_float4(0.f, 0.f, 0.f, 0.f), col = make_float4(0.f, 0.f, 0.f, 0.f);
     if (qx >= 0 && qy >= 0 && qx < out.w && qy < out.h) {          // outside: depth 0 -> bilateral weight 0, colour 0
-      f3 n = sample_gbuffer_normal(normal_tex, (float)qx / tsx, (float)qy / tsy);   // uv without +0.5 (blur.comp:60,:63)
-      nd = make_float4(n.x, n.y, n.z, fetch_d24(depth1, qx, qy));
-      f3 c = unpack_rgb8unorm(ld32(refl, qx, qy));
+      const float2 e = sample_rg16unorm_fast(normal_tex, make_tapw(texel_uv(qx, dim.w, dim.rw), texel_uv(qy, dim.h, dim.rh), normal_tex.w, normal_tex.h));
+      const f3 n = decode_normal_fast(e.x, e.y);                    // uv without +0.5 (blur.comp:60,:63)
+      nd = make_float4(n.x, n.y, n.z, d24_to_float(ld32(depth1, qx, qy)));
+      const f3 c = unpack_rgb8unorm(ld32(refl, qx, qy));
       col = make_float4(c.x, c.y, c.z, 0.f);
     }
     s_nd[ly * BLUR_SPAN + lx] = nd;
@@ -81,55 +82,84 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Mip depth1, Mip
 
   const float center_depth = s_nd[(ty + R) * BLUR_SPAN + tx + R].w;            // texelFetch(DEPTH_TEX, pixel_pos, 1)
   f3 center_normal = mk3(0.f, 0.f, 1.f);
-  if (inside) center_normal = sample_gbuffer_normal(normal_tex, su, sv);
-  const float g = 1.0f / FM(FM(2 * VKR_PI, sigma), sigma);
-  const float e = FM(FM(2.f, sigma), sigma);
-  const float ek = -1.4426950408889634f / e;     // exp(-d2/e) = exp2(d2 * ek)
-  const float bk = 1000.0f / center_depth;
+  if (inside) center_normal = sample_gbuffer_normal_fast(normal_tex, su, sv);
+  const float e2 = 2.f * sigma * sigma;
+  const float g = rcp_fast(VKR_PI * e2);                                       // 1 / (2 pi sigma^2)
+  const float ek = -1.4426950408889634f * rcp_fast(e2);                        // exp(-d2/e) = exp2(d2 * ek)
+  const float bk = 1000.0f * rcp_fast(center_depth);
+  // Gaussian along a column by recurrence: G(j+1) = G(j) * q(j), q(j+1) = q(j) * c, started at the lane's own -r
+  // (two multiplies per tap instead of int->float, multiply, MUFU.EX2 with range fix-up).
+  const float gc = exp2f(2.f * ek);
+  const float q0 = exp2f((float)(1 - 2 * r) * ek);
+  const float g0 = g * exp2f((float)(r * r) * ek);
 
   float weight_sum = 0.f;
-  f3 color = mk3(0.f, 0.f, 0.f);
-  const int base = (ty + R) * BLUR_SPAN + tx + R;
-  for (int i = -wr; i <= wr; i++) {
-    const bool ix_ok = (i >= -r) && (i <= r);
-    for (int j = -wr; j <= wr; j++) {
-      if (ix_ok && j >= -r && j <= r) {
-        const float4 nd = s_nd[base + j * BLUR_SPAN + i];
-        const float4 c = s_col[base + j * BLUR_SPAN + i];
-        float bilateral_weight = gmax(1 - fabsf(center_depth - nd.w) * bk, 0.f);
-        float normal_weight = gmax(center_normal.x * nd.x + center_normal.y * nd.y + center_normal.z * nd.z, 0.f);
-        float w = g * exp2f((float)(i * i + j * j) * ek);
-        w *= bilateral_weight;
-        w *= normal_weight;
-        color.x += c.x * w; color.y += c.y * w; color.z += c.z * w;
-        weight_sum += w;
+  float cr = 0.f, cg = 0.f, cb = 0.f;
+  const float4* pn0 = s_nd + (ty + R - wr) * BLUR_SPAN + tx + R;
+  const float4* pc0 = s_col + (ty + R - wr) * BLUR_SPAN + tx + R;
+#define BLUR_TAP(GJ)                                                                                                              \
+  {                                                                                                                               \
+    const float4 nd = *pn;                                                                                                        \
+    const float4 c = *pc;                                                                                                         \
+    pn += BLUR_SPAN; pc += BLUR_SPAN;                                                                                             \
+    const float bilateral_weight = fmaxf(fmaf(-fabsf(center_depth - nd.w), bk, 1.0f), 0.f);                                       \
+    const float normal_weight = fmaxf(fmaf(center_normal.z, nd.z, fmaf(center_normal.y, nd.y, center_normal.x * nd.x)), 0.f);     \
+    const float w = (GJ) * (bilateral_weight * normal_weight);                                                                    \
+    cr = fmaf(c.x, w, cr); cg = fmaf(c.y, w, cg); cb = fmaf(c.z, w, cb);                                                          \
+    weight_sum += w;                                                                                                              \
+  }
+  if (__all_sync(0xFFFFFFFFu, r == wr)) {
+    // every lane of the warp has the warp's radius (one material under the warp: the common case): no per-tap predicates
+    for (int i = -wr; i <= wr; i++) {
+      const float4* pn = pn0 + i;
+      const float4* pc = pc0 + i;
+      float gj = g0 * exp2f((float)(i * i) * ek), q = q0;
+#pragma unroll 4
+      for (int j = -wr; j <= wr; j++) {
+        BLUR_TAP(gj)
+        gj *= q; q *= gc;
+      }
+    }
+  } else {
+    // mixed radii: lanes outside their own window carry a zero Gaussian (gj = 0 before -r and after +r)
+    for (int i = -wr; i <= wr; i++) {
+      const float gi = ((i >= -r) && (i <= r)) ? exp2f((float)(i * i) * ek) : 0.f;
+      const float4* pn = pn0 + i;
+      const float4* pc = pc0 + i;
+      float gj = 0.f, q = 0.f;
+      for (int j = -wr; j <= wr; j++) {
+        if (j == -r) { gj = g0 * gi; q = q0; }
+        BLUR_TAP(gj)
+        gj *= q; q *= gc;
+        if (j == r) { gj = 0.f; q = 0.f; }
       }
     }
   }
+#undef BLUR_TAP
   if (!inside) return;
-  const float inv = gmax(weight_sum, 0.001f);
-  color = mk3(color.x / inv, color.y / inv, color.z / inv);
+  const float inv = rcp_fast(fmaxf(weight_sum, 0.001f));
+  f3 color = mk3(cr * inv, cg * inv, cb * inv);
 
   // temporal blend (blur.comp:77-105)
   bool reprojected = false;
-  float2 vel = sample_rg16f(velocity, su, sv);
-  float delta_len = sqrtf(FA(FM(vel.x, vel.x), FM(vel.y, vel.y)));
-  float pu = FA(su, vel.x), pv = FA(sv, vel.y);
-  if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
-    f3 v_world_cur = world_pos_lod(depth1, k.inverse_camera, su, sv, k.cam);
-    f3 v_world_prev = world_pos_lod(prev_depth1, k.prev_inverse_camera, pu, pv, k.cam);
-    f3 v_camera = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
-    float error = len3(v_world_cur - v_world_prev);
-    float pixel_dist = len3(v_world_cur - v_camera);
-    reprojected = (delta_len < 0.0001f) || (error < gclamp(FM(FM(0.1f, pixel_dist), delta_len), 0.01f, 0.1f));
+  const float2 vel = SAME ? unpack_rg16f(ld32(velocity, px, py)) : sample_rg16f(velocity, su, sv);
+  const float delta_len = sqrt_fast(fmaf(vel.x, vel.x, vel.y * vel.y));
+  const float pu = su + vel.x, pv = sv + vel.y;
+  if (k.accumulate != 0 && pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
+    const CamF cam = make_camf(k.cam);
+    const f3 v_world_cur = world_pos_lod(depth1, k.inverse_camera, su, sv, cam);
+    const f3 v_world_prev = world_pos_lod(prev_depth1, k.prev_inverse_camera, pu, pv, cam);
+    const f3 v_camera = mk3(k.inverse_camera.m[12], k.inverse_camera.m[13], k.inverse_camera.m[14]);
+    const float error = len3f(sub3f(v_world_cur, v_world_prev));
+    const float pixel_dist = len3f(sub3f(v_world_cur, v_camera));
+    reprojected = (delta_len < 0.0001f) || (error < fminf(fmaxf(0.1f * pixel_dist * delta_len, 0.01f), 0.1f));
   }
-  if (k.accumulate == 0) reprojected = false;
   if (reprojected) {
-    Tap t = make_tap(su, sv, history.w, history.h);            // history at screen_uv, not prev_uv (App. A.6 #3)
+    const TapW t = make_tapw(su, sv, history.w, history.h);     // history at screen_uv, not prev_uv (App. A.6 #3)
     f3 a = unpack_rgb8unorm(ld32(history, t.x0, t.y0)), b = unpack_rgb8unorm(ld32(history, t.x1, t.y0));
     f3 c = unpack_rgb8unorm(ld32(history, t.x0, t.y1)), d = unpack_rgb8unorm(ld32(history, t.x1, t.y1));
-    f3 hc = mk3(bilerp(a.x, b.x, c.x, d.x, t.wx, t.wy), bilerp(a.y, b.y, c.y, d.y, t.wx, t.wy), bilerp(a.z, b.z, c.z, d.z, t.wx, t.wy));
-    color = mix3(hc, color, 0.1f);
+    f3 hc = mk3(wsum(a.x, b.x, c.x, d.x, t), wsum(a.y, b.y, c.y, d.y, t), wsum(a.z, b.z, c.z, d.z, t));
+    color = mk3(fmaf(0.1f, color.x - hc.x, hc.x), fmaf(0.1f, color.y - hc.y, hc.y), fmaf(0.1f, color.z - hc.z, hc.z));   // mix(history, colour, 0.1)
   }
   *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_rgba8unorm(color.x, color.y, color.z, 0.f);
 }
@@ -164,7 +194,9 @@ extern "C" int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, cons
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_blur: sRGB table upload failed"); return VKR_ERR_CUDA; }
   dim3 grid((out_blurred->width + BLUR_TILE - 1) / BLUR_TILE, (out_blurred->height + BLUR_TILE - 1) / BLUR_TILE);
-  sssr_blur_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, 1), make_mip(normal, 0), make_mip(reflections, 0), make_mip(material, 0),
+  const bool same = same_extent(dvelocity, out_blurred) && out_blurred->width <= 8192 && out_blurred->height <= 8192;
+  auto kern = same ? sssr_blur_kernel<true> : sssr_blur_kernel<false>;
+  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_dim(out_blurred->width, out_blurred->height), make_mip(depth, 1), make_mip(normal, 0), make_mip(reflections, 0), make_mip(material, 0),
                                                            make_mip(history, 0), make_mip(dvelocity, 0), make_mip(prev_depth, 1),
                                                            make_mip(out_blurred, 0), srgb);
   return check_launch("sssr_blur_kernel");

@@ -31,8 +31,10 @@ __device__ __forceinline__ float rand_hash(float u, float v) {
 }
 
 __device__ __forceinline__ float fetch_pyramid(const PyramidView& P, int x, int y, int lod) {
-  if (lod < 0 || lod >= P.count) return 0.0f;
-  return fetch_d24(P.mip[lod], x, y);
+  if ((unsigned)lod >= (unsigned)P.count) return 0.0f;
+  const Mip& m = P.mip[lod];
+  if ((unsigned)x >= (unsigned)m.w || (unsigned)y >= (unsigned)m.h) return 0.0f;      // texelFetch out of range = 0 (App. A.3)
+  return d24_to_float(__ldg((const uint32_t*)(m.p + (size_t)y * m.pitch) + x));
 }
 
 // screen_trace.glsl:17-45
@@ -59,6 +61,7 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
   const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
   const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
   const CamK cam = k.cam;
+  const CamF camf = make_camf(cam);
 
   float roughness = sample_srgb8(material, su, sv, srgb).y;                                     // :49-53
   float mg = gmix(0.0f, k.max_roughness, roughness);
@@ -122,9 +125,12 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
     }
     ++i;
     if (current_mip <= 1) {
-      f3 v = reconstruct_view_vec(position.x, position.y, surface_z, cam) - view_vec;
-      float h2 = dot3(pixel_normal, norm3(v));
-      if (len3(v) < 0.3f) h = gmax(h, h2);
+      // horizon sample (:258-262): a running max of a continuous quantity -> value-only arithmetic.
+      // len(v) < 0.3 <=> |v|^2 < 0.09; a zero-length v gives NaN, which both max forms ignore.
+      const f3 v = sub3f(reconstruct_fast(position.x, position.y, surface_z, camf), view_vec);
+      const float d2 = dot3f(v, v);
+      const float h2 = dot3f(pixel_normal, v) * rsqrtf(d2);
+      if (d2 < 0.09f) h = fmaxf(h, h2);
     }
   }
   bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
@@ -159,7 +165,11 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
     float pdfv = sampleGGXdirPDF(pdf, w0, pixel_normal, R, roughness);
     float occlusion = FM(FM(FM(1.0f / VKR_PI, len3(normal_projected)), 0.25f), gmax(FA(FA(-cosf(FS(FM(2.f, hh), n)), cosf(n)), FM(FM(2.f, hh), sinf(n))), 0.f));
     float result = isnan(occlusion) ? 0.0f : occlusion;
+#ifdef VKR_TRACE_STATS
+    *((uint2*)(out_occl.p + (size_t)py * out_occl.pitch) + px) = make_uint2(pack_half2(result, pdfv), pack_half2((float)i, (float)current_mip));
+#else
     *((uint2*)(out_occl.p + (size_t)py * out_occl.pitch) + px) = make_uint2(pack_half2(result, pdfv), 0u);
+#endif
   }
 }
 
