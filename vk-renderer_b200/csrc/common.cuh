@@ -280,6 +280,15 @@ __device__ __forceinline__ f3 mul_m3f(const Mat4& M, f3 v) {   // M * (v, 0), xy
   return mk3(fmaf(M.m[8], v.z, fmaf(M.m[4], v.y, M.m[0] * v.x)), fmaf(M.m[9], v.z, fmaf(M.m[5], v.y, M.m[1] * v.x)),
              fmaf(M.m[10], v.z, fmaf(M.m[6], v.y, M.m[2] * v.x)));
 }
+// a / b rounded to nearest like the IEEE division for normal-range operands (reciprocal refined once, quotient corrected
+// by its exact FMA residual) without the compiler's FCHK + slow-path call: 6 instructions.  Used where a quotient feeds
+// a threshold through an ill-conditioned expression and must carry the oracle's bits.
+__device__ __forceinline__ float div_rn_normal(float a, float b) {
+  float r = rcp_fast(b);
+  r = __fmaf_rn(__fmaf_rn(-b, r, 1.0f), r, r);
+  float q = __fmul_rn(a, r);
+  return __fmaf_rn(__fmaf_rn(-q, b, a), r, q);
+}
 struct CamF { float aspect_tg, tg, nf, fmn, zfar; };   // hoisted products for the fast reconstruct
 __device__ __forceinline__ CamF make_camf(const CamK& c) {
   CamF r; r.aspect_tg = c.aspect * c.tg; r.tg = c.tg; r.nf = FM(c.znear, c.zfar); r.fmn = FS(c.zfar, c.znear); r.zfar = c.zfar; return r;
@@ -288,6 +297,8 @@ __device__ __forceinline__ CamF make_camf(const CamK& c) {
 // evaluation moves z by up to ~1e-2 view units there, which is the size of the reprojection thresholds (0.01 .. 0.2)
 // downstream.  So the denominator keeps the oracle's unfused rounding; only the final division is approximate (2 ulp).
 __device__ __forceinline__ float linearize_fast(float d, const CamF& c) { return c.nf * rcp_fast(FS(FM(d, c.fmn), c.zfar)); }
+// linearize_depth2 with the oracle's bits (exact denominator, correctly rounded quotient)
+__device__ __forceinline__ float linearize_rn(float d, const CamF& c) { return div_rn_normal(c.nf, FS(FM(d, c.fmn), c.zfar)); }
 __device__ __forceinline__ f3 reconstruct_fast(float u, float v, float d, const CamF& c) {
   float z = linearize_fast(d, c);
   return mk3((1.0f - 2.f * u) * (z * c.aspect_tg), (1.0f - 2.f * v) * (z * c.tg), z);

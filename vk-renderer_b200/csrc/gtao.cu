@@ -17,20 +17,23 @@ struct GtaoK {
 #define MAX_THIKNESS 0.1f  // main.comp:82
 
 // main.comp:84-108 — 16 bilinear depth taps along the slice direction.
+// Precision: the thickness break compares view-space z of consecutive samples, and z is ill-conditioned in d, so the
+// depth footprint stays the exact unfused bilinear and z the correctly rounded quotient; the horizon cosine itself is a
+// running max of a continuous quantity (value-only: rsqrt normalisation, FMA dot products).
 __device__ __forceinline__ float find_horizon(const Mip& depth, float su, float sv, f3 camera_start, float dirx, float diry,
-                                              int samples_count, f3 v, const CamK& cam) {
+                                              f3 v, const CamF& cam) {
   float h_cos = -1.0f;
   float previous_z = camera_start.z;
-  for (int i = 1; i <= samples_count; i++) {
-    float s = (float)i / (float)samples_count;
-    float tu = FA(su, FM(s, dirx)), tv = FA(sv, FM(s, diry));
-    float sample_depth = sample_d24(depth, tu, tv);
-    f3 sample_pos = reconstruct_view_vec(tu, tv, sample_depth, cam);
-    if (sample_pos.z > FA(previous_z, MAX_THIKNESS)) break;
-    previous_z = sample_pos.z;
-    f3 sample_offset = sample_pos - camera_start;
-    float sample_cos = dot3(v, norm3(sample_offset));
-    if (sample_cos > h_cos) h_cos = sample_cos;
+#pragma unroll 1
+  for (int i = 1; i <= 16; i++) {
+    const float s = (float)i * 0.0625f;                                      // float(i) / 16, exact
+    const float tu = FA(su, FM(s, dirx)), tv = FA(sv, FM(s, diry));
+    const float z = linearize_rn(sample_d24(depth, tu, tv), cam);
+    if (z > FA(previous_z, MAX_THIKNESS)) break;
+    previous_z = z;
+    const f3 off = mk3(fmaf(1.0f - 2.f * tu, z * cam.aspect_tg, -camera_start.x), fmaf(1.0f - 2.f * tv, z * cam.tg, -camera_start.y), z - camera_start.z);
+    const float sample_cos = dot3f(v, off) * rsqrtf(dot3f(off, off));
+    h_cos = fmaxf(h_cos, sample_cos);                                        // a NaN (zero offset) is ignored by both max forms
   }
   return h_cos;
 }
@@ -38,29 +41,35 @@ __device__ __forceinline__ float find_horizon(const Mip& depth, float su, float 
 // main.comp:276-278
 __device__ __forceinline__ float gtao_direction(int x, int y) { return (1.0f / 16.0f) * (float)((((x + y) & 3) << 2) + (x & 3)); }
 
-// slice integral shared by mis_gtao (:232-246) and gtao_camera_space (:199-214)
-__device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& k, float su, float sv, float frag_depth, f3 camera_pos,
+// slice integral shared by mis_gtao (:232-246) and gtao_camera_space (:199-214).
+// The projected-normal angle n = pi/2 - acos(dot(normalize(np), X)) sits on the edge of acos' domain for grazing
+// surfaces: whether the argument rounds to 1 or 1 + 2^-23 decides between a finite angle and NaN, and a NaN texel
+// spreads through the 4x4 filter and the temporal history.  Everything feeding it therefore keeps the oracle's
+// unfused IEEE evaluation (once per pixel); the 16-tap horizon search and the closing integral are value-only.
+__device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& k, const CamF& cam, float su, float sv, float frag_depth, f3 camera_pos,
                                                  f3 w0, f3 camera_normal, float rx, float ry, float angle, f3* Lout, bool mis) {
-  float sdx = FM(rx, cosf(angle)), sdy = FM(ry, sinf(angle));
-  f3 sample_end_pos = reconstruct_view_vec(FA(su, sdx), FA(sv, sdy), frag_depth, k.cam);
+  const float sdx = FM(rx, cosf(angle)), sdy = FM(ry, sinf(angle));
+  const f3 sample_end_pos = reconstruct_view_vec(FA(su, sdx), FA(sv, sdy), frag_depth, k.cam);
   if (Lout) *Lout = norm3(sample_end_pos - camera_pos);
-  f3 slice_normal = norm3(cross3(w0, -sample_end_pos));
-  f3 normal_projected = camera_normal - dot3(camera_normal, slice_normal) * slice_normal;
-  f3 X = -norm3(cross3(slice_normal, w0));
-  float n = FS(VKR_PI / 2.0f, acosf(dot3(norm3(normal_projected), X)));
-  float h_cos = find_horizon(depth, su, sv, camera_pos, sdx, sdy, 16, w0, k.cam);
+  const f3 slice_normal = norm3(cross3(w0, -sample_end_pos));
+  const f3 normal_projected = camera_normal - dot3(camera_normal, slice_normal) * slice_normal;
+  const f3 X = -norm3(cross3(slice_normal, w0));
+  const float n = FS(VKR_PI / 2.0f, acosf(dot3(norm3(normal_projected), X)));
+  const float h_cos = find_horizon(depth, su, sv, camera_pos, sdx, sdy, w0, cam);
   float h = acosf(h_cos);
-  h = gmin(FA(n, gmin(FS(h, n), VKR_PI / 2.0f)), h);
-  const float lenp = mis ? FM(1.0f / VKR_PI, len3(normal_projected)) : len3(normal_projected);   // main.comp:246 vs :213
-  return FM(FM(lenp, 0.25f), gmax(FA(FA(-cosf(FS(FM(2.f, h), n)), cosf(n)), FM(FM(2.f, h), sinf(n))), 0.0f));
+  h = gmin(FA(n, gmin(FS(h, n), VKR_PI / 2.0f)), h);                        // GLSL min: a NaN n propagates
+  const float len = len3(normal_projected);
+  const float lenp = mis ? (1.0f / VKR_PI) * len : len;                     // main.comp:246 vs :213
+  return (lenp * 0.25f) * gmax(-__cosf(2.f * h - n) + __cosf(n) + 2.f * h * __sinf(n), 0.0f);
 }
 
-__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Mip depth, Mip normal, Mip material, Mip pdf, Mip raw, const float* __restrict__ srgb) {
+__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf, Mip raw, const float* __restrict__ srgb) {
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (px >= k.tw || py >= k.th) return;
-  const float su = ((float)px + 0.5f) / (float)k.tw, sv = ((float)py + 0.5f) / (float)k.th;
+  const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
   uint2* out = (uint2*)(raw.p + (size_t)py * raw.pitch) + px;
   float ox = 0.f, oy = 1.0f / (2 * VKR_PI);
+  const CamF cam = make_camf(k.cam);
 
   const float frag_depth = sample_d24(depth, su, sv);
   if (k.use_mis > 0) {                                                     // mis_gtao, main.comp:219-274
@@ -73,9 +82,15 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Mip depth, Mip 
     float base_angle = FA(gtao_direction(px, py), k.angle_offset);
     float angle = FM(2 * VKR_PI, base_angle);
     f3 L;
-    float occlusion = slice_occlusion(depth, k, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true);
+    float occlusion = slice_occlusion(depth, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true);
 
-    float roughness = sample_srgb8(material, su, sv, srgb).y;
+    float roughness;
+    {
+      const TapW t = make_tapw(su, sv, material.w, material.h);              // only .g of the footprint is needed
+#define CHG(x, y) __ldg(srgb + ((ld32(material, x, y) >> 8) & 255u))
+      roughness = wsum(CHG(t.x0, t.y0), CHG(t.x1, t.y0), CHG(t.x0, t.y1), CHG(t.x1, t.y1), t);
+#undef CHG
+    }
     float pdf_ggx = sampleGGXdirPDF(pdf, w0, camera_normal, L, FM(roughness, roughness));
     float pdf_uniform = 1.0f / (2 * VKR_PI);
     uint2 prev = *out;
@@ -104,7 +119,7 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Mip depth, Mip 
       float sum = 0.f;
       for (int d = 0; d < dirs; d++) {
         float angle = 2 * VKR_PI * (base_angle + (float)d / (float)dirs);
-        sum += slice_occlusion(depth, k, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false);
+        sum += slice_occlusion(depth, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false);
       }
       ox = 2 * sum / (float)dirs;
     }
@@ -221,7 +236,7 @@ extern "C" int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, cons
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("gtao_main: sRGB table upload failed"); return VKR_ERR_CUDA; }
   dim3 grid((k.tw + 31) / 32, (k.th + 7) / 8);
-  gtao_main_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_mip(depth, depth_lod), make_mip(normal, 0), make_mip(material, 0),
+  gtao_main_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_dim(k.tw, k.th), make_mip(depth, depth_lod), make_mip(normal, 0), make_mip(material, 0),
                                                            make_mip(pdf_lut, 0), make_mip(raw, 0), srgb);
   return check_launch("gtao_main_kernel");
 }
