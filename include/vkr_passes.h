@@ -125,6 +125,32 @@ typedef struct VkrTaaParams {
   float fovy_aspect_znear_zfar[4];
 } VkrTaaParams;
 
+/* ---- extended launches: array layers and row windows ------------------------------------
+ * Every pass entry has an `_ex` twin taking a VkrLaunchExt (NULL = the plain call):
+ *  - layers > 1: each VkrImage argument describes layer 0 of an array image whose layers lie
+ *    layer_stride[i] bytes apart (i = position of the image among the entry's VkrImage arguments,
+ *    0-based; stride 0 = one image shared by every layer, e.g. a LUT), `p` points to `layers`
+ *    params structs in HOST memory and params_scratch to device memory of at least
+ *    layers * VKR_PARAMS_SCRATCH_STRIDE bytes that stays untouched until the stream passes the call.
+ *    Layers ride on grid.z, so hundreds of small views fill the GPU in one launch.  This is the
+ *    array_layers / base_layer / layers_count notion of gpu::ImageInfo / gpu::ImageViewRange
+ *    (reference src/gpu/resource_info.hpp:11-45) that probe_renderer renders its cube faces into
+ *    (src/probe_renderer.cpp:205-235).
+ *  - row_begin/row_end: compute only output rows [row_begin, row_end) of the pass's output image
+ *    (0,0 = all).  Both must be multiples of VKR_ROW_ALIGN unless row_end is the image height.
+ *    Used to split one very large frame into row tiles across GPUs; the caller supplies whatever
+ *    rows of the inputs the pass reads beyond its window (halo exchange).  No reference counterpart
+ *    (BASELINE.json configs[4]).  vkr_hiz_build_ex rejects row windows (the pyramid is built whole). */
+#define VKR_ROW_ALIGN 16
+#define VKR_PARAMS_SCRATCH_STRIDE 256
+#define VKR_MAX_IMAGE_ARGS 10
+typedef struct VkrLaunchExt {
+  uint32_t layers;
+  uint32_t row_begin, row_end;
+  uint64_t layer_stride[VKR_MAX_IMAGE_ARGS];
+  void* params_scratch;
+} VkrLaunchExt;
+
 /* ---- utilities ---------------------------------------------------------------- */
 const char* vkr_version(void);
 /* Thread-local text of the last failure on this thread ("" if none). */
@@ -197,6 +223,33 @@ int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* albedo, cons
 /* Task "TAA" (reference src/taa.cpp:14-63, taa/resolve.comp). */
 int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
                     const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, void* stream);
+
+/* ---- _ex twins (see VkrLaunchExt) ---------------------------------------------------- */
+int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity, const VkrImage* out_normal,
+                     const VkrImage* out_velocity, const VkrLaunchExt* ext, void* stream);
+int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth, const VkrImage* dnormal, const VkrImage* material,
+                      const float* halton_vec4x128, const VkrImage* pdf_lut, const VkrImage* out_rays,
+                      const VkrImage* out_occlusion, const VkrLaunchExt* ext, void* stream);
+int vkr_sssr_filter_ex(const VkrTraceParams* p, const VkrImage* rays, const VkrImage* depth, const VkrImage* albedo,
+                       const VkrImage* normal, const VkrImage* material, const VkrImage* out_reflections,
+                       const VkrLaunchExt* ext, void* stream);
+int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
+                     const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity,
+                     const VkrImage* prev_depth, const VkrImage* out_blurred, const VkrLaunchExt* ext, void* stream);
+int vkr_gtao_main_ex(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
+                     const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, const VkrLaunchExt* ext, void* stream);
+int vkr_gtao_filter_ex(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
+                       uint32_t depth_lod, const VkrLaunchExt* ext, void* stream);
+int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth,
+                           const VkrImage* filtered, const VkrImage* accumulated, const VkrImage* dvelocity,
+                           const VkrImage* history, uint32_t depth_lod, const VkrLaunchExt* ext, void* stream);
+int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage* albedo, const VkrImage* normal,
+                            const VkrImage* material, const VkrImage* depth, const VkrImage* occlusion,
+                            const VkrImage* brdf_lut, const VkrImage* reflections, const VkrImage* out_color,
+                            const VkrLaunchExt* ext, void* stream);
+int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
+                       const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target,
+                       const VkrLaunchExt* ext, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,96 @@
+"""Array-layer (batched views) and row-window launches through the `_ex` C-ABI entries.
+
+  * a batch of independent views in ONE launch per pass equals the per-view CPU oracle (same tolerances as the
+    single-view parity tests) — BASELINE configs[3] shape;
+  * a pass computed in two row windows writes exactly the bytes of the whole-frame pass — BASELINE configs[4] shape.
+"""
+import numpy as np
+import pytest
+
+import chain
+import parity
+import vkr
+import vkr_views
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("w,h,views,frames", [(128, 64, [3, 11, 12, 40, 7], 3), (256, 256, [0, 5], 2)])
+def test_batched_views_match_oracle(cuda, w, h, views, frames):
+    import torch
+    ob = chain.OracleBackend()
+    pdf_ref = vkr.Image(256, 256, vkr.R32_SFLOAT, device="cpu")
+    ob.pdf_lut(pdf_ref)
+    brdf_ref = vkr.Image(16, 16, vkr.R16G16_SFLOAT, device="cpu")      # lighting is not part of the view batch
+    oracles = [chain.Chain(w, h, chain.OracleBackend(), luts=(pdf_ref, brdf_ref)) for _ in views]
+    vb = vkr_views.ViewBatch(w, h, views, luts=pdf_ref.clone_to("cuda"))
+    failures = []
+    for f in range(frames):
+        refs = [oc.render(vkr.synth_scene(v, 64), view_seed=v)[0] for oc, v in zip(oracles, views)]
+        vb.synth_inputs()
+        vb.passes(vb.params(jitters=[chain.angle_jitter(f)] * len(views)))
+        torch.cuda.synchronize()
+        got = dict(depth=vb.depth, dn=vb.dn, dv=vb.dv, rays=vb.rays, raw=vb.raw, reflections=vb.reflections, blurred=vb.blurred,
+                   filtered=vb.filtered, accumulated_ao=vb.accumulated_ao)
+        for i, v in enumerate(views):
+            for name, arr in got.items():
+                m = parity.compare_image(name, arr.layer(i), refs[i][name])
+                if not parity.TOLERANCES[name](m):
+                    failures.append((f, v, name, m))
+        vb.end_frame()
+    assert not failures, failures
+
+
+def _split(hh):
+    mid = (hh // 2) // vkr.ROW_ALIGN * vkr.ROW_ALIGN
+    return [(0, mid), (mid, hh)]
+
+
+def test_row_windows_equal_whole_pass(cuda):
+    import torch
+    w, h = 256, 160
+    scene = vkr.synth_scene(2, 64)
+    cc = chain.Chain(w, h, chain.CudaBackend(), lut_size=64)
+    cc.render(scene)                                   # frame 0 fills the histories
+    P = cc.begin_frame(scene)
+    gb = cc.gb
+    hd = cc.b._hd(cc.halton)
+    E = lambda imgs, rows: vkr.make_ext(imgs, rows=rows)  # noqa: E731
+    # (name, whole-pass thunk, windowed call taking rows, outputs, output height)
+    passes = [
+        ("SSSR_trace", lambda r: vkr.sssr_trace_ex(P["trace"], gb.depth, gb.downsampled_normals, gb.material, hd, cc.pdf, cc.rays, cc.raw, E([], r)), [cc.rays, cc.raw]),
+        ("SSSR_filter", lambda r: vkr.sssr_filter_ex(P["trace"], cc.rays, gb.depth, gb.albedo, gb.normal, gb.material, cc.reflections, E([], r)), [cc.reflections]),
+        ("SSSR_blur", lambda r: vkr.sssr_blur_ex(P["blur"], gb.depth, gb.normal, cc.reflections, gb.material, cc.blurred_history, gb.downsampled_velocity_vectors,
+                                                 gb.prev_depth, cc.blurred, E([], r)), [cc.blurred]),
+        ("GTAO_main", lambda r: vkr.gtao_main_ex(P["gtao"], gb.depth, gb.normal, gb.material, cc.pdf, cc.raw, E([], r)), [cc.raw]),
+        ("GTAO_filter", lambda r: vkr.gtao_filter_ex(P["gtao"], gb.depth, cc.raw, cc.filtered, E([], r)), [cc.filtered]),
+        ("GTAO_accumulate", lambda r: vkr.gtao_accumulate_ex(P["accum"], gb.depth, gb.prev_depth, cc.filtered, cc.accumulated_ao, gb.downsampled_velocity_vectors,
+                                                             cc.accumulated_history, E([], r)), [cc.accumulated_ao]),
+        ("DeferedShading", lambda r: vkr.deferred_shading_ex(P["shade"], gb.albedo, gb.normal, gb.material, gb.depth, cc.accumulated_ao, cc.brdf, cc.blurred,
+                                                             cc.color_out, E([], r)), [cc.color_out]),
+        ("TAA", lambda r: vkr.taa_resolve_ex(P["taa"], cc.taa_history, gb.prev_depth, gb.depth, gb.velocity_vectors, cc.color_out, cc.taa_target, E([], r)),
+         [cc.taa_target]),
+    ]
+    cc.b.hiz(gb.depth, gb.normal, gb.velocity_vectors, gb.downsampled_normals, gb.downsampled_velocity_vectors)
+    for name, call, outs in passes:
+        before = [o.buf.clone() for o in outs]
+        call(None)                                      # rows = None -> 0,0 = the whole image
+        torch.cuda.synchronize()
+        whole = [o.buf.clone() for o in outs]
+        for o, b in zip(outs, before):
+            o.buf.copy_(b)
+        for rows in _split(outs[0].height):
+            call(rows)
+        torch.cuda.synchronize()
+        for o, wbuf in zip(outs, whole):
+            assert torch.equal(o.buf, wbuf), f"{name}: windowed result differs from the whole pass"
+
+
+def test_row_window_validation(cuda):
+    cc = chain.Chain(128, 64, chain.CudaBackend(), lut_size=16)
+    P = chain.frame_params(vkr.synth_camera(0, 0, 128, 64, True), 0, 0)
+    with pytest.raises(vkr.VkrError, match="aligned"):
+        vkr.gtao_filter_ex(P["gtao"], cc.gb.depth, cc.raw, cc.filtered, vkr.make_ext([], rows=(8, 32)))
+    with pytest.raises(vkr.VkrError, match="row windows are not supported"):
+        vkr.hiz_build_ex(cc.gb.depth, cc.gb.normal, cc.gb.velocity_vectors, cc.gb.downsampled_normals, cc.gb.downsampled_velocity_vectors,
+                         vkr.make_ext([], rows=(0, 16)))

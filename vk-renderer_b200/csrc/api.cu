@@ -26,6 +26,36 @@ int check_launch(const char* what) {
   return VKR_OK;
 }
 
+int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what) {
+  o->e = e;
+  o->layers = (e && e->layers > 1) ? (int)e->layers : 1;
+  const int total = (int)((out_h + tile_h - 1) / tile_h);
+  o->yb0 = 0; o->yblocks = total;
+  if (e && (e->row_begin != 0 || e->row_end != 0)) {
+    const uint32_t y0 = e->row_begin, y1 = e->row_end < out_h ? e->row_end : out_h;
+    if (y0 >= y1 || (y0 % VKR_ROW_ALIGN) != 0 || (y1 != out_h && (y1 % VKR_ROW_ALIGN) != 0) || (VKR_ROW_ALIGN % tile_h) != 0) {
+      set_error("%s: row window [%u, %u) must be non-empty and aligned to %d rows (or end at the image height %u)", what, e->row_begin, e->row_end, VKR_ROW_ALIGN, out_h);
+      return VKR_ERR_INVALID_ARGUMENT;
+    }
+    o->yb0 = (int)(y0 / tile_h);
+    o->yblocks = (int)((y1 - y0 + tile_h - 1) / tile_h);
+  }
+  if (o->layers > 1 && !e->params_scratch) {
+    set_error("%s: layers > 1 needs params_scratch (device memory, layers * VKR_PARAMS_SCRATCH_STRIDE bytes)", what);
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  if (o->layers > 65535) { set_error("%s: at most 65535 layers per launch", what); return VKR_ERR_INVALID_ARGUMENT; }
+  return VKR_OK;
+}
+
+int upload_params(const void* host, size_t elem, int count, void* scratch, cudaStream_t st, const char* what) {
+  if (elem > VKR_PARAMS_SCRATCH_STRIDE) { set_error("%s: params block larger than the scratch stride", what); return VKR_ERR_UNSUPPORTED; }
+  // pageable source: the runtime stages it before returning, so `host` may be a temporary
+  cudaError_t e = cudaMemcpyAsync(scratch, host, elem * (size_t)count, cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) { set_error("%s: params upload: %s", what, cudaGetErrorString(e)); return VKR_ERR_CUDA; }
+  return VKR_OK;
+}
+
 CamK make_cam(float fovy, float aspect, float znear, float zfar) {
   CamK c;
   c.aspect = aspect; c.znear = znear; c.zfar = zfar;

@@ -25,6 +25,7 @@ struct Mip {
   const unsigned char* p;
   int w, h;
   unsigned pitch;
+  unsigned long long ls;   // bytes between array layers (0 = one image shared by every layer)
 };
 
 inline int mip_dim(uint32_t d, uint32_t lod) { uint32_t v = d >> lod; return v ? (int)v : 1; }
@@ -39,8 +40,26 @@ inline Mip make_mip(const VkrImage* im, uint32_t lod) {
   m.w = mip_dim(im->width, lod);
   m.h = mip_dim(im->height, lod);
   m.pitch = im->row_pitch[lod];
+  m.ls = 0;
   return m;
 }
+
+// ---- extended launches (VkrLaunchExt): array layers on grid.z, row windows as a block-row offset --------------
+struct LaunchX {
+  int yb0;   // first block row of the window (blockIdx.y is relative to it)
+};
+struct ExtInfo {
+  int layers = 1;
+  int yb0 = 0, yblocks = 0;
+  const VkrLaunchExt* e = nullptr;
+  uint64_t stride(int i) const { return (e && e->layers > 1) ? e->layer_stride[i] : 0; }
+  void* scratch() const { return e ? e->params_scratch : nullptr; }
+};
+// Validates ext against a pass whose output has out_h rows processed in tiles of tile_h rows.
+int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what);
+inline Mip make_mip(const VkrImage* im, uint32_t lod, const ExtInfo& x, int arg_index) { Mip m = make_mip(im, lod); m.ls = x.stride(arg_index); return m; }
+// Per-layer kernel parameter blocks: converts nothing, just ships `count` POD structs to the device scratch on `stream`.
+int upload_params(const void* host, size_t elem, int count, void* scratch, cudaStream_t st, const char* what);
 
 struct CamK {  // camera constants; tg = tanf(fovy/2) evaluated once on the host
   float aspect, znear, zfar, tg;
@@ -56,6 +75,8 @@ inline Mat4 make_mat(const float* p) { Mat4 r; for (int i = 0; i < 16; i++) r.m[
 
 #ifdef __CUDACC__
 // ---- device side -------------------------------------------------------------
+__device__ __forceinline__ Mip layer_of(Mip m, int z) { m.p += (size_t)z * m.ls; return m; }
+#define VKR_BLOCK_Y ((int)blockIdx.y + lx.yb0)
 #define VKR_PI 3.1415926535897932384626433832795f
 
 // Unfused fp32: the oracle evaluates every expression as separate IEEE mul/add/sub (it is

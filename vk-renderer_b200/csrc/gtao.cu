@@ -2,6 +2,7 @@
 //
 // Replaces tasks "GTAO_main", "GTAO_filter", "GTAO_accumulate"
 // (reference src/gtao.cpp:84-148,:198-239,:286-347; shaders/gtao/{main,filter,accum}.comp).
+#include <vector>
 #include "brdf.cuh"
 
 namespace vkr {
@@ -63,8 +64,17 @@ __device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& 
   return (lenp * 0.25f) * gmax(-__cosf(2.f * h - n) + __cosf(n) + 2.f * h * __sinf(n), 0.0f);
 }
 
-__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf, Mip raw, const float* __restrict__ srgb) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+template <bool LAYERED>
+__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k0, const GtaoK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf,
+                                                        Mip raw, const float* __restrict__ srgb) {
+  GtaoK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    depth = layer_of(depth, z); normal = layer_of(normal, z); material = layer_of(material, z); pdf = layer_of(pdf, z); raw = layer_of(raw, z);
+  }
+  const GtaoK& k = LAYERED ? kl : k0;
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
   if (px >= k.tw || py >= k.th) return;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
   uint2* out = (uint2*)(raw.p + (size_t)py * raw.pitch) + px;
@@ -133,10 +143,11 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k, Dim dim, Mip de
 #define GF_H 8
 #define GF_SW (GF_W + 3)
 #define GF_SH (GF_H + 3)
-__global__ void __launch_bounds__(256) gtao_filter_kernel(Mip depth, Mip raw, Mip filtered, int tw, int th, float znear, float zfar) {
+__global__ void __launch_bounds__(256) gtao_filter_kernel(LaunchX lx, Mip depth, Mip raw, Mip filtered, int tw, int th, float znear, float zfar) {
   __shared__ float s_z[GF_SH][GF_SW + 1];
   __shared__ float s_r[GF_SH][GF_SW + 1];
-  const int bx = blockIdx.x * GF_W - 2, by = blockIdx.y * GF_H - 2;
+  depth = layer_of(depth, blockIdx.z); raw = layer_of(raw, blockIdx.z); filtered = layer_of(filtered, blockIdx.z);   // znear/zfar: one set per launch
+  const int bx = blockIdx.x * GF_W - 2, by = VKR_BLOCK_Y * GF_H - 2;
   const float nf = FM(znear, zfar), fmn = FS(zfar, znear);
   for (int t = threadIdx.x; t < GF_SW * GF_SH; t += 256) {
     const int ly = t / GF_SW, lx = t - ly * GF_SW;
@@ -147,7 +158,7 @@ __global__ void __launch_bounds__(256) gtao_filter_kernel(Mip depth, Mip raw, Mi
   }
   __syncthreads();
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int px = blockIdx.x * GF_W + tx, py = blockIdx.y * GF_H + ty;
+  const int px = blockIdx.x * GF_W + tx, py = VKR_BLOCK_Y * GF_H + ty;
   if (px >= tw || py >= th) return;
   const float linear_depth = s_z[ty + 2][tx + 2];
   const float k5 = 5.f * rcp_fast(fabsf(linear_depth));
@@ -172,9 +183,18 @@ struct AccumK {
 
 // accum.comp:29-99.  Depth footprints keep the exact unfused bilinear and the exact z denominator (far depths amplify a
 // 1-ulp difference to ~1e-3 view units, and depth_err is thresholded); everything else is value-only.
-template <bool SAME>
-__global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k, Dim dim, Mip depth, Mip prev_depth, Mip filtered, Mip out, Mip velocity, Mip history) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+template <bool SAME, bool LAYERED>
+__global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k0, const AccumK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip prev_depth, Mip filtered,
+                                                              Mip out, Mip velocity, Mip history) {
+  AccumK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    depth = layer_of(depth, z); prev_depth = layer_of(prev_depth, z); filtered = layer_of(filtered, z); out = layer_of(out, z);
+    velocity = layer_of(velocity, z); history = layer_of(history, z);
+  }
+  const AccumK& k = LAYERED ? kl : k0;
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
   const float tw = dim.w, th = dim.h;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
@@ -219,30 +239,52 @@ __global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k, Dim dim,
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
-                             const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, void* stream) {
-  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth_lod >= depth->mip_count || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) ||
-      !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(pdf_lut, VKR_FORMAT_R32_SFLOAT) || !image_ok(raw, VKR_FORMAT_R16G16B16A16_SFLOAT)) {
-    set_error("gtao_main: null argument or unexpected format");
-    return VKR_ERR_INVALID_ARGUMENT;
-  }
+static GtaoK make_gtao_k(const VkrGtaoParams* p, const VkrImage* raw) {
   GtaoK k;
   k.normal_mat = make_mat(p->normal_mat);
   k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
   k.angle_offset = p->angle_offset; k.weight_ratio = p->weight_ratio;
   k.use_mis = p->use_mis; k.two_directions = p->two_directions; k.reflections_only = p->reflections_only;
   k.tw = (int)(raw->width / 8) * 8; k.th = (int)(raw->height / 4) * 4;  // truncating dispatch, gtao.cpp:145
+  return k;
+}
+
+extern "C" int vkr_gtao_main_ex(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
+                                const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, const VkrLaunchExt* ext, void* stream) {
+  if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth_lod >= depth->mip_count || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) ||
+      !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(pdf_lut, VKR_FORMAT_R32_SFLOAT) || !image_ok(raw, VKR_FORMAT_R16G16B16A16_SFLOAT)) {
+    set_error("gtao_main: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  GtaoK k = make_gtao_k(p, raw);
   if (k.tw == 0 || k.th == 0) return VKR_OK;
+  ExtInfo x;
+  int rc = resolve_ext(ext, (uint32_t)k.th, 8, &x, "gtao_main");
+  if (rc) return rc;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("gtao_main: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((k.tw + 31) / 32, (k.th + 7) / 8);
-  gtao_main_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_dim(k.tw, k.th), make_mip(depth, depth_lod), make_mip(normal, 0), make_mip(material, 0),
-                                                           make_mip(pdf_lut, 0), make_mip(raw, 0), srgb);
+  cudaStream_t st = (cudaStream_t)stream;
+  const GtaoK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<GtaoK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_gtao_k(p + i, raw);
+    if ((rc = upload_params(ks.data(), sizeof(GtaoK), x.layers, x.scratch(), st, "gtao_main"))) return rc;
+    kv = (const GtaoK*)x.scratch();
+  }
+  dim3 grid((k.tw + 31) / 32, x.yblocks, x.layers);
+  auto kern = kv ? gtao_main_kernel<true> : gtao_main_kernel<false>;
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, make_dim(k.tw, k.th), make_mip(depth, depth_lod, x, 0), make_mip(normal, 0, x, 1), make_mip(material, 0, x, 2),
+                             make_mip(pdf_lut, 0, x, 3), make_mip(raw, 0, x, 4), srgb);
   return check_launch("gtao_main_kernel");
 }
 
-extern "C" int vkr_gtao_filter(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
-                               uint32_t depth_lod, void* stream) {
+extern "C" int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,
+                             const VkrImage* pdf_lut, const VkrImage* raw, uint32_t depth_lod, void* stream) {
+  return vkr_gtao_main_ex(p, depth, normal, material, pdf_lut, raw, depth_lod, nullptr, stream);
+}
+
+extern "C" int vkr_gtao_filter_ex(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
+                                  uint32_t depth_lod, const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth_lod >= depth->mip_count ||
       !image_ok(raw, VKR_FORMAT_R16G16B16A16_SFLOAT) || !image_ok(filtered, VKR_FORMAT_R16_SFLOAT)) {
     set_error("gtao_filter: null argument or unexpected format");
@@ -250,13 +292,33 @@ extern "C" int vkr_gtao_filter(const VkrGtaoParams* p, const VkrImage* depth, co
   }
   int tw = (int)(filtered->width / 8) * 8, th = (int)(filtered->height / 4) * 4;  // gtao.cpp:237
   if (tw == 0 || th == 0) return VKR_OK;
-  dim3 grid((tw + 31) / 32, (th + 7) / 8);
-  gtao_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(make_mip(depth, depth_lod), make_mip(raw, 0), make_mip(filtered, 0), tw, th, p->znear, p->zfar);
+  ExtInfo x;
+  int rc = resolve_ext(ext, (uint32_t)th, 8, &x, "gtao_filter");
+  if (rc) return rc;
+  for (int i = 1; i < x.layers; i++)
+    if (p[i].znear != p[0].znear || p[i].zfar != p[0].zfar) { set_error("gtao_filter: layers must share znear/zfar"); return VKR_ERR_UNSUPPORTED; }
+  dim3 grid((tw + 31) / 32, x.yblocks, x.layers);
+  gtao_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(LaunchX{x.yb0}, make_mip(depth, depth_lod, x, 0), make_mip(raw, 0, x, 1), make_mip(filtered, 0, x, 2), tw, th,
+                                                             p->znear, p->zfar);
   return check_launch("gtao_filter_kernel");
 }
 
-extern "C" int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth, const VkrImage* filtered,
-                                   const VkrImage* accumulated, const VkrImage* dvelocity, const VkrImage* history, uint32_t depth_lod, void* stream) {
+extern "C" int vkr_gtao_filter(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* raw, const VkrImage* filtered,
+                               uint32_t depth_lod, void* stream) {
+  return vkr_gtao_filter_ex(p, depth, raw, filtered, depth_lod, nullptr, stream);
+}
+
+static AccumK make_accum_k(const VkrAccumParams* p) {
+  AccumK k;
+  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera); k.mvp = make_mat(p->mvp);
+  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  k.clear_history = p->clear_history;
+  return k;
+}
+
+extern "C" int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth, const VkrImage* filtered,
+                                      const VkrImage* accumulated, const VkrImage* dvelocity, const VkrImage* history, uint32_t depth_lod,
+                                      const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || !image_ok(prev_depth, VKR_FORMAT_D24_UNORM_S8_UINT) ||
       depth_lod >= depth->mip_count || depth_lod >= prev_depth->mip_count || !image_ok(filtered, VKR_FORMAT_R16_SFLOAT) ||
       !image_ok(accumulated, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(dvelocity, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(history, VKR_FORMAT_R16G16_SFLOAT)) {
@@ -267,15 +329,29 @@ extern "C" int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* dept
     set_error("gtao_accumulate: filtered and accumulated sizes differ");
     return VKR_ERR_SIZE_MISMATCH;
   }
-  AccumK k;
-  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera); k.mvp = make_mat(p->mvp);
-  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
-  k.clear_history = p->clear_history;
-  dim3 grid((accumulated->width + 31) / 32, (accumulated->height + 7) / 8);
+  ExtInfo x;
+  int rc = resolve_ext(ext, accumulated->height, 8, &x, "gtao_accumulate");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  AccumK k = make_accum_k(p);
+  const AccumK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<AccumK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_accum_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(AccumK), x.layers, x.scratch(), st, "gtao_accumulate"))) return rc;
+    kv = (const AccumK*)x.scratch();
+  }
+  dim3 grid((accumulated->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(accumulated->width, accumulated->height);
   const bool same = same_extent(dvelocity, accumulated) && accumulated->width <= 8192 && accumulated->height <= 8192;
-  auto kern = same ? gtao_accumulate_kernel<true> : gtao_accumulate_kernel<false>;
-  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(depth, depth_lod), make_mip(prev_depth, depth_lod), make_mip(filtered, 0),
-                                                                 make_mip(accumulated, 0), make_mip(dvelocity, 0), make_mip(history, 0));
+  auto kern = same ? (kv ? gtao_accumulate_kernel<true, true> : gtao_accumulate_kernel<true, false>)
+                   : (kv ? gtao_accumulate_kernel<false, true> : gtao_accumulate_kernel<false, false>);
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, dim, make_mip(depth, depth_lod, x, 0), make_mip(prev_depth, depth_lod, x, 1), make_mip(filtered, 0, x, 2),
+                             make_mip(accumulated, 0, x, 3), make_mip(dvelocity, 0, x, 4), make_mip(history, 0, x, 5));
   return check_launch("gtao_accumulate_kernel");
+}
+
+extern "C" int vkr_gtao_accumulate(const VkrAccumParams* p, const VkrImage* depth, const VkrImage* prev_depth, const VkrImage* filtered,
+                                   const VkrImage* accumulated, const VkrImage* dvelocity, const VkrImage* history, uint32_t depth_lod, void* stream) {
+  return vkr_gtao_accumulate_ex(p, depth, prev_depth, filtered, accumulated, dvelocity, history, depth_lod, nullptr, stream);
 }

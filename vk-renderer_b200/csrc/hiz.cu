@@ -25,10 +25,11 @@ struct HizLevels {
 // level i is "degenerate" when its source level i-1 has a dimension of 1.
 __device__ __forceinline__ bool degenerate(const HizLevels& L, int i) { return L.mip[i - 1].w == 1 || L.mip[i - 1].h == 1; }
 
-__device__ __forceinline__ void st_level(const HizLevels& L, int i, int x, int y, uint32_t v) {
+// loff: byte offset of this launch's array layer inside the depth allocation (0 for a single image)
+__device__ __forceinline__ void st_level(const HizLevels& L, size_t loff, int i, int x, int y, uint32_t v) {
   if (i < L.count && x < L.mip[i].w && y < L.mip[i].h) {
     if (degenerate(L, i)) v = 0u;
-    *((uint32_t*)(L.mip[i].p + (size_t)y * L.mip[i].pitch) + x) = v;
+    *((uint32_t*)(L.mip[i].p + loff + (size_t)y * L.mip[i].pitch) + x) = v;
   }
 }
 
@@ -39,7 +40,10 @@ template <bool PAYLOAD>
 __global__ void __launch_bounds__(256) hiz_tile_kernel(HizLevels L, int src, int levels, Mip normal, Mip velocity, Mip out_normal, Mip out_velocity) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tx = (warp & 1) * 8 + (lane & 7), ty = (warp >> 1) * 4 + (lane >> 3);
-  const Mip s = L.mip[src];
+  const size_t loff = (size_t)blockIdx.z * L.mip[0].ls;
+  if (PAYLOAD) { normal = layer_of(normal, blockIdx.z); velocity = layer_of(velocity, blockIdx.z); out_normal = layer_of(out_normal, blockIdx.z); out_velocity = layer_of(out_velocity, blockIdx.z); }
+  Mip s = L.mip[src];
+  s.p += loff;
   const int x0 = blockIdx.x * 64 + tx * 4, y0 = blockIdx.y * 64 + ty * 4;
 
   // 4 rows x uint4 of source depth; absent texels are neutral for min.
@@ -56,7 +60,8 @@ __global__ void __launch_bounds__(256) hiz_tile_kernel(HizLevels L, int src, int
 
   // level src+1: 2x2 texels per thread (+ payload select, downsample_gbuffer.frag:24-36)
   uint32_t m1[2][2];
-  const Mip l1 = L.mip[src + 1];
+  Mip l1 = L.mip[src + 1];
+  l1.p += loff;
 #pragma unroll
   for (int j = 0; j < 2; j++)
 #pragma unroll
@@ -86,22 +91,22 @@ __global__ void __launch_bounds__(256) hiz_tile_kernel(HizLevels L, int src, int
       if (Y + j < l1.h && X + 1 < l1.w && !degenerate(L, src + 1)) {
         *((uint2*)(l1.p + (size_t)(Y + j) * l1.pitch + (size_t)X * 4)) = make_uint2(m1[j][0], m1[j][1]);
       } else {
-        st_level(L, src + 1, X, Y + j, m1[j][0]);
-        st_level(L, src + 1, X + 1, Y + j, m1[j][1]);
+        st_level(L, loff, src + 1, X, Y + j, m1[j][0]);
+        st_level(L, loff, src + 1, X + 1, Y + j, m1[j][1]);
       }
     }
   }
   if (levels < 2) return;
   uint32_t m = min(min(m1[0][0], m1[0][1]), min(m1[1][0], m1[1][1]));
-  st_level(L, src + 2, x0 >> 2, y0 >> 2, m);
+  st_level(L, loff, src + 2, x0 >> 2, y0 >> 2, m);
   if (levels < 3) return;
   m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, 1));
   m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, 8));
-  if ((lane & 9) == 0) st_level(L, src + 3, x0 >> 3, y0 >> 3, m);
+  if ((lane & 9) == 0) st_level(L, loff, src + 3, x0 >> 3, y0 >> 3, m);
   if (levels < 4) return;
   m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, 2));
   m = min(m, __shfl_xor_sync(0xFFFFFFFFu, m, 16));
-  if ((lane & 27) == 0) st_level(L, src + 4, x0 >> 4, y0 >> 4, m);
+  if ((lane & 27) == 0) st_level(L, loff, src + 4, x0 >> 4, y0 >> 4, m);
   if (levels < 5) return;
   // warp = 2x1 level-4 texels (lanes 0 and 4); level-5 texel = 2 (x) x 2 (y) of them.
   __shared__ uint32_t s4[4][4];  // [level-4 row][level-4 column] of the tile
@@ -110,19 +115,21 @@ __global__ void __launch_bounds__(256) hiz_tile_kernel(HizLevels L, int src, int
   if (threadIdx.x < 4) {
     int cx = threadIdx.x & 1, cy = threadIdx.x >> 1;
     uint32_t v = min(min(s4[2 * cy][2 * cx], s4[2 * cy][2 * cx + 1]), min(s4[2 * cy + 1][2 * cx], s4[2 * cy + 1][2 * cx + 1]));
-    st_level(L, src + 5, blockIdx.x * 2 + cx, blockIdx.y * 2 + cy, v);
+    st_level(L, loff, src + 5, blockIdx.x * 2 + cx, blockIdx.y * 2 + cy, v);
     if (levels >= 6) {
       v = min(v, __shfl_xor_sync(0xFu, v, 1));
       v = min(v, __shfl_xor_sync(0xFu, v, 2));
-      if (threadIdx.x == 0) st_level(L, src + 6, blockIdx.x, blockIdx.y, v);
+      if (threadIdx.x == 0) st_level(L, loff, src + 6, blockIdx.x, blockIdx.y, v);
     }
   }
 }
 
 // One CTA walks the remaining (small) levels; plain loads so the CTA sees its own stores.
 __global__ void __launch_bounds__(1024) hiz_tail_kernel(HizLevels L, int first) {
+  const size_t loff = (size_t)blockIdx.x * L.mip[0].ls;     // one CTA per array layer
   for (int i = first; i < L.count; i++) {
-    const Mip s = L.mip[i - 1], o = L.mip[i];
+    Mip s = L.mip[i - 1], o = L.mip[i];
+    s.p += loff; o.p += loff;
     const int n = o.w * o.h;
     for (int t = threadIdx.x; t < n; t += blockDim.x) {
       int x = t % o.w, y = t / o.w;
@@ -139,17 +146,20 @@ __global__ void __launch_bounds__(1024) hiz_tail_kernel(HizLevels L, int first) 
   }
 }
 
-static HizLevels make_levels(const VkrImage* depth) {
+static HizLevels make_levels(const VkrImage* depth, uint64_t layer_stride) {
   HizLevels L;
   L.count = (int)depth->mip_count;
-  for (int i = 0; i < VKR_MAX_MIPS; i++) L.mip[i] = (i < L.count) ? make_mip(depth, i) : Mip{nullptr, 0, 0, 0};
+  for (int i = 0; i < VKR_MAX_MIPS; i++) {
+    L.mip[i] = (i < L.count) ? make_mip(depth, i) : Mip{nullptr, 0, 0, 0, 0};
+    L.mip[i].ls = layer_stride;
+  }
   return L;
 }
 
 // Builds levels src+1 .. L-1.  payload images may be null (depth only).
 static int hiz_run(const VkrImage* depth, int src, const VkrImage* normal, const VkrImage* velocity,
-                   const VkrImage* out_normal, const VkrImage* out_velocity, int max_levels, cudaStream_t st) {
-  HizLevels L = make_levels(depth);
+                   const VkrImage* out_normal, const VkrImage* out_velocity, int max_levels, cudaStream_t st, const ExtInfo& x = ExtInfo()) {
+  HizLevels L = make_levels(depth, x.stride(0));
   int cur = src;
   bool payload = normal != nullptr;
   const int TAIL_TEXELS = 16384;
@@ -157,14 +167,14 @@ static int hiz_run(const VkrImage* depth, int src, const VkrImage* normal, const
     int remaining = L.count - 1 - cur;
     if (max_levels > 0 && remaining > max_levels) remaining = max_levels;
     if (!payload && L.mip[cur].w * L.mip[cur].h <= TAIL_TEXELS && max_levels <= 0) {
-      hiz_tail_kernel<<<1, 1024, 0, st>>>(L, cur + 1);
+      hiz_tail_kernel<<<x.layers, 1024, 0, st>>>(L, cur + 1);
       return check_launch("hiz_tail_kernel");
     }
     int levels = remaining < 6 ? remaining : 6;
-    dim3 grid((L.mip[cur].w + 63) / 64, (L.mip[cur].h + 63) / 64);
-    Mip none{nullptr, 0, 0, 0};
+    dim3 grid((L.mip[cur].w + 63) / 64, (L.mip[cur].h + 63) / 64, x.layers);
+    Mip none{nullptr, 0, 0, 0, 0};
     if (payload)
-      hiz_tile_kernel<true><<<grid, 256, 0, st>>>(L, cur, levels, make_mip(normal, 0), make_mip(velocity, 0), make_mip(out_normal, 0), make_mip(out_velocity, 0));
+      hiz_tile_kernel<true><<<grid, 256, 0, st>>>(L, cur, levels, make_mip(normal, 0, x, 1), make_mip(velocity, 0, x, 2), make_mip(out_normal, 0, x, 3), make_mip(out_velocity, 0, x, 4));
     else
       hiz_tile_kernel<false><<<grid, 256, 0, st>>>(L, cur, levels, none, none, none, none);
     int rc = check_launch("hiz_tile_kernel");
@@ -215,9 +225,22 @@ extern "C" int vkr_depth_mips(const VkrImage* depth, uint32_t src_mip, void* str
   return hiz_run(depth, (int)src_mip, nullptr, nullptr, nullptr, nullptr, 0, (cudaStream_t)stream);
 }
 
-extern "C" int vkr_hiz_build(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity,
-                             const VkrImage* out_normal, const VkrImage* out_velocity, void* stream) {
+extern "C" int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity,
+                                const VkrImage* out_normal, const VkrImage* out_velocity, const VkrLaunchExt* ext, void* stream) {
   int rc = check_downsample_args(depth, normal, velocity, out_normal, out_velocity);
   if (rc) return rc;
-  return hiz_run(depth, 0, normal, velocity, out_normal, out_velocity, 0, (cudaStream_t)stream);
+  if (ext && (ext->row_begin != 0 || ext->row_end != 0)) {
+    set_error("hiz_build: row windows are not supported (the pyramid is built whole)");
+    return VKR_ERR_UNSUPPORTED;
+  }
+  ExtInfo x;
+  VkrLaunchExt e2;
+  if (ext) { e2 = *ext; if (e2.layers > 1 && !e2.params_scratch) e2.params_scratch = (void*)depth->base; }   // no params: scratch unused
+  if ((rc = resolve_ext(ext ? &e2 : nullptr, depth->height, 16, &x, "hiz_build"))) return rc;
+  return hiz_run(depth, 0, normal, velocity, out_normal, out_velocity, 0, (cudaStream_t)stream, x);
+}
+
+extern "C" int vkr_hiz_build(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity,
+                             const VkrImage* out_normal, const VkrImage* out_velocity, void* stream) {
+  return vkr_hiz_build_ex(depth, normal, velocity, out_normal, out_velocity, nullptr, stream);
 }

@@ -2,6 +2,7 @@
 // reflections + split-sum BRDF LUT.  Replaces task "DeferedShading"
 // (reference src/defered_shading.cpp:47-118, shaders/defered_shading/shader.frag:41-130).
 // Output is R8G8B8A8_SRGB (linear -> sRGB on store, reference src/main.cpp:289-291).
+#include <vector>
 #include "brdf.cuh"
 
 namespace vkr {
@@ -34,11 +35,20 @@ __device__ __forceinline__ float srgb_encode_fast(float l) {       // linear -> 
 
 // SAME: albedo / normal / material have the output's extent, so their bilinear footprint at the pixel's own
 // centre is the texel itself (common.cuh tap_is_texel).
-template <bool SAME>
-__global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Dim dim, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip depth0, Mip depth1,
-                                                               Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex, Mip out,
-                                                               const float* __restrict__ srgb) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+template <bool SAME, bool LAYERED>
+__global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const ShadeK* __restrict__ kv, LaunchX lx, Dim dim, Mip albedo_tex, Mip normal_tex,
+                                                               Mip material_tex, Mip depth0, Mip depth1, Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex,
+                                                               Mip out, const float* __restrict__ srgb) {
+  ShadeK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    albedo_tex = layer_of(albedo_tex, z); normal_tex = layer_of(normal_tex, z); material_tex = layer_of(material_tex, z);
+    depth0 = layer_of(depth0, z); depth1 = layer_of(depth1, z); occlusion_tex = layer_of(occlusion_tex, z);
+    brdf_tex = layer_of(brdf_tex, z); reflections_tex = layer_of(reflections_tex, z); out = layer_of(out, z);
+  }
+  const ShadeK& k = LAYERED ? kl : k0;
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
 #define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
@@ -163,28 +173,51 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k, Dim dim
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* albedo, const VkrImage* normal, const VkrImage* material,
-                                    const VkrImage* depth, const VkrImage* occlusion, const VkrImage* brdf_lut, const VkrImage* reflections,
-                                    const VkrImage* out_color, void* stream) {
+static ShadeK make_shade_k(const VkrShadingParams* p) {
+  ShadeK k;
+  k.inverse_camera = make_mat(p->inverse_camera);
+  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
+  k.min_r = p->min_max_roughness[0]; k.max_r = p->min_max_roughness[1]; k.show_ao = p->show_ao;
+  return k;
+}
+
+extern "C" int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage* albedo, const VkrImage* normal, const VkrImage* material,
+                                       const VkrImage* depth, const VkrImage* occlusion, const VkrImage* brdf_lut, const VkrImage* reflections,
+                                       const VkrImage* out_color, const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(albedo, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) || !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) ||
       !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 || !image_ok(occlusion, VKR_FORMAT_R16G16_SFLOAT) ||
       !image_ok(brdf_lut, VKR_FORMAT_R16G16_SFLOAT) || !image_ok(reflections, VKR_FORMAT_R8G8B8A8_UNORM) || !image_ok(out_color, VKR_FORMAT_R8G8B8A8_SRGB)) {
     set_error("deferred_shading: null argument or unexpected format");
     return VKR_ERR_INVALID_ARGUMENT;
   }
-  ShadeK k;
-  k.inverse_camera = make_mat(p->inverse_camera);
-  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
-  k.min_r = p->min_max_roughness[0]; k.max_r = p->min_max_roughness[1]; k.show_ao = p->show_ao;
+  ExtInfo x;
+  int rc = resolve_ext(ext, out_color->height, 8, &x, "deferred_shading");
+  if (rc) return rc;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("deferred_shading: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_color->width + 31) / 32, (out_color->height + 7) / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  ShadeK k = make_shade_k(p);
+  const ShadeK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<ShadeK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_shade_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(ShadeK), x.layers, x.scratch(), st, "deferred_shading"))) return rc;
+    kv = (const ShadeK*)x.scratch();
+  }
+  dim3 grid((out_color->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(out_color->width, out_color->height);
   const bool same = same_extent(albedo, out_color) && same_extent(normal, out_color) && same_extent(material, out_color) &&
                     out_color->width <= 8192 && out_color->height <= 8192;
-  auto kern = same ? deferred_shading_kernel<true> : deferred_shading_kernel<false>;
-  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(albedo, 0), make_mip(normal, 0), make_mip(material, 0), make_mip(depth, 0),
-                                                                  make_mip(depth, 1), make_mip(occlusion, 0), make_mip(brdf_lut, 0),
-                                                                  make_mip(reflections, 0), make_mip(out_color, 0), srgb);
+  auto kern = same ? (kv ? deferred_shading_kernel<true, true> : deferred_shading_kernel<true, false>)
+                   : (kv ? deferred_shading_kernel<false, true> : deferred_shading_kernel<false, false>);
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, dim, make_mip(albedo, 0, x, 0), make_mip(normal, 0, x, 1), make_mip(material, 0, x, 2),
+                             make_mip(depth, 0, x, 3), make_mip(depth, 1, x, 3), make_mip(occlusion, 0, x, 4), make_mip(brdf_lut, 0, x, 5),
+                             make_mip(reflections, 0, x, 6), make_mip(out_color, 0, x, 7), srgb);
   return check_launch("deferred_shading_kernel");
+}
+
+extern "C" int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* albedo, const VkrImage* normal, const VkrImage* material,
+                                    const VkrImage* depth, const VkrImage* occlusion, const VkrImage* brdf_lut, const VkrImage* reflections,
+                                    const VkrImage* out_color, void* stream) {
+  return vkr_deferred_shading_ex(p, albedo, normal, material, depth, occlusion, brdf_lut, reflections, out_color, nullptr, stream);
 }

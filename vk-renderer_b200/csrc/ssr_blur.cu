@@ -11,6 +11,7 @@
 // Warps iterate the window of their largest radius in lockstep (lanes outside their own
 // radius skip), which keeps the shared-memory reads conflict-free and preserves each pixel's
 // accumulation order (i = x offset outer, j = y offset inner, as in blur.comp:57-75).
+#include <vector>
 #include "common.cuh"
 
 namespace vkr {
@@ -31,15 +32,23 @@ __device__ __forceinline__ f3 world_pos_lod(const Mip& depth1, const Mat4& inv, 
   return mul_m4f(inv, reconstruct_fast(u, v, sample_d24(depth1, u, v), cam));
 }
 
-template <bool SAME>
-__global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Dim dim, Mip depth1, Mip normal_tex, Mip refl, Mip material_tex, Mip history, Mip velocity,
-                                                        Mip prev_depth1, Mip out, const float* __restrict__ srgb) {
+template <bool SAME, bool LAYERED>
+__global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k0, const BlurK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth1, Mip normal_tex, Mip refl,
+                                                        Mip material_tex, Mip history, Mip velocity, Mip prev_depth1, Mip out, const float* __restrict__ srgb) {
   __shared__ float4 s_nd[BLUR_SPAN * BLUR_SPAN];
   __shared__ float4 s_col[BLUR_SPAN * BLUR_SPAN];
   __shared__ int s_rmax;
+  BlurK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    depth1 = layer_of(depth1, z); normal_tex = layer_of(normal_tex, z); refl = layer_of(refl, z); material_tex = layer_of(material_tex, z);
+    history = layer_of(history, z); velocity = layer_of(velocity, z); prev_depth1 = layer_of(prev_depth1, z); out = layer_of(out, z);
+  }
+  const BlurK& k = LAYERED ? kl : k0;
 
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const int px = blockIdx.x * BLUR_TILE + tx, py = blockIdx.y * BLUR_TILE + ty;
+  const int px = blockIdx.x * BLUR_TILE + tx, py = VKR_BLOCK_Y * BLUR_TILE + ty;
   const bool inside = px < out.w && py < out.h;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
 
@@ -63,7 +72,7 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Dim dim, Mip de
   const int span = BLUR_TILE + 2 * R;
 
   // stage {normal, depth} and colour for every tap position of the tile
-  const int ox = blockIdx.x * BLUR_TILE - R, oy = blockIdx.y * BLUR_TILE - R;
+  const int ox = blockIdx.x * BLUR_TILE - R, oy = VKR_BLOCK_Y * BLUR_TILE - R;
   for (int t = threadIdx.x; t < span * span; t += 256) {
     const int ly = t / span, lx = t - ly * span;
     const int qx = ox + lx, qy = oy + ly;
@@ -167,9 +176,17 @@ __global__ void __launch_bounds__(256) sssr_blur_kernel(BlurK k, Dim dim, Mip de
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
-                             const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity, const VkrImage* prev_depth,
-                             const VkrImage* out_blurred, void* stream) {
+static BlurK make_blur_k(const VkrBlurParams* p) {
+  BlurK k;
+  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera);
+  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  k.max_roughness = p->max_roughness; k.accumulate = p->accumulate; k.disable_blur = p->disable_blur;
+  return k;
+}
+
+extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
+                                const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity, const VkrImage* prev_depth,
+                                const VkrImage* out_blurred, const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 || !image_ok(prev_depth, VKR_FORMAT_D24_UNORM_S8_UINT) ||
       prev_depth->mip_count < 2 || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) || !image_ok(reflections, VKR_FORMAT_R8G8B8A8_UNORM) ||
       !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(history, VKR_FORMAT_R8G8B8A8_UNORM) ||
@@ -182,22 +199,37 @@ extern "C" int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, cons
     set_error("sssr_blur: reflections / history / blurred sizes differ");
     return VKR_ERR_SIZE_MISMATCH;
   }
-  if (!(p->max_roughness >= 0.f && p->max_roughness <= 1.f)) {   // radius bound r <= 11 assumes sigma <= 4
-    set_error("sssr_blur: max_roughness outside [0,1]");
-    return VKR_ERR_UNSUPPORTED;
-  }
+  ExtInfo x;
+  int rc = resolve_ext(ext, out_blurred->height, BLUR_TILE, &x, "sssr_blur");
+  if (rc) return rc;
+  for (int i = 0; i < x.layers; i++)
+    if (!(p[i].max_roughness >= 0.f && p[i].max_roughness <= 1.f)) {   // radius bound r <= 11 assumes sigma <= 4
+      set_error("sssr_blur: max_roughness outside [0,1]");
+      return VKR_ERR_UNSUPPORTED;
+    }
   if (history->base == out_blurred->base) { set_error("sssr_blur: history and output alias"); return VKR_ERR_INVALID_ARGUMENT; }
-  BlurK k;
-  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera);
-  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
-  k.max_roughness = p->max_roughness; k.accumulate = p->accumulate; k.disable_blur = p->disable_blur;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_blur: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_blurred->width + BLUR_TILE - 1) / BLUR_TILE, (out_blurred->height + BLUR_TILE - 1) / BLUR_TILE);
+  cudaStream_t st = (cudaStream_t)stream;
+  BlurK k = make_blur_k(p);
+  const BlurK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<BlurK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_blur_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(BlurK), x.layers, x.scratch(), st, "sssr_blur"))) return rc;
+    kv = (const BlurK*)x.scratch();
+  }
+  dim3 grid((out_blurred->width + BLUR_TILE - 1) / BLUR_TILE, x.yblocks, x.layers);
   const bool same = same_extent(dvelocity, out_blurred) && out_blurred->width <= 8192 && out_blurred->height <= 8192;
-  auto kern = same ? sssr_blur_kernel<true> : sssr_blur_kernel<false>;
-  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_dim(out_blurred->width, out_blurred->height), make_mip(depth, 1), make_mip(normal, 0), make_mip(reflections, 0), make_mip(material, 0),
-                                                           make_mip(history, 0), make_mip(dvelocity, 0), make_mip(prev_depth, 1),
-                                                           make_mip(out_blurred, 0), srgb);
+  auto kern = same ? (kv ? sssr_blur_kernel<true, true> : sssr_blur_kernel<true, false>) : (kv ? sssr_blur_kernel<false, true> : sssr_blur_kernel<false, false>);
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, make_dim(out_blurred->width, out_blurred->height), make_mip(depth, 1, x, 0), make_mip(normal, 0, x, 1),
+                             make_mip(reflections, 0, x, 2), make_mip(material, 0, x, 3), make_mip(history, 0, x, 4), make_mip(dvelocity, 0, x, 5),
+                             make_mip(prev_depth, 1, x, 6), make_mip(out_blurred, 0, x, 7), srgb);
   return check_launch("sssr_blur_kernel");
+}
+
+extern "C" int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* reflections,
+                             const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity, const VkrImage* prev_depth,
+                             const VkrImage* out_blurred, void* stream) {
+  return vkr_sssr_blur_ex(p, depth, normal, reflections, material, history, dvelocity, prev_depth, out_blurred, nullptr, stream);
 }

@@ -2,6 +2,7 @@
 // Replaces task "SSSR_filter" (reference src/advanced_ssr.cpp:308-369,
 // shaders/advanced_ssr/filter.comp:36-149).  Quirks kept on purpose:
 // uv = pixel / size without +0.5 (#5) and the swapped brdfG1 arguments (#4).
+#include <vector>
 #include "brdf.cuh"
 
 namespace vkr {
@@ -28,11 +29,20 @@ struct TapRec {
 
 // Nothing here selects between discrete alternatives (ray validity is an exact unorm16 compare), so the whole pass runs on
 // the value-only helpers of common.cuh; depth linearisation keeps its exact denominator.
-__global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k, Dim dim, Mip rays, Mip depth1, Mip albedo_tex, Mip normal_tex, Mip material_tex, Mip out,
-                                                          const float* __restrict__ srgb) {
+template <bool LAYERED>
+__global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k0, const FilterK* __restrict__ kv, LaunchX lx, Dim dim, Mip rays, Mip depth1, Mip albedo_tex,
+                                                          Mip normal_tex, Mip material_tex, Mip out, const float* __restrict__ srgb) {
   __shared__ float4 s_a[(FT_W + 2) * (FT_H + 2)];
   __shared__ float4 s_b[(FT_W + 2) * (FT_H + 2)];
-  const int bx = blockIdx.x * FT_W - 1, by = blockIdx.y * FT_H - 1;
+  FilterK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    rays = layer_of(rays, z); depth1 = layer_of(depth1, z); albedo_tex = layer_of(albedo_tex, z); normal_tex = layer_of(normal_tex, z);
+    material_tex = layer_of(material_tex, z); out = layer_of(out, z);
+  }
+  const FilterK& k = LAYERED ? kl : k0;
+  const int bx = blockIdx.x * FT_W - 1, by = VKR_BLOCK_Y * FT_H - 1;
   const CamF cam = make_camf(k.cam);
 #define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
 
@@ -70,7 +80,7 @@ __global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k, Dim dim, Mi
   __syncthreads();
 
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int px = blockIdx.x * FT_W + tx, py = blockIdx.y * FT_H + ty;
+  const int px = blockIdx.x * FT_W + tx, py = VKR_BLOCK_Y * FT_H + ty;
   if (px >= out.w || py >= out.h) return;
   const float su = texel_uv(px, dim.w, dim.rw), sv = texel_uv(py, dim.h, dim.rh);                // :39
 
@@ -119,8 +129,16 @@ __global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k, Dim dim, Mi
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_sssr_filter(const VkrTraceParams* p, const VkrImage* rays, const VkrImage* depth, const VkrImage* albedo,
-                               const VkrImage* normal, const VkrImage* material, const VkrImage* out_reflections, void* stream) {
+static FilterK make_filter_k(const VkrTraceParams* p) {
+  FilterK k;
+  k.normal_mat = make_mat(p->normal_mat);
+  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
+  k.render_flags = p->render_flags;
+  return k;
+}
+
+extern "C" int vkr_sssr_filter_ex(const VkrTraceParams* p, const VkrImage* rays, const VkrImage* depth, const VkrImage* albedo,
+                                  const VkrImage* normal, const VkrImage* material, const VkrImage* out_reflections, const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(rays, VKR_FORMAT_R16G16B16A16_UNORM) || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 ||
       !image_ok(albedo, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(normal, VKR_FORMAT_R16G16_UNORM) || !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) ||
       !image_ok(out_reflections, VKR_FORMAT_R8G8B8A8_UNORM)) {
@@ -131,14 +149,28 @@ extern "C" int vkr_sssr_filter(const VkrTraceParams* p, const VkrImage* rays, co
     set_error("sssr_filter: rays and reflections sizes differ");
     return VKR_ERR_SIZE_MISMATCH;
   }
-  FilterK k;
-  k.normal_mat = make_mat(p->normal_mat);
-  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
-  k.render_flags = p->render_flags;
+  ExtInfo x;
+  int rc = resolve_ext(ext, out_reflections->height, FT_H, &x, "sssr_filter");
+  if (rc) return rc;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_filter: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_reflections->width + FT_W - 1) / FT_W, (out_reflections->height + FT_H - 1) / FT_H);
-  sssr_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(k, make_dim(out_reflections->width, out_reflections->height), make_mip(rays, 0), make_mip(depth, 1), make_mip(albedo, 0), make_mip(normal, 0),
-                                                             make_mip(material, 0), make_mip(out_reflections, 0), srgb);
+  cudaStream_t st = (cudaStream_t)stream;
+  FilterK k = make_filter_k(p);
+  const FilterK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<FilterK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_filter_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(FilterK), x.layers, x.scratch(), st, "sssr_filter"))) return rc;
+    kv = (const FilterK*)x.scratch();
+  }
+  dim3 grid((out_reflections->width + FT_W - 1) / FT_W, x.yblocks, x.layers);
+  auto kern = kv ? sssr_filter_kernel<true> : sssr_filter_kernel<false>;
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, make_dim(out_reflections->width, out_reflections->height), make_mip(rays, 0, x, 0), make_mip(depth, 1, x, 1),
+                             make_mip(albedo, 0, x, 2), make_mip(normal, 0, x, 3), make_mip(material, 0, x, 4), make_mip(out_reflections, 0, x, 5), srgb);
   return check_launch("sssr_filter_kernel");
+}
+
+extern "C" int vkr_sssr_filter(const VkrTraceParams* p, const VkrImage* rays, const VkrImage* depth, const VkrImage* albedo,
+                               const VkrImage* normal, const VkrImage* material, const VkrImage* out_reflections, void* stream) {
+  return vkr_sssr_filter_ex(p, rays, depth, albedo, normal, material, out_reflections, nullptr, stream);
 }

@@ -3,6 +3,7 @@
 // validity tests, and the ray's (occlusion, pdf) deposited into gtao.raw for the MIS combine.
 // Replaces task "SSSR_trace" (reference src/advanced_ssr.cpp:147-214,
 // shaders/advanced_ssr/trace.comp:41-141,:206-268, shaders/include/screen_trace.glsl:8-45).
+#include <vector>
 #include "brdf.cuh"
 
 namespace vkr {
@@ -30,11 +31,11 @@ __device__ __forceinline__ float rand_hash(float u, float v) {
   return __fsub_rn(p, floorf(p));
 }
 
-__device__ __forceinline__ float fetch_pyramid(const PyramidView& P, int x, int y, int lod) {
+__device__ __forceinline__ float fetch_pyramid(const PyramidView& P, unsigned long long layer_off, int x, int y, int lod) {
   if ((unsigned)lod >= (unsigned)P.count) return 0.0f;
   const Mip& m = P.mip[lod];
   if ((unsigned)x >= (unsigned)m.w || (unsigned)y >= (unsigned)m.h) return 0.0f;      // texelFetch out of range = 0 (App. A.3)
-  return d24_to_float(__ldg((const uint32_t*)(m.p + (size_t)y * m.pitch) + x));
+  return d24_to_float(__ldg((const uint32_t*)(m.p + layer_off + (size_t)y * m.pitch) + x));
 }
 
 // screen_trace.glsl:17-45
@@ -54,9 +55,19 @@ __device__ __forceinline__ bool advance_ray(f3 origin, f3 direction, f3 inv_dire
   return skipped_tile;
 }
 
-__global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P, Mip normal, Mip material, const float4* __restrict__ halton,
-                                                         Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
-  const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = blockIdx.y * 8 + (threadIdx.x >> 4);
+template <bool LAYERED>
+__global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
+                                                         const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
+  TraceK kl;
+  unsigned long long poff = 0;                         // layer offset of the depth pyramid (one allocation per layer holds every mip)
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    poff = (unsigned long long)z * P.mip[0].ls;
+    normal = layer_of(normal, z); material = layer_of(material, z); pdf = layer_of(pdf, z); out_rays = layer_of(out_rays, z); out_occl = layer_of(out_occl, z);
+  }
+  const TraceK& k = LAYERED ? kl : k0;
+  const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 4);
   if (px >= out_rays.w || py >= out_rays.h) return;
   const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
   const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
@@ -67,7 +78,8 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
   float mg = gmix(0.0f, k.max_roughness, roughness);
   roughness = FM(mg, mg);
 
-  const Mip d0 = P.mip[0];
+  Mip d0 = P.mip[0];
+  d0.p += poff;
   float pixel_depth = sample_d24(d0, su, sv);
   f3 pixel_normal = norm3(mul_m4(k.normal_mat, sample_gbuffer_normal(normal, su, sv), 0.f));
   f3 view_vec = reconstruct_view_vec(su, sv, pixel_depth, cam);
@@ -115,7 +127,7 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
   int i = 0;
   while (i < 80 && current_mip >= 0) {
     float mpx = FM(resx, position.x), mpy = FM(resy, position.y);
-    float surface_z = fetch_pyramid(P, (int)mpx, (int)mpy, current_mip);
+    float surface_z = fetch_pyramid(P, poff, (int)mpx, (int)mpy, current_mip);
     bool skipped = advance_ray(origin, direction, inv_direction, mpx, mpy, rinvx, rinvy, fox, foy, uox, uoy, surface_z, position, current_t);
     bool mip0sample = i < 15;
     if (!mip0sample) {
@@ -176,9 +188,17 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k, PyramidView P
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_sssr_trace(const VkrTraceParams* p, const VkrImage* depth, const VkrImage* dnormal, const VkrImage* material,
-                              const float* halton_vec4x128, const VkrImage* pdf_lut, const VkrImage* out_rays,
-                              const VkrImage* out_occlusion, void* stream) {
+static TraceK make_trace_k(const VkrTraceParams* p) {
+  TraceK k;
+  k.normal_mat = make_mat(p->normal_mat);
+  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
+  k.frame_random = p->frame_random; k.max_roughness = p->max_roughness;
+  return k;
+}
+
+extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth, const VkrImage* dnormal, const VkrImage* material,
+                                 const float* halton_vec4x128, const VkrImage* pdf_lut, const VkrImage* out_rays,
+                                 const VkrImage* out_occlusion, const VkrLaunchExt* ext, void* stream) {
   if (!p || !halton_vec4x128 || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 ||
       !image_ok(dnormal, VKR_FORMAT_R16G16_UNORM) || !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(pdf_lut, VKR_FORMAT_R32_SFLOAT) ||
       !image_ok(out_rays, VKR_FORMAT_R16G16B16A16_UNORM) || !image_ok(out_occlusion, VKR_FORMAT_R16G16B16A16_SFLOAT)) {
@@ -189,17 +209,32 @@ extern "C" int vkr_sssr_trace(const VkrTraceParams* p, const VkrImage* depth, co
     set_error("sssr_trace: rays and occlusion sizes differ");
     return VKR_ERR_SIZE_MISMATCH;
   }
-  TraceK k;
-  k.normal_mat = make_mat(p->normal_mat);
-  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
-  k.frame_random = p->frame_random; k.max_roughness = p->max_roughness;
+  ExtInfo x;
+  int rc = resolve_ext(ext, out_rays->height, 8, &x, "sssr_trace");
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  TraceK k = make_trace_k(p);
+  const TraceK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<TraceK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_trace_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(TraceK), x.layers, x.scratch(), st, "sssr_trace"))) return rc;
+    kv = (const TraceK*)x.scratch();
+  }
   PyramidView P;
   P.count = (int)depth->mip_count - 1;
-  for (int i = 0; i < VKR_MAX_MIPS; i++) P.mip[i] = (i < P.count) ? make_mip(depth, i + 1) : Mip{nullptr, 0, 0, 0};
+  for (int i = 0; i < VKR_MAX_MIPS; i++) P.mip[i] = (i < P.count) ? make_mip(depth, i + 1, x, 0) : Mip{nullptr, 0, 0, 0, 0};
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_trace: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_rays->width + 15) / 16, (out_rays->height + 7) / 8);
-  sssr_trace_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(k, P, make_mip(dnormal, 0), make_mip(material, 0), (const float4*)halton_vec4x128,
-                                                            make_mip(pdf_lut, 0), make_mip(out_rays, 0), make_mip(out_occlusion, 0), srgb);
+  dim3 grid((out_rays->width + 15) / 16, x.yblocks, x.layers);
+  auto kern = kv ? sssr_trace_kernel<true> : sssr_trace_kernel<false>;
+  kern<<<grid, 128, 0, st>>>(k, kv, LaunchX{x.yb0}, P, make_mip(dnormal, 0, x, 1), make_mip(material, 0, x, 2), (const float4*)halton_vec4x128,
+                             make_mip(pdf_lut, 0, x, 3), make_mip(out_rays, 0, x, 4), make_mip(out_occlusion, 0, x, 5), srgb);
   return check_launch("sssr_trace_kernel");
+}
+
+extern "C" int vkr_sssr_trace(const VkrTraceParams* p, const VkrImage* depth, const VkrImage* dnormal, const VkrImage* material,
+                              const float* halton_vec4x128, const VkrImage* pdf_lut, const VkrImage* out_rays,
+                              const VkrImage* out_occlusion, void* stream) {
+  return vkr_sssr_trace_ex(p, depth, dnormal, material, halton_vec4x128, pdf_lut, out_rays, out_occlusion, nullptr, stream);
 }

@@ -1,6 +1,7 @@
 // taa.cu — TAA resolve: velocity reprojection, 4-neighbour history clamp, 0.1 blend,
 // world-position rejection.  Replaces task "TAA" (reference src/taa.cpp:14-63,
 // shaders/taa/resolve.comp:20-77).  target is RGBA16F (the image's real format, App. A.6 #1).
+#include <vector>
 #include "common.cuh"
 
 namespace vkr {
@@ -39,10 +40,18 @@ __device__ __forceinline__ f3 wsum3(f3 a, f3 b, f3 c, f3 d, const TapW& w) {
 
 // SAME: colour and velocity have the output's extent, so their bilinear footprint at the pixel's own centre is the
 // texel itself (common.cuh tap_is_texel); otherwise the general footprint is evaluated.
-template <bool SAME>
-__global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k, Dim dim, Mip history, Mip prev_depth, Mip depth, Mip velocity, Mip color, Mip out,
-                                                          const float* __restrict__ srgb) {
-  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = blockIdx.y * 8 + (threadIdx.x >> 5);
+template <bool SAME, bool LAYERED>
+__global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k0, const TaaK* __restrict__ kv, LaunchX lx, Dim dim, Mip history, Mip prev_depth, Mip depth,
+                                                          Mip velocity, Mip color, Mip out, const float* __restrict__ srgb) {
+  TaaK kl;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    history = layer_of(history, z); prev_depth = layer_of(prev_depth, z); depth = layer_of(depth, z);
+    velocity = layer_of(velocity, z); color = layer_of(color, z); out = layer_of(out, z);
+  }
+  const TaaK& k = LAYERED ? kl : k0;
+  const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
   if (px >= out.w || py >= out.h) return;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
   const CamF cam = make_camf(k.cam);
@@ -106,8 +115,15 @@ __global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k, Dim dim, Mip h
 }  // namespace vkr
 using namespace vkr;
 
-extern "C" int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
-                               const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, void* stream) {
+static TaaK make_taa_k(const VkrTaaParams* p) {
+  TaaK k;
+  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera);
+  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  return k;
+}
+
+extern "C" int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
+                                  const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, const VkrLaunchExt* ext, void* stream) {
   if (!p || !image_ok(history, VKR_FORMAT_R16G16B16A16_SFLOAT) || !image_ok(prev_depth, VKR_FORMAT_D24_UNORM_S8_UINT) ||
       !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || !image_ok(velocity, VKR_FORMAT_R16G16_SFLOAT) ||
       !image_ok(color, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(out_target, VKR_FORMAT_R16G16B16A16_SFLOAT)) {
@@ -115,16 +131,30 @@ extern "C" int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, c
     return VKR_ERR_INVALID_ARGUMENT;
   }
   if (history->base == out_target->base) { set_error("taa_resolve: history and target alias"); return VKR_ERR_INVALID_ARGUMENT; }
-  TaaK k;
-  k.inverse_camera = make_mat(p->inverse_camera); k.prev_inverse_camera = make_mat(p->prev_inverse_camera);
-  k.cam = make_cam(p->fovy_aspect_znear_zfar[0], p->fovy_aspect_znear_zfar[1], p->fovy_aspect_znear_zfar[2], p->fovy_aspect_znear_zfar[3]);
+  ExtInfo x;
+  int rc = resolve_ext(ext, out_target->height, 8, &x, "taa_resolve");
+  if (rc) return rc;
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("taa_resolve: sRGB table upload failed"); return VKR_ERR_CUDA; }
-  dim3 grid((out_target->width + 31) / 32, (out_target->height + 7) / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  TaaK k = make_taa_k(p);
+  const TaaK* kv = nullptr;
+  if (x.layers > 1) {
+    std::vector<TaaK> ks(x.layers);
+    for (int i = 0; i < x.layers; i++) ks[i] = make_taa_k(p + i);
+    if ((rc = upload_params(ks.data(), sizeof(TaaK), x.layers, x.scratch(), st, "taa_resolve"))) return rc;
+    kv = (const TaaK*)x.scratch();
+  }
+  dim3 grid((out_target->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(out_target->width, out_target->height);
   const bool same = same_extent(color, out_target) && same_extent(velocity, out_target) && out_target->width <= 8192 && out_target->height <= 8192;
-  auto kern = same ? taa_resolve_kernel<true> : taa_resolve_kernel<false>;
-  kern<<<grid, 256, 0, (cudaStream_t)stream>>>(k, dim, make_mip(history, 0), make_mip(prev_depth, 0), make_mip(depth, 0),
-                                               make_mip(velocity, 0), make_mip(color, 0), make_mip(out_target, 0), srgb);
+  auto kern = same ? (kv ? taa_resolve_kernel<true, true> : taa_resolve_kernel<true, false>) : (kv ? taa_resolve_kernel<false, true> : taa_resolve_kernel<false, false>);
+  kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, dim, make_mip(history, 0, x, 0), make_mip(prev_depth, 0, x, 1), make_mip(depth, 0, x, 2),
+                             make_mip(velocity, 0, x, 3), make_mip(color, 0, x, 4), make_mip(out_target, 0, x, 5), srgb);
   return check_launch("taa_resolve_kernel");
+}
+
+extern "C" int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
+                               const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, void* stream) {
+  return vkr_taa_resolve_ex(p, history, prev_depth, depth, velocity, color, out_target, nullptr, stream);
 }

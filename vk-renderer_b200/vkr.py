@@ -342,3 +342,118 @@ def deferred_shading(p, albedo, normal, material, depth, occlusion, brdf, reflec
 
 def taa_resolve(p, history, prev_depth, depth, velocity, color, out, stream=None):
     check(lib.vkr_taa_resolve(C.byref(p), history.ptr, prev_depth.ptr, depth.ptr, velocity.ptr, color.ptr, out.ptr, stream_ptr(stream)))
+
+
+# ---- extended launches: array layers and row windows (include/vkr_passes.h VkrLaunchExt) ---------------
+class LaunchExt(C.Structure):
+    _fields_ = [("layers", C.c_uint32), ("row_begin", C.c_uint32), ("row_end", C.c_uint32), ("layer_stride", C.c_uint64 * 10),
+                ("params_scratch", C.c_void_p)]
+
+
+PARAMS_SCRATCH_STRIDE = 256
+ROW_ALIGN = 16
+EP = PT(LaunchExt)
+_sig("vkr_hiz_build_ex", IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_sssr_trace_ex", PT(TraceParams), IP, IP, IP, FP, IP, IP, IP, EP, VP)
+_sig("vkr_sssr_filter_ex", PT(TraceParams), IP, IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_sssr_blur_ex", PT(BlurParams), IP, IP, IP, IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_gtao_main_ex", PT(GtaoParams), IP, IP, IP, IP, IP, C.c_uint32, EP, VP)
+_sig("vkr_gtao_filter_ex", PT(GtaoParams), IP, IP, IP, C.c_uint32, EP, VP)
+_sig("vkr_gtao_accumulate_ex", PT(AccumParams), IP, IP, IP, IP, IP, IP, C.c_uint32, EP, VP)
+_sig("vkr_deferred_shading_ex", PT(ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_taa_resolve_ex", PT(TaaParams), IP, IP, IP, IP, IP, IP, EP, VP)
+
+
+class ImageArray:
+    """`layers` images of one extent/format in ONE allocation, layer i at base + i * layer_stride (an array image:
+    gpu::ImageInfo.array_layers, reference src/gpu/resource_info.hpp).  `desc` describes layer 0."""
+
+    def __init__(self, width, height, fmt, mips=1, layers=1, device="cuda"):
+        self.desc = VkrImage()
+        nbytes = int(lib.vkr_image_layout(width, height, fmt, mips, C.byref(self.desc)))
+        if nbytes == 0:
+            raise VkrError("vkr_image_layout rejected the arguments")
+        self.layer_stride = (nbytes + 255) & ~255
+        self.layers, self.width, self.height, self.format, self.mips = layers, width, height, fmt, mips
+        self.device = torch.device(device)
+        self.buf = torch.zeros(self.layer_stride * layers, dtype=torch.uint8, device=self.device)
+        self.desc.base = self.buf.data_ptr()
+        self.nbytes = nbytes
+
+    @property
+    def ptr(self):
+        return C.byref(self.desc)
+
+    def layer(self, i):
+        """An Image aliasing layer i (shares storage)."""
+        im = Image.__new__(Image)
+        im.desc = VkrImage.from_buffer_copy(self.desc)
+        im.nbytes, im.device = self.nbytes, self.device
+        im.buf = self.buf[i * self.layer_stride: i * self.layer_stride + self.nbytes]
+        im.desc.base = im.buf.data_ptr()
+        im.width, im.height, im.format, im.mips = self.width, self.height, self.format, self.mips
+        return im
+
+
+def make_ext(images, layers=1, rows=None, scratch=None):
+    """VkrLaunchExt for a call whose VkrImage arguments are `images` (ImageArray or Image, in argument order)."""
+    e = LaunchExt()
+    e.layers = layers
+    if rows is not None:
+        e.row_begin, e.row_end = rows
+    for i, im in enumerate(images):
+        e.layer_stride[i] = getattr(im, "layer_stride", 0) if layers > 1 else 0
+    e.params_scratch = scratch.data_ptr() if scratch is not None else None
+    return e
+
+
+def params_array(ptype, items):
+    arr = (ptype * len(items))()
+    for i, it in enumerate(items):
+        C.memmove(C.byref(arr, i * C.sizeof(ptype)), C.byref(it), C.sizeof(ptype))
+    return arr
+
+
+def _p(p):
+    """A single params struct or a ctypes array of them -> pointer to the first."""
+    return p if isinstance(p, C.Array) else C.byref(p)
+
+
+def hiz_build_ex(depth, normal, velocity, out_normal, out_velocity, ext, stream=None):
+    check(lib.vkr_hiz_build_ex(depth.ptr, normal.ptr, velocity.ptr, out_normal.ptr, out_velocity.ptr, C.byref(ext), stream_ptr(stream)))
+
+
+def sssr_trace_ex(p, depth, dnormal, material, halton_dev, pdf, rays, occlusion, ext, stream=None):
+    check(lib.vkr_sssr_trace_ex(_p(p), depth.ptr, dnormal.ptr, material.ptr, C.c_void_p(halton_dev.data_ptr()), pdf.ptr, rays.ptr, occlusion.ptr,
+                                C.byref(ext), stream_ptr(stream)))
+
+
+def sssr_filter_ex(p, rays, depth, albedo, normal, material, out, ext, stream=None):
+    check(lib.vkr_sssr_filter_ex(_p(p), rays.ptr, depth.ptr, albedo.ptr, normal.ptr, material.ptr, out.ptr, C.byref(ext), stream_ptr(stream)))
+
+
+def sssr_blur_ex(p, depth, normal, refl, material, history, dvel, prev_depth, out, ext, stream=None):
+    check(lib.vkr_sssr_blur_ex(_p(p), depth.ptr, normal.ptr, refl.ptr, material.ptr, history.ptr, dvel.ptr, prev_depth.ptr, out.ptr, C.byref(ext),
+                               stream_ptr(stream)))
+
+
+def gtao_main_ex(p, depth, normal, material, pdf, raw, ext, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_main_ex(_p(p), depth.ptr, normal.ptr, material.ptr, pdf.ptr, raw.ptr, depth_lod, C.byref(ext), stream_ptr(stream)))
+
+
+def gtao_filter_ex(p, depth, raw, filtered, ext, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_filter_ex(_p(p), depth.ptr, raw.ptr, filtered.ptr, depth_lod, C.byref(ext), stream_ptr(stream)))
+
+
+def gtao_accumulate_ex(p, depth, prev_depth, filtered, accumulated, dvel, history, ext, depth_lod=1, stream=None):
+    check(lib.vkr_gtao_accumulate_ex(_p(p), depth.ptr, prev_depth.ptr, filtered.ptr, accumulated.ptr, dvel.ptr, history.ptr, depth_lod, C.byref(ext),
+                                     stream_ptr(stream)))
+
+
+def deferred_shading_ex(p, albedo, normal, material, depth, occlusion, brdf, reflections, out, ext, stream=None):
+    check(lib.vkr_deferred_shading_ex(_p(p), albedo.ptr, normal.ptr, material.ptr, depth.ptr, occlusion.ptr, brdf.ptr, reflections.ptr, out.ptr,
+                                      C.byref(ext), stream_ptr(stream)))
+
+
+def taa_resolve_ex(p, history, prev_depth, depth, velocity, color, out, ext, stream=None):
+    check(lib.vkr_taa_resolve_ex(_p(p), history.ptr, prev_depth.ptr, depth.ptr, velocity.ptr, color.ptr, out.ptr, C.byref(ext), stream_ptr(stream)))

@@ -1,0 +1,150 @@
+"""Batched independent views (BASELINE.json configs[3]: 512 probe views of 256x256, GTAO + SSR) and their sharding.
+
+A view batch keeps every image of the per-view chain as an ARRAY image (vkr.ImageArray: one allocation, one layer per
+view) and runs each pass ONCE for the whole batch through the `_ex` entries with layers on grid.z — a single 256x256
+view has 64..256 CTAs and cannot fill 148 SMs, 512 of them in one launch can.  Views are independent units
+(SURVEY §8e): a rank owns a contiguous block of views, keeps their temporal state, and no collective touches the data
+path; only the final outputs are gathered (NCCL all_gather on GPUs, gloo in the CPU tests).
+
+The pass order is the reference's (src/main.cpp:347-390) without lighting and TAA, which probe views do not use
+(reference src/probe_renderer.cpp renders cube faces and traces them; config 4 asks for GTAO + SSR on those views).
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+import vkr
+
+ANGLE_TABLE = [60., 300., 180., 240., 120., 0., 300., 60., 180., 120., 240., 0.]  # src/gtao.cpp:109
+
+
+def shard_range(n_units, world, rank):
+    """Contiguous block [begin, end) of units owned by `rank`; the first n_units % world ranks get one extra."""
+    base, extra = divmod(n_units, world)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+def shard_sizes(n_units, world):
+    return [shard_range(n_units, world, r)[1] - shard_range(n_units, world, r)[0] for r in range(world)]
+
+
+def gather_blocks(local, n_units, group=None):
+    """All-gather per-rank blocks of shape (units_r, ...) into (n_units, ...) on every rank (ragged blocks are padded
+    to the largest one for the collective and trimmed afterwards).  Works on CUDA tensors over NCCL and CPU tensors
+    over gloo."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return local
+    sizes = shard_sizes(n_units, world)
+    m = max(sizes)
+    pad = local
+    if local.shape[0] < m:
+        pad = torch.cat([local, local.new_zeros((m - local.shape[0],) + tuple(local.shape[1:]))], dim=0)
+    out = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(out, pad.contiguous(), group=group)
+    return torch.cat([o[:s] for o, s in zip(out, sizes)], dim=0)
+
+
+def _angle_offset(frame, jitter):
+    return float(np.float32(np.float32(ANGLE_TABLE[frame % 12]) / np.float32(360.0)) + np.float32(jitter))
+
+
+def view_params(dp, frame, counter, jitter=0.0):
+    """Per-view parameter blocks of the GTAO + SSR passes from DrawTAAParams (src/main.cpp:366-373 and the pass .cpp files)."""
+    inv_cam, inv_prev = vkr.mat_inverse(dp.camera), vkr.mat_inverse(dp.prev_camera)
+    normal_mat = vkr.mat_transpose(inv_cam)
+    fovy, aspect, zn, zf = list(dp.fovy_aspect_znear_zfar)
+    tr = vkr.TraceParams(); C.memmove(tr.normal_mat, normal_mat, 64)
+    tr.frame_random, tr.fovy, tr.aspect, tr.znear, tr.zfar, tr.max_roughness, tr.render_flags = counter, fovy, aspect, zn, zf, 1.0, 7
+    bl = vkr.BlurParams(); C.memmove(bl.inverse_camera, inv_cam, 64); C.memmove(bl.prev_inverse_camera, inv_prev, 64)
+    bl.fovy_aspect_znear_zfar[:] = [fovy, aspect, zn, zf]; bl.max_roughness, bl.accumulate, bl.disable_blur = 1.0, 1, 0
+    gt = vkr.GtaoParams(); C.memmove(gt.normal_mat, normal_mat, 64)
+    gt.fovy, gt.aspect, gt.znear, gt.zfar = fovy, aspect, zn, zf
+    gt.angle_offset, gt.weight_ratio, gt.use_mis, gt.two_directions, gt.reflections_only = _angle_offset(frame, jitter), 1.0, 1, 0, 0
+    ac = vkr.AccumParams(); C.memmove(ac.inverse_camera, inv_cam, 64); C.memmove(ac.prev_inverse_camera, inv_prev, 64); C.memmove(ac.mvp, dp.mvp, 64)
+    ac.fovy_aspect_znear_zfar[:] = [fovy, aspect, zn, zf]; ac.clear_history = 0
+    return dict(trace=tr, blur=bl, gtao=gt, accum=ac)
+
+
+class ViewBatch:
+    """`views` independent w x h views on one device: images as arrays, passes batched over grid.z."""
+
+    def __init__(self, w, h, view_ids, device="cuda", luts=None, lut_size=1024, stream=None):
+        self.w, self.h, self.view_ids, self.V = w, h, list(view_ids), len(view_ids)
+        self.device, self.stream = torch.device(device), stream
+        V, w2, h2 = self.V, w // 2, h // 2
+        mips = vkr.full_mip_count(w, h)
+        A = lambda ww, hh, f, m=1: vkr.ImageArray(ww, hh, f, m, V, device=device)  # noqa: E731
+        self.albedo, self.normal, self.material = A(w, h, vkr.R8G8B8A8_SRGB), A(w, h, vkr.R16G16_UNORM), A(w, h, vkr.R8G8B8A8_SRGB)
+        self.velocity = A(w, h, vkr.R16G16_SFLOAT)
+        self.depth, self.prev_depth = A(w, h, vkr.D24_UNORM_S8_UINT, mips), A(w, h, vkr.D24_UNORM_S8_UINT, mips)
+        self.prev_depth.buf.view(torch.int32).fill_(0x00FFFFFF)           # clear_depth(prev_depth, 1.0), src/main.cpp:306
+        self.dn, self.dv = A(w2, h2, vkr.R16G16_UNORM), A(w2, h2, vkr.R16G16_SFLOAT)
+        self.raw, self.filtered = A(w2, h2, vkr.R16G16B16A16_SFLOAT), A(w2, h2, vkr.R16_SFLOAT)
+        self.accumulated_ao, self.accumulated_history = A(w2, h2, vkr.R16G16_SFLOAT), A(w2, h2, vkr.R16G16_SFLOAT)
+        self.rays = A(w2, h2, vkr.R16G16B16A16_UNORM)
+        self.reflections, self.blurred, self.blurred_history = A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM)
+        self.halton = torch.from_numpy(vkr.halton23_seq(128)).to(device)
+        if luts is None:
+            self.pdf = vkr.Image(lut_size, lut_size, vkr.R32_SFLOAT, device=device)
+            vkr.pdf_preintegrate(self.pdf, stream=stream)
+        else:
+            self.pdf = luts
+        self.scratch = torch.zeros(max(V, 1) * vkr.PARAMS_SCRATCH_STRIDE * 7, dtype=torch.uint8, device=device)   # one slice per pass
+        self.counter, self.frame = 0, 0
+        self.scenes = [vkr.synth_scene(v, 64) for v in self.view_ids]
+
+    def _scratch(self, i):
+        n = self.V * vkr.PARAMS_SCRATCH_STRIDE
+        return self.scratch[i * n:(i + 1) * n]
+
+    def synth_inputs(self, frame=None):
+        """Produce every view's G-buffer for `frame` on the device (the path's INPUT; not part of the timed chain)."""
+        f = self.frame if frame is None else frame
+        for i, v in enumerate(self.view_ids):
+            dp = vkr.synth_camera(v, f, self.w, self.h, True)
+            a = (self.albedo.layer(i).ptr, self.normal.layer(i).ptr, self.material.layer(i).ptr, self.velocity.layer(i).ptr, self.depth.layer(i).ptr)
+            vkr.check(vkr.lib.vkr_synth_gbuffer(C.byref(self.scenes[i]), C.byref(dp), *a, vkr.stream_ptr(self.stream)))
+
+    def params(self, jitters=None):
+        ps = []
+        for i, v in enumerate(self.view_ids):
+            dp = vkr.synth_camera(v, self.frame, self.w, self.h, True)
+            ps.append(view_params(dp, self.frame, self.counter, 0.0 if jitters is None else jitters[i]))
+        return {k: vkr.params_array(type(ps[0][k]), [p[k] for p in ps]) for k in ps[0]}
+
+    def passes(self, P):
+        """Hi-Z, SSSR trace/filter/blur, GTAO main/filter/accumulate for every view: 8 launches in total."""
+        V, st = self.V, self.stream
+        ext = lambda imgs, slot: vkr.make_ext(imgs, layers=V, scratch=self._scratch(slot))  # noqa: E731
+        vkr.hiz_build_ex(self.depth, self.normal, self.velocity, self.dn, self.dv, ext([self.depth, self.normal, self.velocity, self.dn, self.dv], 0), st)
+        vkr.sssr_trace_ex(P["trace"], self.depth, self.dn, self.material, self.halton, self.pdf, self.rays, self.raw,
+                          ext([self.depth, self.dn, self.material, self.pdf, self.rays, self.raw], 1), st)
+        vkr.sssr_filter_ex(P["trace"], self.rays, self.depth, self.albedo, self.normal, self.material, self.reflections,
+                           ext([self.rays, self.depth, self.albedo, self.normal, self.material, self.reflections], 2), st)
+        vkr.sssr_blur_ex(P["blur"], self.depth, self.normal, self.reflections, self.material, self.blurred_history, self.dv, self.prev_depth, self.blurred,
+                         ext([self.depth, self.normal, self.reflections, self.material, self.blurred_history, self.dv, self.prev_depth, self.blurred], 3), st)
+        vkr.gtao_main_ex(P["gtao"], self.depth, self.normal, self.material, self.pdf, self.raw,
+                         ext([self.depth, self.normal, self.material, self.pdf, self.raw], 4), 1, st)
+        vkr.gtao_filter_ex(P["gtao"], self.depth, self.raw, self.filtered, ext([self.depth, self.raw, self.filtered], 5), 1, st)
+        vkr.gtao_accumulate_ex(P["accum"], self.depth, self.prev_depth, self.filtered, self.accumulated_ao, self.dv, self.accumulated_history,
+                               ext([self.depth, self.prev_depth, self.filtered, self.accumulated_ao, self.dv, self.accumulated_history], 6), 1, st)
+
+    def end_frame(self):
+        """The remaps of src/main.cpp:416-420 that concern these passes."""
+        self.depth, self.prev_depth = self.prev_depth, self.depth
+        self.blurred, self.blurred_history = self.blurred_history, self.blurred
+        self.accumulated_ao, self.accumulated_history = self.accumulated_history, self.accumulated_ao
+        self.counter = (self.counter + 1) % 16
+        self.frame += 1
+
+    def outputs(self):
+        """(V, bytes) uint8 tensors of the two per-view results (accumulated AO, blurred reflections) for the gather."""
+        def rows(a):
+            return a.buf.view(a.layers, a.layer_stride)[:, :a.nbytes]
+        return rows(self.accumulated_ao), rows(self.blurred)
+
+    KERNELS_PER_FRAME = 9   # hiz tile + tail, trace, filter, blur, gtao main/filter/accumulate
