@@ -33,6 +33,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=3840)
     ap.add_argument("--height", type=int, default=2160)
+    ap.add_argument("--workload", default="chain", choices=["chain", "probes"],
+                    help="chain: full chain on the 3840x2160 TAA sequence (BASELINE configs[2], the headline); "
+                         "probes: 512 independent 256x256 views, Hi-Z+GTAO+SSR, sharded over the ranks (configs[3])")
+    ap.add_argument("--views", type=int, default=512)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -254,11 +258,109 @@ def run_ours(args, rank, world):
     print(json.dumps(line))
 
 
+def run_probes(args, rank, world):
+    """BASELINE configs[3]: args.views independent 256x256 views (Hi-Z + SSR trace/filter/blur + GTAO main/filter/accumulate),
+    contiguous blocks of views per rank, every pass ONE launch per rank (layers on grid.z), outputs all-gathered per frame on a
+    side stream (the only collective; it overlaps the next frame).  Strong scaling: the batch is fixed, ranks split it."""
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import vkr
+    import vkr_views
+    w = h = 256
+    K, W = args.steps, args.warmup
+    b, e = vkr_views.shard_range(args.views, world, rank)
+    stream, side = torch.cuda.Stream(), torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        vb = vkr_views.ViewBatch(w, h, list(range(b, e)), device=f"cuda:{local}", stream=stream)
+        nres = 4                                            # resident input frames (cycled); > L2 in total
+        frames = []
+        for f in range(nres):
+            vb.frame = f
+            vb.synth_inputs()
+            frames.append((vb.albedo, vb.normal, vb.material, vb.velocity, vb.depth))
+            A = lambda ww, hh, fmt, m=1: vkr.ImageArray(ww, hh, fmt, m, vb.V, device=f"cuda:{local}")  # noqa: E731
+            vb.albedo, vb.normal, vb.material = A(w, h, vkr.R8G8B8A8_SRGB), A(w, h, vkr.R16G16_UNORM), A(w, h, vkr.R8G8B8A8_SRGB)
+            vb.velocity, vb.depth = A(w, h, vkr.R16G16_SFLOAT), A(w, h, vkr.D24_UNORM_S8_UINT, vkr.full_mip_count(w, h))
+        params = []
+        for f in range(nres):
+            vb.frame, vb.counter = f, f % 16
+            params.append(vb.params())
+        vb.frame = vb.counter = 0
+    stream.synchronize()
+    done = torch.cuda.Event()
+    gathered = []
+
+    def step(i):
+        f = i % nres
+        vb.albedo, vb.normal, vb.material, vb.velocity, vb.depth = frames[f]
+        vb.prev_depth = frames[(f - 1) % nres][4] if i > 0 else vb.prev_depth     # last frame's depth with its pyramid (main.cpp:416)
+        vb.passes(params[f])
+        ao, refl = vb.outputs()
+        if world > 1:                                        # final gather of the per-view results, off the compute stream
+            done.record(stream)
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                gathered[:] = [vkr_views.gather_blocks(ao, args.views), vkr_views.gather_blocks(refl, args.views)]
+        vb.blurred, vb.blurred_history = vb.blurred_history, vb.blurred
+        vb.accumulated_ao, vb.accumulated_history = vb.accumulated_history, vb.accumulated_ao
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    with torch.cuda.stream(stream):
+        for i in range(W):
+            step(i)
+        barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(W, W + K):
+            step(i)
+        stream.wait_stream(side)
+        e1.record(stream)
+        stream.synchronize()
+        sampler.stop_flag = True
+        barrier()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    sampler.join(timeout=1.0)
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    npix = args.views * w * h
+    alg = 73.0 * npix                                        # Hi-Z + SSR + GTAO subset of the chain, SURVEY §8d
+    line = {"metric": "probe_batch_throughput", "value": npix * K / (ms * 1e-3) / 1e9, "unit": "Gpix/s", "views_per_s": args.views * K / (ms * 1e-3),
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.views} probe views 256x256, Hi-Z+GTAO+SSR, contiguous view blocks per rank (BASELINE configs[3])",
+                       "frames_resident": nres, "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
+                       "parallelism": f"views sharded over {world} rank(s); all_gather of AO + reflections per frame on a side stream"},
+            "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
+            "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+    print(json.dumps(line))
+
+
 def main():
     args = parse()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.workload == "probes":
+        run_probes(args, rank, world)
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
     else:
         run_ours(args, rank, world)
         if world > 1:
