@@ -274,9 +274,10 @@ def run_probes(args, rank, world):
     K, W = args.steps, args.warmup
     b, e = vkr_views.shard_range(args.views, world, rank)
     stream, side = torch.cuda.Stream(), torch.cuda.Stream()
+    assert e - b > 1, "the batched path needs at least 2 views per rank"
+    nres = 4                                                # resident input frames (cycled); > L2 in total
     with torch.cuda.stream(stream):
-        vb = vkr_views.ViewBatch(w, h, list(range(b, e)), device=f"cuda:{local}", stream=stream)
-        nres = 4                                            # resident input frames (cycled); > L2 in total
+        vb = vkr_views.ViewBatch(w, h, list(range(b, e)), device=f"cuda:{local}", stream=stream, param_sets=nres)
         frames = []
         for f in range(nres):
             vb.frame = f
@@ -289,30 +290,61 @@ def run_probes(args, rank, world):
         for f in range(nres):
             vb.frame, vb.counter = f, f % 16
             params.append(vb.params())
+            vb.albedo, vb.normal, vb.material, vb.velocity, vb.depth = frames[f]
+            vb.passes(params[f], flags=vkr.EXT_PREPARE_ONLY, param_set=f)       # per-view parameter blocks uploaded once
         vb.frame = vb.counter = 0
     stream.synchronize()
     done = torch.cuda.Event()
-    gathered = []
+    graphs, outs = {}, {}
+    ao0, refl0 = vb.outputs()
+    eq = len(set(vkr_views.shard_sizes(args.views, world))) == 1
+    gout = [torch.empty((args.views, t.shape[1]), dtype=torch.uint8, device=t.device) if (world > 1 and eq) else None for t in (ao0, refl0)]
 
-    def step(i):
+    def bind(i):
         f = i % nres
         vb.albedo, vb.normal, vb.material, vb.velocity, vb.depth = frames[f]
-        vb.prev_depth = frames[(f - 1) % nres][4] if i > 0 else vb.prev_depth     # last frame's depth with its pyramid (main.cpp:416)
-        vb.passes(params[f])
-        ao, refl = vb.outputs()
+        if i > 0:
+            vb.prev_depth = frames[(f - 1) % nres][4]        # last frame's depth with its pyramid (main.cpp:416)
+        return f
+
+    def swap():
+        vb.blurred, vb.blurred_history = vb.blurred_history, vb.blurred
+        vb.accumulated_ao, vb.accumulated_history = vb.accumulated_history, vb.accumulated_ao
+
+    def gather(ao, refl):
         if world > 1:                                        # final gather of the per-view results, off the compute stream
             done.record(stream)
             side.wait_event(done)
             with torch.cuda.stream(side):
-                gathered[:] = [vkr_views.gather_blocks(ao, args.views), vkr_views.gather_blocks(refl, args.views)]
-        vb.blurred, vb.blurred_history = vb.blurred_history, vb.blurred
-        vb.accumulated_ao, vb.accumulated_history = vb.accumulated_history, vb.accumulated_ao
+                vkr_views.gather_blocks(ao, args.views, out=gout[0])
+                vkr_views.gather_blocks(refl, args.views, out=gout[1])
+
+    def step(i):
+        """Steps 0..nres-1 run eagerly, steps nres..2*nres-1 are captured into one CUDA graph each (the image bindings repeat
+        with period nres, nres even), later steps replay: 9 kernel launches per frame with no host work between them."""
+        f = i % nres
+        if i >= 2 * nres:
+            graphs[f].replay()
+            gather(*outs[f])
+            return
+        bind(i)
+        if i >= nres:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f)
+            graphs[f], outs[f] = g, vb.outputs()
+            g.replay()
+        else:
+            vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f)
+        gather(*vb.outputs())
+        swap()
 
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
 
+    W = max(W, 2 * nres)                                     # eager + capture steps are warm-up
     with torch.cuda.stream(stream):
         for i in range(W):
             step(i)
@@ -343,7 +375,7 @@ def run_probes(args, rank, world):
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.views} probe views 256x256, Hi-Z+GTAO+SSR, contiguous view blocks per rank (BASELINE configs[3])",
-                       "frames_resident": nres, "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
+                       "frames_resident": nres, "launch": "one CUDA graph of 9 kernels per frame, parameter blocks prepared once", "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
                        "parallelism": f"views sharded over {world} rank(s); all_gather of AO + reflections per frame on a side stream"},
             "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},

@@ -140,13 +140,20 @@ typedef struct VkrTaaParams {
  *    (0,0 = all).  Both must be multiples of VKR_ROW_ALIGN unless row_end is the image height.
  *    Used to split one very large frame into row tiles across GPUs; the caller supplies whatever
  *    rows of the inputs the pass reads beyond its window (halo exchange).  No reference counterpart
- *    (BASELINE.json configs[4]).  vkr_hiz_build_ex rejects row windows (the pyramid is built whole). */
+ *    (BASELINE.json configs[4]).  vkr_hiz_build_ex rejects row windows (the pyramid is built whole).
+ *  - flags (layers > 1 only): VKR_EXT_PREPARE_ONLY converts and uploads the params blocks into params_scratch and
+ *    returns without launching; VKR_EXT_PARAMS_PREPARED launches with the blocks an earlier call of the SAME entry
+ *    left in params_scratch (no host conversion, no copy: the call is then pure kernel launches and can be captured
+ *    into a CUDA graph). */
 #define VKR_ROW_ALIGN 16
 #define VKR_PARAMS_SCRATCH_STRIDE 256
 #define VKR_MAX_IMAGE_ARGS 10
+#define VKR_EXT_PREPARE_ONLY 1u
+#define VKR_EXT_PARAMS_PREPARED 2u
 typedef struct VkrLaunchExt {
   uint32_t layers;
   uint32_t row_begin, row_end;
+  uint32_t flags;
   uint64_t layer_stride[VKR_MAX_IMAGE_ARGS];
   void* params_scratch;
 } VkrLaunchExt;

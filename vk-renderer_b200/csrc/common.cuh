@@ -54,6 +54,8 @@ struct ExtInfo {
   const VkrLaunchExt* e = nullptr;
   uint64_t stride(int i) const { return (e && e->layers > 1) ? e->layer_stride[i] : 0; }
   void* scratch() const { return e ? e->params_scratch : nullptr; }
+  bool prepared() const { return e && (e->flags & VKR_EXT_PARAMS_PREPARED); }
+  bool prepare_only() const { return e && (e->flags & VKR_EXT_PREPARE_ONLY); }
 };
 // Validates ext against a pass whose output has out_h rows processed in tiles of tile_h rows.
 int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what);

@@ -266,10 +266,13 @@ extern "C" int vkr_gtao_main_ex(const VkrGtaoParams* p, const VkrImage* depth, c
   cudaStream_t st = (cudaStream_t)stream;
   const GtaoK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<GtaoK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_gtao_k(p + i, raw);
-    if ((rc = upload_params(ks.data(), sizeof(GtaoK), x.layers, x.scratch(), st, "gtao_main"))) return rc;
+    if (!x.prepared()) {
+      std::vector<GtaoK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_gtao_k(p + i, raw);
+      if ((rc = upload_params(ks.data(), sizeof(GtaoK), x.layers, x.scratch(), st, "gtao_main"))) return rc;
+    }
     kv = (const GtaoK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((k.tw + 31) / 32, x.yblocks, x.layers);
   auto kern = kv ? gtao_main_kernel<true> : gtao_main_kernel<false>;
@@ -297,6 +300,7 @@ extern "C" int vkr_gtao_filter_ex(const VkrGtaoParams* p, const VkrImage* depth,
   if (rc) return rc;
   for (int i = 1; i < x.layers; i++)
     if (p[i].znear != p[0].znear || p[i].zfar != p[0].zfar) { set_error("gtao_filter: layers must share znear/zfar"); return VKR_ERR_UNSUPPORTED; }
+  if (x.prepare_only()) return VKR_OK;
   dim3 grid((tw + 31) / 32, x.yblocks, x.layers);
   gtao_filter_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(LaunchX{x.yb0}, make_mip(depth, depth_lod, x, 0), make_mip(raw, 0, x, 1), make_mip(filtered, 0, x, 2), tw, th,
                                                              p->znear, p->zfar);
@@ -336,10 +340,13 @@ extern "C" int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* d
   AccumK k = make_accum_k(p);
   const AccumK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<AccumK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_accum_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(AccumK), x.layers, x.scratch(), st, "gtao_accumulate"))) return rc;
+    if (!x.prepared()) {
+      std::vector<AccumK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_accum_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(AccumK), x.layers, x.scratch(), st, "gtao_accumulate"))) return rc;
+    }
     kv = (const AccumK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((accumulated->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(accumulated->width, accumulated->height);

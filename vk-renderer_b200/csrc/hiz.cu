@@ -237,6 +237,7 @@ extern "C" int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, c
   VkrLaunchExt e2;
   if (ext) { e2 = *ext; if (e2.layers > 1 && !e2.params_scratch) e2.params_scratch = (void*)depth->base; }   // no params: scratch unused
   if ((rc = resolve_ext(ext ? &e2 : nullptr, depth->height, 16, &x, "hiz_build"))) return rc;
+  if (x.prepare_only()) return VKR_OK;
   return hiz_run(depth, 0, normal, velocity, out_normal, out_velocity, 0, (cudaStream_t)stream, x);
 }
 

@@ -199,10 +199,13 @@ extern "C" int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage
   ShadeK k = make_shade_k(p);
   const ShadeK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<ShadeK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_shade_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(ShadeK), x.layers, x.scratch(), st, "deferred_shading"))) return rc;
+    if (!x.prepared()) {
+      std::vector<ShadeK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_shade_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(ShadeK), x.layers, x.scratch(), st, "deferred_shading"))) return rc;
+    }
     kv = (const ShadeK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_color->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(out_color->width, out_color->height);

@@ -214,10 +214,13 @@ extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, c
   BlurK k = make_blur_k(p);
   const BlurK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<BlurK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_blur_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(BlurK), x.layers, x.scratch(), st, "sssr_blur"))) return rc;
+    if (!x.prepared()) {
+      std::vector<BlurK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_blur_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(BlurK), x.layers, x.scratch(), st, "sssr_blur"))) return rc;
+    }
     kv = (const BlurK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_blurred->width + BLUR_TILE - 1) / BLUR_TILE, x.yblocks, x.layers);
   const bool same = same_extent(dvelocity, out_blurred) && out_blurred->width <= 8192 && out_blurred->height <= 8192;

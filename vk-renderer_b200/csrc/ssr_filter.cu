@@ -158,10 +158,13 @@ extern "C" int vkr_sssr_filter_ex(const VkrTraceParams* p, const VkrImage* rays,
   FilterK k = make_filter_k(p);
   const FilterK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<FilterK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_filter_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(FilterK), x.layers, x.scratch(), st, "sssr_filter"))) return rc;
+    if (!x.prepared()) {
+      std::vector<FilterK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_filter_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(FilterK), x.layers, x.scratch(), st, "sssr_filter"))) return rc;
+    }
     kv = (const FilterK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_reflections->width + FT_W - 1) / FT_W, x.yblocks, x.layers);
   auto kern = kv ? sssr_filter_kernel<true> : sssr_filter_kernel<false>;

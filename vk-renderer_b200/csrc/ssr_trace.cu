@@ -216,10 +216,13 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
   TraceK k = make_trace_k(p);
   const TraceK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<TraceK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_trace_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(TraceK), x.layers, x.scratch(), st, "sssr_trace"))) return rc;
+    if (!x.prepared()) {
+      std::vector<TraceK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_trace_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(TraceK), x.layers, x.scratch(), st, "sssr_trace"))) return rc;
+    }
     kv = (const TraceK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   PyramidView P;
   P.count = (int)depth->mip_count - 1;

@@ -140,10 +140,13 @@ extern "C" int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history
   TaaK k = make_taa_k(p);
   const TaaK* kv = nullptr;
   if (x.layers > 1) {
-    std::vector<TaaK> ks(x.layers);
-    for (int i = 0; i < x.layers; i++) ks[i] = make_taa_k(p + i);
-    if ((rc = upload_params(ks.data(), sizeof(TaaK), x.layers, x.scratch(), st, "taa_resolve"))) return rc;
+    if (!x.prepared()) {
+      std::vector<TaaK> ks(x.layers);
+      for (int i = 0; i < x.layers; i++) ks[i] = make_taa_k(p + i);
+      if ((rc = upload_params(ks.data(), sizeof(TaaK), x.layers, x.scratch(), st, "taa_resolve"))) return rc;
+    }
     kv = (const TaaK*)x.scratch();
+    if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_target->width + 31) / 32, x.yblocks, x.layers);
   const Dim dim = make_dim(out_target->width, out_target->height);

@@ -346,7 +346,7 @@ def taa_resolve(p, history, prev_depth, depth, velocity, color, out, stream=None
 
 # ---- extended launches: array layers and row windows (include/vkr_passes.h VkrLaunchExt) ---------------
 class LaunchExt(C.Structure):
-    _fields_ = [("layers", C.c_uint32), ("row_begin", C.c_uint32), ("row_end", C.c_uint32), ("layer_stride", C.c_uint64 * 10),
+    _fields_ = [("layers", C.c_uint32), ("row_begin", C.c_uint32), ("row_end", C.c_uint32), ("flags", C.c_uint32), ("layer_stride", C.c_uint64 * 10),
                 ("params_scratch", C.c_void_p)]
 
 
@@ -395,10 +395,14 @@ class ImageArray:
         return im
 
 
-def make_ext(images, layers=1, rows=None, scratch=None):
+EXT_PREPARE_ONLY, EXT_PARAMS_PREPARED = 1, 2
+
+
+def make_ext(images, layers=1, rows=None, scratch=None, flags=0):
     """VkrLaunchExt for a call whose VkrImage arguments are `images` (ImageArray or Image, in argument order)."""
     e = LaunchExt()
     e.layers = layers
+    e.flags = flags
     if rows is not None:
         e.row_begin, e.row_end = rows
     for i, im in enumerate(images):

@@ -30,16 +30,21 @@ def shard_sizes(n_units, world):
     return [shard_range(n_units, world, r)[1] - shard_range(n_units, world, r)[0] for r in range(world)]
 
 
-def gather_blocks(local, n_units, group=None):
+def gather_blocks(local, n_units, group=None, out=None):
     """All-gather per-rank blocks of shape (units_r, ...) into (n_units, ...) on every rank (ragged blocks are padded
     to the largest one for the collective and trimmed afterwards).  Works on CUDA tensors over NCCL and CPU tensors
-    over gloo."""
+    over gloo.  Equal blocks go through ONE all_gather_into_tensor straight into `out` (preallocated (n_units, ...))."""
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     if world == 1:
         return local
     sizes = shard_sizes(n_units, world)
     m = max(sizes)
+    if min(sizes) == m and local.is_contiguous():
+        if out is None:
+            out = local.new_empty((n_units,) + tuple(local.shape[1:]))
+        dist.all_gather_into_tensor(out, local, group=group)
+        return out
     pad = local
     if local.shape[0] < m:
         pad = torch.cat([local, local.new_zeros((m - local.shape[0],) + tuple(local.shape[1:]))], dim=0)
@@ -72,7 +77,7 @@ def view_params(dp, frame, counter, jitter=0.0):
 class ViewBatch:
     """`views` independent w x h views on one device: images as arrays, passes batched over grid.z."""
 
-    def __init__(self, w, h, view_ids, device="cuda", luts=None, lut_size=1024, stream=None):
+    def __init__(self, w, h, view_ids, device="cuda", luts=None, lut_size=1024, stream=None, param_sets=1):
         self.w, self.h, self.view_ids, self.V = w, h, list(view_ids), len(view_ids)
         self.device, self.stream = torch.device(device), stream
         V, w2, h2 = self.V, w // 2, h // 2
@@ -93,7 +98,8 @@ class ViewBatch:
             vkr.pdf_preintegrate(self.pdf, stream=stream)
         else:
             self.pdf = luts
-        self.scratch = torch.zeros(max(V, 1) * vkr.PARAMS_SCRATCH_STRIDE * 7, dtype=torch.uint8, device=device)   # one slice per pass
+        # one slice of device scratch per (parameter set, pass): a set prepared once can be replayed without host work
+        self.scratch = torch.zeros(max(V, 1) * vkr.PARAMS_SCRATCH_STRIDE * 7 * param_sets, dtype=torch.uint8, device=device)
         self.counter, self.frame = 0, 0
         self.scenes = [vkr.synth_scene(v, 64) for v in self.view_ids]
 
@@ -116,10 +122,12 @@ class ViewBatch:
             ps.append(view_params(dp, self.frame, self.counter, 0.0 if jitters is None else jitters[i]))
         return {k: vkr.params_array(type(ps[0][k]), [p[k] for p in ps]) for k in ps[0]}
 
-    def passes(self, P):
-        """Hi-Z, SSSR trace/filter/blur, GTAO main/filter/accumulate for every view: 8 launches in total."""
+    def passes(self, P, flags=0, param_set=0):
+        """Hi-Z, SSSR trace/filter/blur, GTAO main/filter/accumulate for every view: 8 launches in total.
+        flags: vkr.EXT_PREPARE_ONLY uploads the per-view parameter blocks of `param_set` without launching,
+        vkr.EXT_PARAMS_PREPARED launches on blocks prepared earlier (pure kernel launches: CUDA-graph capturable)."""
         V, st = self.V, self.stream
-        ext = lambda imgs, slot: vkr.make_ext(imgs, layers=V, scratch=self._scratch(slot))  # noqa: E731
+        ext = lambda imgs, slot: vkr.make_ext(imgs, layers=V, scratch=self._scratch(param_set * 7 + slot), flags=flags if V > 1 else 0)  # noqa: E731
         vkr.hiz_build_ex(self.depth, self.normal, self.velocity, self.dn, self.dv, ext([self.depth, self.normal, self.velocity, self.dn, self.dv], 0), st)
         vkr.sssr_trace_ex(P["trace"], self.depth, self.dn, self.material, self.halton, self.pdf, self.rays, self.raw,
                           ext([self.depth, self.dn, self.material, self.pdf, self.rays, self.raw], 1), st)
