@@ -33,9 +33,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--width", type=int, default=3840)
     ap.add_argument("--height", type=int, default=2160)
-    ap.add_argument("--workload", default="chain", choices=["chain", "probes"],
+    ap.add_argument("--workload", default="chain", choices=["chain", "probes", "tiles"],
                     help="chain: full chain on the 3840x2160 TAA sequence (BASELINE configs[2], the headline); "
-                         "probes: 512 independent 256x256 views, Hi-Z+GTAO+SSR, sharded over the ranks (configs[3])")
+                         "probes: 512 independent 256x256 views, Hi-Z+GTAO+SSR, sharded over the ranks (configs[3]); "
+                         "tiles: ONE 7680x4320 frame sequence split into row tiles, halo rows over NVLink peer memory (configs[4])")
     ap.add_argument("--views", type=int, default=512)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -383,13 +384,122 @@ def run_probes(args, rank, world):
     print(json.dumps(line))
 
 
+def run_tiles(args, rank, world):
+    """BASELINE configs[4]: one 7680x4320 sequence, full chain, rows split over the ranks (vkr_tiles.RowTiledFrame): inputs and
+    Hi-Z replicated, six halo exchanges per frame as direct peer stores + stream-side flags, the finished TAA rows sent to rank 0
+    (NCCL send/recv on a side stream: the final gather).  Strong scaling."""
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import vkr
+    import vkr_tiles
+    w, h = (7680, 4320) if args.width == 3840 else (args.width, args.height)
+    K, W = args.steps, args.warmup
+    stream, side = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def allgather_bytes(b):
+        if world == 1:
+            return [b]
+        out = [None] * world
+        dist.all_gather_object(out, b)
+        return out
+
+    nres = 3
+    with torch.cuda.stream(stream):
+        tf = vkr_tiles.RowTiledFrame(w, h, rank, world, allgather_bytes, device=f"cuda:{local}", motion_rows=16, stream=stream)
+        scene = vkr.synth_scene(0, 64)
+        dps = [vkr.synth_camera(0, f, w, h, True) for f in range(nres)]
+        G = []
+        for f in range(nres):
+            gb = vkr.Gbuffer(w, h, device=f"cuda:{local}")
+            vkr.synth_gbuffer(scene, dps[f], gb, stream=stream)
+            G.append(gb)
+        D = [g.depth for g in G]
+        cleared = tf.gb.prev_depth
+    stream.synchronize()
+    jit = [float(((f * 2654435761) % 1000) / 1000.0 - 0.5) for f in range(nres)]
+    y0, y1 = tf.own_rows(True)
+    spans = [None] * world
+    if world > 1:
+        dist.all_gather_object(spans, (y0, y1))
+    done = torch.cuda.Event()
+
+    def rows_of(img, r0, r1):
+        pitch = img.desc.row_pitch[0]
+        return img.buf[r0 * pitch:r1 * pitch]
+
+    def step(i):
+        f = i % nres
+        gb = G[f]
+        gb.prev_depth = D[(f - 1) % nres] if i > 0 else cleared
+        tf.gb = gb
+        out = tf.render_frame(dps[f], jit[f], swap_depth=False)
+        if world > 1:                                        # final gather: finished rows to rank 0, off the compute stream
+            done.record(stream)
+            side.wait_event(done)
+            with torch.cuda.stream(side):
+                if rank == 0:
+                    for r in range(1, world):
+                        dist.recv(rows_of(out, *spans[r]), src=r)
+                else:
+                    dist.send(rows_of(out, y0, y1), dst=0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    with torch.cuda.stream(stream):
+        for i in range(W):
+            step(i)
+        barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(W, W + K):
+            step(i)
+        stream.wait_stream(side)
+        e1.record(stream)
+        stream.synchronize()
+        sampler.stop_flag = True
+        barrier()
+    ms = e0.elapsed_time(e1)
+    fails = tf.wait_failures()
+    if world > 1:
+        t = torch.tensor([ms, float(fails)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, fails = float(t[0].item()), int(t[1].item())
+    sampler.join(timeout=1.0)
+    tf.close()
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    npix = w * h
+    alg = 128.0 * npix
+    line = {"metric": "tiled_frame_throughput", "value": npix * K / (ms * 1e-3) / 1e9, "unit": "Gpix/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"full chain on ONE {w}x{h} sequence, row tiles over {world} rank(s) (BASELINE configs[4])", "frames_resident": nres,
+                       "l2": "inputs larger than L2 (one 8K frame touches > 4 GB)",
+                       "parallelism": "rows split in 16-row strips; inputs + Hi-Z replicated; 6 halo exchanges per frame as peer stores over NVLink with "
+                                      "stream-side flags; finished TAA rows sent to rank 0 (NCCL send/recv, side stream)",
+                       "halo_rows": tf.halo, "wait_timeouts": fails},
+            "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
+            "gpu_launches": vkr_tiles.RowTiledFrame.KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+    print(json.dumps(line))
+
+
 def main():
     args = parse()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     if args.impl == "reference":
         run_reference(args, rank, world)
-    elif args.workload == "probes":
-        run_probes(args, rank, world)
+    elif args.workload in ("probes", "tiles"):
+        (run_probes if args.workload == "probes" else run_tiles)(args, rank, world)
         if world > 1:
             import torch.distributed as dist
             dist.destroy_process_group()

@@ -1,0 +1,46 @@
+/* vkr_peer.h — peer-memory plumbing for row-tiled frames (BASELINE.json configs[4]: one very large frame split into
+ * row tiles across the GPUs of one box, halo rows exchanged over NVLink P2P).
+ *
+ * No reference counterpart: vk-renderer is single-GPU (src/gpu/driver.cpp:99 picks the first discrete device).  One
+ * process per GPU; every rank allocates the SAME slab layout with vkr_peer_alloc, exports it (cudaIpc), opens its
+ * neighbours' slabs and then writes halo rows straight into the neighbour's copy of an image (a peer store over
+ * NVLink, no staging, no collective).  Ordering between ranks is carried by 32-bit flags inside the slabs:
+ *   producer:  vkr_peer_push_rows(...) ; vkr_peer_signal(neighbour_flag, epoch)      (stream-ordered)
+ *   consumer:  vkr_peer_wait(my_flag, epoch)  ; <kernel that reads the halo>          (stream-ordered)
+ * Nothing here synchronises the host.  All calls return 0 / negative VkrStatus (vkr_last_error() has the text).
+ */
+#ifndef VKR_PEER_H_INCLUDED
+#define VKR_PEER_H_INCLUDED
+#include "vkr_passes.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct VkrIpcHandle { unsigned char bytes[64]; } VkrIpcHandle;
+
+/* Device allocation that can be exported to other processes (zero-initialised). */
+int vkr_peer_alloc(uint64_t bytes, void** dptr);
+int vkr_peer_free(void* dptr);
+int vkr_peer_export(void* dptr, VkrIpcHandle* out);
+/* Maps another process's exported allocation into this process (peer access over NVLink when on another GPU). */
+int vkr_peer_open(const VkrIpcHandle* handle, void** peer_ptr);
+int vkr_peer_close(void* peer_ptr);
+
+/* Copies rows [row_begin, row_end) of mip `lod` of the local image `img` into the same rows of the peer's copy of that
+ * image.  `peer_image_base` is the address of the peer image's allocation base in THIS process (peer slab + the
+ * image's offset).  Rows are clamped to the mip's height; an empty range is a no-op.  Asynchronous on `stream`. */
+int vkr_peer_push_rows(const VkrImage* img, uint32_t lod, uint32_t row_begin, uint32_t row_end, void* peer_image_base, void* stream);
+
+/* After everything queued on `stream` so far: system-scope release store of `value` to *flag (usually peer memory). */
+int vkr_peer_signal(uint32_t* flag, uint32_t value, void* stream);
+/* Holds `stream` until *flag >= value (system-scope acquire loads from a one-thread kernel).  After timeout_ms without
+ * progress the kernel gives up and raises a sticky failure bit readable with vkr_peer_wait_failed() — it never hangs. */
+int vkr_peer_wait(const uint32_t* flag, uint32_t value, uint32_t timeout_ms, void* stream);
+/* Number of waits that timed out on the current device since the last call (resets the counter). Synchronises the device. */
+int vkr_peer_wait_failed(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

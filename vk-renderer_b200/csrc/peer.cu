@@ -1,0 +1,94 @@
+// peer.cu — IPC-mapped peer memory, halo-row pushes and stream-ordered flags for row-tiled frames (include/vkr_peer.h).
+#include "common.cuh"
+#include "../../include/vkr_peer.h"
+
+namespace vkr {
+
+__device__ unsigned int g_wait_failed = 0;
+
+__global__ void peer_signal_kernel(uint32_t* flag, uint32_t value) {
+  __threadfence_system();                                            // everything this stream wrote before is visible first
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+
+__global__ void peer_wait_kernel(const uint32_t* flag, uint32_t value, unsigned long long timeout_ns) {
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if ((int32_t)(v - value) >= 0) return;                           // epochs wrap
+    __nanosleep(200);
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) { atomicAdd(&g_wait_failed, 1u); return; }
+  }
+}
+
+static int cuda_rc(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return VKR_OK;
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return VKR_ERR_CUDA;
+}
+
+}  // namespace vkr
+using namespace vkr;
+
+extern "C" int vkr_peer_alloc(uint64_t bytes, void** dptr) {
+  if (!dptr || !bytes) { set_error("peer_alloc: bad arguments"); return VKR_ERR_INVALID_ARGUMENT; }
+  int rc = cuda_rc(cudaMalloc(dptr, bytes), "peer_alloc");
+  if (rc) return rc;
+  return cuda_rc(cudaMemset(*dptr, 0, bytes), "peer_alloc memset");
+}
+
+extern "C" int vkr_peer_free(void* dptr) { return cuda_rc(cudaFree(dptr), "peer_free"); }
+
+extern "C" int vkr_peer_export(void* dptr, VkrIpcHandle* out) {
+  static_assert(sizeof(cudaIpcMemHandle_t) <= sizeof(VkrIpcHandle), "handle size");
+  if (!dptr || !out) { set_error("peer_export: bad arguments"); return VKR_ERR_INVALID_ARGUMENT; }
+  cudaIpcMemHandle_t h;
+  int rc = cuda_rc(cudaIpcGetMemHandle(&h, dptr), "peer_export");
+  if (rc) return rc;
+  memset(out, 0, sizeof(*out));
+  memcpy(out->bytes, &h, sizeof(h));
+  return VKR_OK;
+}
+
+extern "C" int vkr_peer_open(const VkrIpcHandle* handle, void** peer_ptr) {
+  if (!handle || !peer_ptr) { set_error("peer_open: bad arguments"); return VKR_ERR_INVALID_ARGUMENT; }
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle->bytes, sizeof(h));
+  return cuda_rc(cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess), "peer_open");
+}
+
+extern "C" int vkr_peer_close(void* peer_ptr) { return cuda_rc(cudaIpcCloseMemHandle(peer_ptr), "peer_close"); }
+
+extern "C" int vkr_peer_push_rows(const VkrImage* img, uint32_t lod, uint32_t row_begin, uint32_t row_end, void* peer_image_base, void* stream) {
+  if (!img || !img->base || !peer_image_base || lod >= img->mip_count) { set_error("peer_push_rows: bad arguments"); return VKR_ERR_INVALID_ARGUMENT; }
+  const uint32_t h = (uint32_t)mip_dim(img->height, lod);
+  if (row_end > h) row_end = h;
+  if (row_begin >= row_end) return VKR_OK;
+  const size_t off = (size_t)img->mip_offset[lod] + (size_t)row_begin * img->row_pitch[lod];
+  const size_t bytes = (size_t)(row_end - row_begin) * img->row_pitch[lod];       // full-width rows are contiguous
+  return cuda_rc(cudaMemcpyAsync((unsigned char*)peer_image_base + off, (const unsigned char*)img->base + off, bytes, cudaMemcpyDefault, (cudaStream_t)stream),
+                 "peer_push_rows");
+}
+
+extern "C" int vkr_peer_signal(uint32_t* flag, uint32_t value, void* stream) {
+  if (!flag) { set_error("peer_signal: null flag"); return VKR_ERR_INVALID_ARGUMENT; }
+  peer_signal_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value);
+  return check_launch("peer_signal_kernel");
+}
+
+extern "C" int vkr_peer_wait(const uint32_t* flag, uint32_t value, uint32_t timeout_ms, void* stream) {
+  if (!flag) { set_error("peer_wait: null flag"); return VKR_ERR_INVALID_ARGUMENT; }
+  peer_wait_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value, (unsigned long long)timeout_ms * 1000000ull);
+  return check_launch("peer_wait_kernel");
+}
+
+extern "C" int vkr_peer_wait_failed(void) {
+  unsigned int h = 0, z = 0;
+  if (cudaMemcpyFromSymbol(&h, g_wait_failed, sizeof(h)) != cudaSuccess) return -1;
+  cudaMemcpyToSymbol(g_wait_failed, &z, sizeof(z));
+  return (int)h;
+}

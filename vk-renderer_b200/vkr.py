@@ -128,6 +128,24 @@ class Image:
         self.desc.base = self.buf.data_ptr()
         self.width, self.height, self.format, self.mips = width, height, fmt, mips
 
+    @classmethod
+    def over(cls, buf, width, height, fmt, mips=1):
+        """An Image laid out over the start of an existing uint8 tensor (e.g. a slice of a peer-exported slab)."""
+        im = cls.__new__(cls)
+        im.desc = VkrImage()
+        im.nbytes = int(lib.vkr_image_layout(width, height, fmt, mips, C.byref(im.desc)))
+        if im.nbytes == 0 or buf.numel() < im.nbytes:
+            raise VkrError("Image.over: bad layout or buffer too small")
+        im.device, im.buf = buf.device, buf[:im.nbytes]
+        im.desc.base = im.buf.data_ptr()
+        im.width, im.height, im.format, im.mips = width, height, fmt, mips
+        return im
+
+    @staticmethod
+    def layout_bytes(width, height, fmt, mips=1):
+        d = VkrImage()
+        return (int(lib.vkr_image_layout(width, height, fmt, mips, C.byref(d))) + 255) & ~255
+
     @property
     def ptr(self):
         return C.byref(self.desc)

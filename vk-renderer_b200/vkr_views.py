@@ -71,7 +71,13 @@ def view_params(dp, frame, counter, jitter=0.0):
     gt.angle_offset, gt.weight_ratio, gt.use_mis, gt.two_directions, gt.reflections_only = _angle_offset(frame, jitter), 1.0, 1, 0, 0
     ac = vkr.AccumParams(); C.memmove(ac.inverse_camera, inv_cam, 64); C.memmove(ac.prev_inverse_camera, inv_prev, 64); C.memmove(ac.mvp, dp.mvp, 64)
     ac.fovy_aspect_znear_zfar[:] = [fovy, aspect, zn, zf]; ac.clear_history = 0
-    return dict(trace=tr, blur=bl, gtao=gt, accum=ac)
+    ident = (C.c_float * 16)(*np.eye(4, dtype=np.float32).reshape(16))
+    sh = vkr.ShadingParams(); C.memmove(sh.inverse_camera, inv_cam, 64); C.memmove(sh.camera, dp.camera, 64); C.memmove(sh.shadow_mvp, ident, 64)
+    sh.fovy, sh.aspect, sh.znear, sh.zfar = fovy, aspect, zn, zf
+    sh.min_max_roughness[:] = [0.0, 1.0]; sh.show_ao = 0                      # defered_shading.hpp:30-31
+    ta = vkr.TaaParams(); C.memmove(ta.inverse_camera, inv_cam, 64); C.memmove(ta.prev_inverse_camera, inv_prev, 64)
+    ta.fovy_aspect_znear_zfar[:] = [fovy, aspect, zn, zf]
+    return dict(trace=tr, blur=bl, gtao=gt, accum=ac, shade=sh, taa=ta)
 
 
 class ViewBatch:
