@@ -35,7 +35,12 @@ __device__ __forceinline__ float srgb_encode_fast(float l) {       // linear -> 
 
 // SAME: albedo / normal / material have the output's extent, so their bilinear footprint at the pixel's own
 // centre is the texel itself (common.cuh tap_is_texel).
-template <bool SAME, bool LAYERED>
+// HALF: depth mip 1, the AO image and the reflections all have the extent (W/2, H/2) of the reference (W, H even).  The
+// 32x8 pixel tile then touches a 19x7 block of half-res texels; each is fetched and decoded once per CTA into shared memory
+// ({reflection rgb, AO} and the exact mip-1 depth) instead of ~17 times by the threads whose 3x3 / 2x2 footprints cover it.
+#define SH_HW 19
+#define SH_HH 7
+template <bool SAME, bool LAYERED, bool HALF>
 __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const ShadeK* __restrict__ kv, LaunchX lx, Dim dim, Mip albedo_tex, Mip normal_tex,
                                                                Mip material_tex, Mip depth0, Mip depth1, Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex,
                                                                Mip out, const float* __restrict__ srgb) {
@@ -49,6 +54,19 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const 
   }
   const ShadeK& k = LAYERED ? kl : k0;
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
+  __shared__ float4 s_ra[HALF ? SH_HH * SH_HW : 1];
+  __shared__ float s_d1[HALF ? SH_HH * SH_HW : 1];
+  const int hx0 = (int)blockIdx.x * 16 - 1, hy0 = VKR_BLOCK_Y * 4 - 1;      // half-res origin of the staged block
+  if (HALF) {
+    if (threadIdx.x < SH_HH * SH_HW) {
+      const int ly = threadIdx.x / SH_HW, lx = threadIdx.x - ly * SH_HW;
+      const int qx = min(max(hx0 + lx, 0), depth1.w - 1), qy = min(max(hy0 + ly, 0), depth1.h - 1);   // clamp-to-edge per index
+      const f3 c = unpack_rgb8unorm(ld32(reflections_tex, qx, qy));
+      s_ra[threadIdx.x] = make_float4(c.x, c.y, c.z, unpack_rg16f(ld32(occlusion_tex, qx, qy)).x);
+      s_d1[threadIdx.x] = d24_to_float(ld32(depth1, qx, qy));
+    }
+    __syncthreads();
+  }
   if (px >= out.w || py >= out.h) return;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
 #define CH(k, s) __ldg(srgb + (((k) >> (s)) & 255u))
@@ -89,19 +107,27 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const 
 
   // sample_ocllusion_ssr, shader.frag:103-130.  The four textureLodOffset(depth, uv, 1, off) footprints
   // cover a 3x3 block of half-res texels: fetch and decode each once.
-  int ox, oy;
+  int ox, oy, hbase = 0;
   Tap t1 = make_tap(su, sv, depth1.w, depth1.h);
   {
     float x = __fsub_rn(__fmul_rn(su, (float)depth1.w), 0.5f), y = __fsub_rn(__fmul_rn(sv, (float)depth1.h), 0.5f);
     const int ix = (int)floorf(x), iy = (int)floorf(y);
-    int cx[3], cy[3];
-#pragma unroll
-    for (int i = 0; i < 3; i++) { cx[i] = min(max(ix + i, 0), depth1.w - 1); cy[i] = min(max(iy + i, 0), depth1.h - 1); }
     float d[3][3];
+    if (HALF) {
+      hbase = (iy - hy0) * SH_HW + (ix - hx0);
 #pragma unroll
-    for (int j = 0; j < 3; j++)
+      for (int j = 0; j < 3; j++)
 #pragma unroll
-      for (int i = 0; i < 3; i++) d[j][i] = d24_to_float(ld32(depth1, cx[i], cy[j]));
+        for (int i = 0; i < 3; i++) d[j][i] = s_d1[hbase + j * SH_HW + i];
+    } else {
+      int cx[3], cy[3];
+#pragma unroll
+      for (int i = 0; i < 3; i++) { cx[i] = min(max(ix + i, 0), depth1.w - 1); cy[i] = min(max(iy + i, 0), depth1.h - 1); }
+#pragma unroll
+      for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int i = 0; i < 3; i++) d[j][i] = d24_to_float(ld32(depth1, cx[i], cy[j]));
+    }
     float dl0 = fabsf(FS(bilerp(d[0][0], d[0][1], d[1][0], d[1][1], t1.wx, t1.wy), depth));
     float dl1 = fabsf(FS(bilerp(d[0][1], d[0][2], d[1][1], d[1][2], t1.wx, t1.wy), depth));
     float dl2 = fabsf(FS(bilerp(d[1][0], d[1][1], d[2][0], d[2][1], t1.wx, t1.wy), depth));
@@ -115,7 +141,13 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const 
   // --- value-only from here on ---
   float occlusion;
   c3 reflection;
-  {
+  if (HALF) {
+    const TapW t = make_tapw(t1);                                          // same extent: same weights; indices come from the staged block
+    const int b = hbase + oy * SH_HW + ox;
+    const float4 a00 = s_ra[b], a10 = s_ra[b + 1], a01 = s_ra[b + SH_HW], a11 = s_ra[b + SH_HW + 1];
+    occlusion = wsum(a00.w, a10.w, a01.w, a11.w, t);
+    reflection = C3(wsum(a00.x, a10.x, a01.x, a11.x, t), wsum(a00.y, a10.y, a01.y, a11.y, t), wsum(a00.z, a10.z, a01.z, a11.z, t));
+  } else {
     // occlusion and reflections have the extent of depth mip 1 in the reference (W/2 x H/2): one footprint serves both
     const bool shared_fp = occlusion_tex.w == reflections_tex.w && occlusion_tex.h == reflections_tex.h;
     const TapW t = make_tapw(su, sv, occlusion_tex.w, occlusion_tex.h, ox, oy);
@@ -211,8 +243,13 @@ extern "C" int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage
   const Dim dim = make_dim(out_color->width, out_color->height);
   const bool same = same_extent(albedo, out_color) && same_extent(normal, out_color) && same_extent(material, out_color) &&
                     out_color->width <= 8192 && out_color->height <= 8192;
-  auto kern = same ? (kv ? deferred_shading_kernel<true, true> : deferred_shading_kernel<true, false>)
-                   : (kv ? deferred_shading_kernel<false, true> : deferred_shading_kernel<false, false>);
+  const uint32_t w2 = out_color->width / 2, h2 = out_color->height / 2;
+  const bool half = same && (out_color->width % 2 == 0) && (out_color->height % 2 == 0) && occlusion->width == w2 && occlusion->height == h2 &&
+                    reflections->width == w2 && reflections->height == h2 && mip_dim(depth->width, 1) == (int)w2 && mip_dim(depth->height, 1) == (int)h2 &&
+                    same_extent(depth, out_color);
+  auto kern = half ? (kv ? deferred_shading_kernel<true, true, true> : deferred_shading_kernel<true, false, true>)
+              : same ? (kv ? deferred_shading_kernel<true, true, false> : deferred_shading_kernel<true, false, false>)
+                     : (kv ? deferred_shading_kernel<false, true, false> : deferred_shading_kernel<false, false, false>);
   kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, dim, make_mip(albedo, 0, x, 0), make_mip(normal, 0, x, 1), make_mip(material, 0, x, 2),
                              make_mip(depth, 0, x, 3), make_mip(depth, 1, x, 3), make_mip(occlusion, 0, x, 4), make_mip(brdf_lut, 0, x, 5),
                              make_mip(reflections, 0, x, 6), make_mip(out_color, 0, x, 7), srgb);
