@@ -141,8 +141,11 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
       // len(v) < 0.3 <=> |v|^2 < 0.09; a zero-length v gives NaN, which both max forms ignore.
       const f3 v = sub3f(reconstruct_fast(position.x, position.y, surface_z, camf), view_vec);
       const float d2 = dot3f(v, v);
-      const float h2 = dot3f(pixel_normal, v) * rsqrtf(d2);
-      if (d2 < 0.09f) h = fmaxf(h, h2);
+      if (d2 < 0.09f) {                                   // most samples of a long ray are farther than 0.3: skip the normalisation
+        float r;
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d2));
+        h = fmaxf(h, dot3f(pixel_normal, v) * r);
+      }
     }
   }
   bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
