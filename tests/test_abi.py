@@ -59,3 +59,32 @@ def test_compute_entry_fails_loudly_without_a_device():
     on = vkr.Image(32, 32, vkr.R16G16_UNORM, device="cpu")
     ov = vkr.Image(32, 32, vkr.R16G16_SFLOAT, device="cpu")
     assert vkr.lib.vkr_hiz_build(d.ptr, n.ptr, v.ptr, on.ptr, ov.ptr, None) == -3      # VKR_ERR_CUDA: no CPU fallback
+
+
+def test_pixel_uv_division_is_exact(tmp_path):
+    """common.cuh pixel_uv / texel_uv: q = k*r, e = fma(-q, W, k), q + e*r with r = RN(1/W) equals the IEEE quotient for
+    every extent W <= 16384 and every pixel p < W, for k = p + 0.5 and k = p (host check with hardware FMA)."""
+    import subprocess
+    src = tmp_path / "div.c"
+    src.write_text("""
+#include <math.h>
+#include <stdio.h>
+int main(void) {
+  long bad = 0;
+  for (int w = 1; w <= 16384; w++) {
+    float d = (float)w, r = 1.0f / d;
+    for (int p = 0; p < w; p++) {
+      float k = (float)p + 0.5f, q = k * r, e = fmaf(-q, d, k);
+      if (fmaf(e, r, q) != k / d) bad++;
+      k = (float)p; q = k * r; e = fmaf(-q, d, k);
+      if (fmaf(e, r, q) != k / d) bad++;
+    }
+  }
+  printf("%ld\n", bad);
+  return bad != 0;
+}
+""")
+    exe = tmp_path / "div"
+    subprocess.run(["gcc", "-O2", "-mfma", "-ffp-contract=off", "-o", str(exe), str(src), "-lm"], check=True)
+    r = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "0", r.stdout
