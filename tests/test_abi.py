@@ -80,7 +80,7 @@ int main(void) {
       if (fmaf(e, r, q) != k / d) bad++;
     }
   }
-  printf("%ld\n", bad);
+  printf("%ld", bad);
   return bad != 0;
 }
 """)
