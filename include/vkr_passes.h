@@ -39,6 +39,7 @@ typedef enum VkrStatus {
 /* Values are VkFormat numbers so descriptors read like gpu::ImageInfo
  * (reference src/scene_renderer.cpp:15-27, src/gtao.cpp:26-39, src/advanced_ssr.cpp:62-92). */
 typedef enum VkrFormat {
+  VKR_FORMAT_R8_UNORM = 9,
   VKR_FORMAT_R8G8B8A8_UNORM = 37,
   VKR_FORMAT_R8G8B8A8_SRGB = 43,
   VKR_FORMAT_R16_UNORM = 70,
@@ -124,6 +125,22 @@ typedef struct VkrTaaParams {
   float prev_inverse_camera[16];
   float fovy_aspect_znear_zfar[4];
 } VkrTaaParams;
+
+/* SSAO: UBO SSAOParams as the SHADER declares it (reference shaders/ssao/shader.frag:11-19; std140, so every vec3 of
+ * samples[] occupies 16 bytes — samples[i][3] is padding).  The reference's C++ mirror of the block packs glm::vec3 at
+ * 12 bytes (src/ssao.cpp:15-22), so its shader reads the sample floats at a 16-byte stride out of a 12-byte-strided
+ * array; a caller that wants those very bytes copies its 48 packed floats into samples[0..11][0..3]. */
+typedef struct VkrSsaoParams {
+  float projection[16];
+  float fovy, aspect, znear, zfar;
+  float samples[16][4];
+} VkrSsaoParams;
+
+/* Legacy SSR: UBO SSRParams (reference src/ssr.hpp:11-17). */
+typedef struct VkrSsrParams {
+  float normal_mat[16];
+  float fovy, aspect, znear, zfar;
+} VkrSsrParams;
 
 /* ---- extended launches: array layers and row windows ------------------------------------
  * Every pass entry has an `_ex` twin taking a VkrLaunchExt (NULL = the plain call):
@@ -231,6 +248,16 @@ int vkr_deferred_shading(const VkrShadingParams* p, const VkrImage* albedo, cons
 int vkr_taa_resolve(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
                     const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target, void* stream);
 
+/* ---- earlier passes kept beside the live ones (north_star: "GTAO/SSAO", "SSR/advanced_ssr") ------ */
+/* Task "SSAO" (reference src/ssao.cpp:54-96 SSAOPass::draw, ssao/shader.frag): depth mip 0, out R8_UNORM (:8-11).
+ * With layers > 1 every layer uses p[0].samples (one sample set per pass object, :34-52). */
+int vkr_ssao(const VkrSsaoParams* p, const VkrImage* depth, const VkrImage* out_occlusion, void* stream);
+/* Task "SSR" (reference src/ssr.cpp:10-73 add_ssr_pass, ssr/shader.frag + include/screen_trace.glsl:51-100).
+ * depth = whole D24 image with its min-pyramid; frame = the lit colour image (R8G8B8A8_SRGB or R16G16B16A16_SFLOAT);
+ * out R8G8B8A8_UNORM (:5-8). */
+int vkr_ssr_legacy(const VkrSsrParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* frame,
+                   const VkrImage* material, const VkrImage* out_reflection, void* stream);
+
 /* ---- _ex twins (see VkrLaunchExt) ---------------------------------------------------- */
 int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity, const VkrImage* out_normal,
                      const VkrImage* out_velocity, const VkrLaunchExt* ext, void* stream);
@@ -257,6 +284,9 @@ int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage* albedo, c
 int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history, const VkrImage* prev_depth, const VkrImage* depth,
                        const VkrImage* velocity, const VkrImage* color, const VkrImage* out_target,
                        const VkrLaunchExt* ext, void* stream);
+int vkr_ssao_ex(const VkrSsaoParams* p, const VkrImage* depth, const VkrImage* out_occlusion, const VkrLaunchExt* ext, void* stream);
+int vkr_ssr_legacy_ex(const VkrSsrParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* frame,
+                      const VkrImage* material, const VkrImage* out_reflection, const VkrLaunchExt* ext, void* stream);
 
 #ifdef __cplusplus
 }

@@ -20,6 +20,7 @@ using namespace glsl;
 
 // Numeric values = VkFormat, so the descriptor reads like the reference's ImageInfo.
 enum Format : uint32_t {
+  FMT_R8_UNORM = 9,
   FMT_R8G8B8A8_UNORM = 37,
   FMT_R8G8B8A8_SRGB = 43,
   FMT_R16_UNORM = 70,
@@ -46,6 +47,7 @@ struct Image {
 
 inline uint32_t texel_size(uint32_t f) {
   switch (f) {
+    case FMT_R8_UNORM: return 1;
     case FMT_R16_UNORM: case FMT_R16_SFLOAT: return 2;
     case FMT_R16G16B16A16_UNORM: case FMT_R16G16B16A16_SFLOAT: return 8;
     case FMT_R32G32B32A32_SFLOAT: return 16;
@@ -104,6 +106,7 @@ inline const uint8_t* texel_ptr(const Image& im, int x, int y, int lod) {
 inline vec4 decode_texel(uint32_t fmt, const uint8_t* p) {
   switch (fmt) {
     case FMT_D24_UNORM_S8_UINT: { uint32_t k; std::memcpy(&k, p, 4); return vec4((float)(k & 0xFFFFFFu) / 16777215.0f, 0, 0, 1); }
+    case FMT_R8_UNORM: return vec4(p[0] / 255.0f, 0, 0, 1);
     case FMT_R8G8B8A8_UNORM: return vec4(p[0] / 255.0f, p[1] / 255.0f, p[2] / 255.0f, p[3] / 255.0f);
     case FMT_R8G8B8A8_SRGB: { const float* t = srgb_decode_table(); return vec4(t[p[0]], t[p[1]], t[p[2]], p[3] / 255.0f); }
     case FMT_R16_UNORM: { uint16_t a; std::memcpy(&a, p, 2); return vec4(a / 65535.0f, 0, 0, 1); }
@@ -162,6 +165,7 @@ inline void imageStore(const Image& im, int lod, ivec2 p, vec4 c) {
   uint8_t* q = (uint8_t*)texel_ptr(im, p.x, p.y, lod);
   float v[4] = {c.x, c.y, c.z, c.w};
   switch (im.format) {
+    case FMT_R8_UNORM: q[0] = (uint8_t)unorm_store(v[0], 255.0f); break;
     case FMT_R8G8B8A8_UNORM: for (int i = 0; i < 4; i++) q[i] = (uint8_t)unorm_store(v[i], 255.0f); break;
     case FMT_R8G8B8A8_SRGB: for (int i = 0; i < 3; i++) q[i] = (uint8_t)unorm_store(srgb_encode(v[i]), 255.0f); q[3] = (uint8_t)unorm_store(v[3], 255.0f); break;
     case FMT_R16G16_UNORM: case FMT_R16G16B16A16_UNORM: case FMT_R16_UNORM: {

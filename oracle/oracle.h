@@ -85,6 +85,19 @@ typedef struct OrcTaaParams {
   float fovy_aspect_znear_zfar[4];
 } OrcTaaParams;
 
+/* SSAOParams as the SHADER declares it (reference shaders/ssao/shader.frag:11-19, std140: vec3 array stride 16). */
+typedef struct OrcSsaoParams {
+  float projection[16];
+  float fovy, aspect, znear, zfar;
+  float samples[16][4];
+} OrcSsaoParams;
+
+/* SSRParams (reference src/ssr.hpp:11-17). */
+typedef struct OrcSsrParams {
+  float normal_mat[16];
+  float fovy, aspect, znear, zfar;
+} OrcSsrParams;
+
 void orc_set_threads(int n);
 int  orc_get_max_threads(void);
 
@@ -123,6 +136,11 @@ int orc_deferred_shading(const OrcShadingParams* p, const OrcImage* albedo, cons
                          const OrcImage* brdf_lut, const OrcImage* reflections, const OrcImage* out_color, int y0, int y1);
 int orc_taa_resolve(const OrcTaaParams* p, const OrcImage* history, const OrcImage* prev_depth, const OrcImage* depth,
                     const OrcImage* velocity, const OrcImage* color, const OrcImage* out_target, int y0, int y1);
+
+/* secondary passes: reference shaders/ssao/shader.frag, shaders/ssr/shader.frag (+ include/screen_trace.glsl:51-100) */
+int orc_ssao(const OrcSsaoParams* p, const OrcImage* depth, const OrcImage* out_r8, int y0, int y1);
+int orc_ssr_legacy(const OrcSsrParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* frame,
+                   const OrcImage* material, const OrcImage* out_rgba8, int y0, int y1);
 
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);

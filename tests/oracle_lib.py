@@ -55,6 +55,8 @@ _sig("orc_gtao_filter", C.POINTER(vkr.GtaoParams), IP, IP, IP, U, I, I)
 _sig("orc_gtao_accumulate", C.POINTER(vkr.AccumParams), IP, IP, IP, IP, IP, IP, U, I, I)
 _sig("orc_deferred_shading", C.POINTER(vkr.ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, I, I)
 _sig("orc_taa_resolve", C.POINTER(vkr.TaaParams), IP, IP, IP, IP, IP, IP, I, I)
+_sig("orc_ssao", C.POINTER(vkr.SsaoParams), IP, IP, I, I)
+_sig("orc_ssr_legacy", C.POINTER(vkr.SsrParams), IP, IP, IP, IP, IP, I, I)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

@@ -1,0 +1,162 @@
+"""The renderer's earlier AO / reflection passes (reference src/ssao.cpp, src/ssr.cpp) through the C ABI vs the CPU oracle.
+
+Both passes are evaluated with the oracle's unfused arithmetic (SSAO's output is a count of 16 strict comparisons, the SSR
+march picks texels), so the bar is bit-exact bytes, allowing a 1e-4 fraction of pixels for libm-vs-device differences in the
+last place of a division feeding a comparison.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import chain
+import oracle_lib as orc
+import vkr
+import vkr_host
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_frame(w, h, scene_seed=0, objects=64, frames=1):
+    scene = vkr.synth_scene(scene_seed, objects)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=64)
+    for _ in range(frames):
+        imgs, P = oc.render(scene)
+    return imgs, P
+
+
+def _ssao_params(w, h, P, seed=3, reference_packing=False):
+    p = vkr.SsaoParams()
+    fovy, aspect, zn, zf = P["trace"].fovy, P["trace"].aspect, P["trace"].znear, P["trace"].zfar
+    C.memmove(p.projection, vkr.perspective(fovy, aspect, zn, zf), 64)
+    p.fovy, p.aspect, p.znear, p.zfar = fovy, aspect, zn, zf
+    vkr.set_ssao_samples(p, vkr.sphere_samples(seed), reference_packing)
+    return p
+
+
+def _ssr_params(P):
+    sp = vkr.SsrParams()
+    C.memmove(sp.normal_mat, P["trace"].normal_mat, 64)
+    sp.fovy, sp.aspect, sp.znear, sp.zfar = P["trace"].fovy, P["trace"].aspect, P["trace"].znear, P["trace"].zfar
+    return sp
+
+
+@pytest.mark.parametrize("w,h,packing", [(320, 180, False), (250, 130, True), (1280, 720, False)])
+def test_ssao_matches_oracle(cuda, w, h, packing):
+    import torch
+    imgs, P = _oracle_frame(w, h)
+    p = _ssao_params(w, h, P, reference_packing=packing)
+    ref = vkr.Image(w, h, vkr.R8_UNORM, device="cpu")
+    orc.ok(orc.lib.orc_ssao(C.byref(p), imgs["depth"].ptr, ref.ptr, 0, 0))
+    out = vkr.Image(w, h, vkr.R8_UNORM)
+    vkr.ssao(p, imgs["depth"].clone_to("cuda"), out)
+    torch.cuda.synchronize()
+    g, r = out.download(), ref.download()
+    assert len(np.unique(r)) > 8, "the scene should produce a spread of occlusion values"
+    bad = (g != r)
+    assert bad.mean() <= 1e-4, (bad.sum(), np.abs(g.astype(int) - r.astype(int)).max())
+    assert np.abs(g.astype(int) - r.astype(int)).max() <= 16         # a flipped comparison moves the count by one sample
+
+
+@pytest.mark.parametrize("w,h,frame_name", [(320, 180, "color"), (254, 126, "taa"), (1280, 720, "color")])
+def test_ssr_legacy_matches_oracle(cuda, w, h, frame_name):
+    import torch
+    imgs, P = _oracle_frame(w, h, frames=2)
+    sp = _ssr_params(P)
+    ref = vkr.Image(w, h, vkr.R8G8B8A8_UNORM, device="cpu")
+    orc.ok(orc.lib.orc_ssr_legacy(C.byref(sp), imgs["depth"].ptr, imgs["normal"].ptr, imgs[frame_name].ptr, imgs["material"].ptr, ref.ptr, 0, 0))
+    out = vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
+    dev = {k: imgs[k].clone_to("cuda") for k in ("depth", "normal", "material", frame_name)}
+    vkr.ssr_legacy(sp, dev["depth"], dev["normal"], dev[frame_name], dev["material"], out)
+    torch.cuda.synchronize()
+    g, r = out.download().astype(np.int32), ref.download().astype(np.int32)
+    hit = (r[..., :3].max(axis=-1) > 0)
+    assert hit.mean() > 0.02, "the scene should have reflecting pixels"
+    d = np.abs(g - r).max(axis=-1)
+    # a march whose branch flips on the last place of an IEEE-vs-device division may end elsewhere: <= 1e-4 of the pixels
+    assert (d > 1).mean() <= 1e-4, ((d > 1).sum(), d.max())
+    assert (d > 0).mean() <= 1e-3, (d > 0).sum()
+
+
+def test_alt_passes_row_windows_and_layers(cuda):
+    """Row windows write the bytes of the whole pass; two array layers equal two single launches."""
+    import torch
+    w, h = 256, 160
+    imgs, P = _oracle_frame(w, h)
+    p, sp = _ssao_params(w, h, P), _ssr_params(P)
+    dev = {k: imgs[k].clone_to("cuda") for k in ("depth", "normal", "material", "color")}
+    whole_ao, whole_ssr = vkr.Image(w, h, vkr.R8_UNORM), vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
+    vkr.ssao(p, dev["depth"], whole_ao)
+    vkr.ssr_legacy(sp, dev["depth"], dev["normal"], dev["color"], dev["material"], whole_ssr)
+    part_ao, part_ssr = vkr.Image(w, h, vkr.R8_UNORM), vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
+    mid = (h // 2) // vkr.ROW_ALIGN * vkr.ROW_ALIGN
+    for rows in ((0, mid), (mid, h)):
+        vkr.ssao(p, dev["depth"], part_ao, ext=vkr.make_ext([], rows=rows))
+        vkr.ssr_legacy(sp, dev["depth"], dev["normal"], dev["color"], dev["material"], part_ssr, ext=vkr.make_ext([], rows=rows))
+    torch.cuda.synchronize()
+    assert torch.equal(whole_ao.buf, part_ao.buf) and torch.equal(whole_ssr.buf, part_ssr.buf)
+
+    # layers: the same view twice with different cameras' parameter blocks
+    imgs2, P2 = _oracle_frame(w, h, scene_seed=5)
+    arrs = {}
+    for k, fmt, mips in (("depth", vkr.D24_UNORM_S8_UINT, imgs["depth"].mips), ("normal", vkr.R16G16_UNORM, 1), ("material", vkr.R8G8B8A8_SRGB, 1),
+                         ("color", vkr.R8G8B8A8_SRGB, 1)):
+        a = vkr.ImageArray(w, h, fmt, mips, layers=2)
+        a.layer(0).buf.copy_(imgs[k].buf)
+        a.layer(1).buf.copy_(imgs2[k].buf)
+        arrs[k] = a
+    out_ao, out_ssr = vkr.ImageArray(w, h, vkr.R8_UNORM, 1, layers=2), vkr.ImageArray(w, h, vkr.R8G8B8A8_UNORM, 1, layers=2)
+    scratch = torch.zeros(2 * vkr.PARAMS_SCRATCH_STRIDE, dtype=torch.uint8, device="cuda")
+    p2, sp2 = _ssao_params(w, h, P2), _ssr_params(P2)
+    vkr.ssao(vkr.params_array(vkr.SsaoParams, [p, p2]), arrs["depth"], out_ao, ext=vkr.make_ext([arrs["depth"], out_ao], layers=2, scratch=scratch))
+    torch.cuda.synchronize()
+    vkr.ssr_legacy(vkr.params_array(vkr.SsrParams, [sp, sp2]), arrs["depth"], arrs["normal"], arrs["color"], arrs["material"], out_ssr,
+                   ext=vkr.make_ext([arrs["depth"], arrs["normal"], arrs["color"], arrs["material"], out_ssr], layers=2, scratch=scratch))
+    torch.cuda.synchronize()
+    dev2 = {k: imgs2[k].clone_to("cuda") for k in ("depth", "normal", "material", "color")}
+    single_ao, single_ssr = vkr.Image(w, h, vkr.R8_UNORM), vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
+    vkr.ssao(p2, dev2["depth"], single_ao)
+    vkr.ssr_legacy(sp2, dev2["depth"], dev2["normal"], dev2["color"], dev2["material"], single_ssr)
+    torch.cuda.synchronize()
+    assert torch.equal(out_ao.layer(0).buf, whole_ao.buf) and torch.equal(out_ao.layer(1).buf, single_ao.buf)
+    assert torch.equal(out_ssr.layer(0).buf, whole_ssr.buf) and torch.equal(out_ssr.layer(1).buf, single_ssr.buf)
+
+
+def test_alt_passes_validation(cuda):
+    w, h = 64, 32
+    depth = vkr.Image(w, h, vkr.D24_UNORM_S8_UINT, vkr.full_mip_count(w, h))
+    bad = vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
+    with pytest.raises(vkr.VkrError):
+        vkr.ssao(vkr.SsaoParams(), depth, bad)                     # SSAO target must be R8_UNORM
+    nrm, mat, frame = vkr.Image(w, h, vkr.R16G16_UNORM), vkr.Image(w, h, vkr.R8G8B8A8_SRGB), vkr.Image(w, h, vkr.R8G8B8A8_SRGB)
+    with pytest.raises(vkr.VkrError):
+        vkr.ssr_legacy(vkr.SsrParams(), depth, nrm, frame, mat, vkr.Image(w, h, vkr.R8_UNORM))
+
+
+def test_host_app_runs_the_alt_passes(cuda):
+    """SSAOPass / add_ssr_pass scheduled behind TAA by the C++ host equal the oracle fed with the blocks the host built."""
+    w, h = 320, 180
+    scene = vkr.synth_scene(0, 32)
+    app = vkr_host.App(w, h, device=0)
+    app.set_option("alt.ssao", 1)
+    app.set_option("alt.ssr", 1)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=1024)
+    for f in range(2):
+        dp = vkr.synth_camera(0, f, w, h, True)
+        P = oc.begin_frame(scene)
+        app.upload_gbuffer(oc.gb)
+        app.render_frame(dp, chain.angle_jitter(f))
+        oc.passes(P)
+        ref = oc.images()
+        assert app.last_tasks()[-2:] == ["SSAO", "SSR"]
+        a, r = app.alt_params()
+        ref_ao, ref_ssr = vkr.Image(w, h, vkr.R8_UNORM, device="cpu"), vkr.Image(w, h, vkr.R8G8B8A8_UNORM, device="cpu")
+        color_dev = app.readback("color")                 # the host's own lit frame is the SSR input (1 LSB from the oracle's)
+        orc.ok(orc.lib.orc_ssao(C.byref(a), ref["depth"].ptr, ref_ao.ptr, 0, 0))
+        orc.ok(orc.lib.orc_ssr_legacy(C.byref(r), ref["depth"].ptr, ref["normal"].ptr, color_dev.ptr, ref["material"].ptr, ref_ssr.ptr, 0, 0))
+        g_ao, g_ssr = app.readback("ssao").download(), app.readback("ssr_legacy").download().astype(np.int32)
+        assert (g_ao != ref_ao.download()).mean() <= 1e-4
+        d = np.abs(g_ssr - ref_ssr.download().astype(np.int32)).max(axis=-1)
+        assert (d > 1).mean() <= 1e-4 and (d > 0).mean() <= 1e-3
+        oc.end_frame()
+    app.close()

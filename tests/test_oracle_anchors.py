@@ -224,3 +224,79 @@ def test_ssr_mirror_floor_hits_the_reflected_ray():
     lin = lambda d: nn * f / (d * (f - nn) - f)  # noqa: E731
     dz = lin(hit[floor, 2]) - lin(d1[hy, hx])
     assert np.quantile(np.abs(dz), 0.99) < 0.35
+
+
+# ---- (vii) the earlier passes: SSAO and the mirror SSR -------------------------------------------------------
+def test_ssao_flat_plane_counts_the_samples_facing_the_camera():
+    """Constant depth buffer: a tap at camera_pos + 0.05 s projects nearer than the plane iff s.z > 0 (the camera looks
+    down -z), so every pixel holds (#samples with s.z > 0) / 16 exactly (ssao/shader.frag:28-40)."""
+    w, h = 160, 96
+    gb, _ = flat_gbuffer(w, h, -5.0)
+    p = vkr.SsaoParams()
+    C.memmove(p.projection, vkr.perspective(FOVY, w / h, ZN, ZF), 64)
+    p.fovy, p.aspect, p.znear, p.zfar = FOVY, w / h, ZN, ZF
+    s = vkr.sphere_samples(7)
+    assert np.allclose(np.linalg.norm(s[:, :3], axis=1), 1.0, atol=1e-6) and np.abs(s[:, 2]).min() > 1e-2
+    vkr.set_ssao_samples(p, s)
+    out = vkr.Image(w, h, vkr.R8_UNORM, device="cpu")
+    orc.ok(orc.lib.orc_ssao(C.byref(p), gb.depth.ptr, out.ptr, 0, 0))
+    want = int(np.floor((s[:, 2] > 0).sum() / 16.0 * 255.0 + 0.5))
+    got = out.download()
+    assert (got == want).all(), (want, np.unique(got))
+    # the reference's own packing (12-byte stride read at 16): sample i = packed floats [4i, 4i+1, 4i+2], 12..15 zero
+    vkr.set_ssao_samples(p, s, reference_packing=True)
+    flat = s[:, :3].reshape(-1)
+    z_seen = np.array([flat[4 * i + 2] for i in range(12)] + [0.0] * 4)
+    orc.ok(orc.lib.orc_ssao(C.byref(p), gb.depth.ptr, out.ptr, 0, 0))
+    # a zero sample sits on the plane: pos_depth == sample_depth up to the D24 rounding of the plane, decided by the 1e-7 bias
+    lo = int(np.floor((z_seen > 0).sum() / 16.0 * 255.0 + 0.5))
+    hi = int(np.floor(((z_seen > 0).sum() + 4) / 16.0 * 255.0 + 0.5))
+    got = out.download()
+    assert ((got >= lo) & (got <= hi)).all()
+
+
+def test_ssr_legacy_floor_reflects_a_constant_frame_with_ggx_weight():
+    """Ground + wall, constant frame colour c, floor roughness code 255 (alpha = 1): wherever the floor sees the wall,
+    out = coef * c * D(N,N,1) * max(N.R, 0) with D = 1/pi and N.R = -N.view_vec (ssr/shader.frag:37-41,:92-96)."""
+    w, h = 384, 216
+    scene = vkr.synth_scene(0, 0)
+    scene.ground_material = 255 << 8                       # roughness code 255 in .g
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=16)
+    P = oc.begin_frame(scene, jitter=False)
+    oc.steps(P)[0][1]()                                    # Hi-Z (the march reads every mip)
+    gb = oc.gb
+    frame = vkr.Image(w, h, vkr.R8G8B8A8_SRGB, device="cpu")
+    frame.upload(np.full((h, w, 4), 255, dtype=np.uint8))  # linear 1.0, alpha 1.0
+    out = vkr.Image(w, h, vkr.R8G8B8A8_UNORM, device="cpu")
+    sp = vkr.SsrParams()
+    C.memmove(sp.normal_mat, P["trace"].normal_mat, 64)
+    sp.fovy, sp.aspect, sp.znear, sp.zfar = FOVY, np.float32(w) / np.float32(h), ZN, ZF
+    orc.ok(orc.lib.orc_ssr_legacy(C.byref(sp), gb.depth.ptr, gb.normal.ptr, frame.ptr, gb.material.ptr, out.ptr, 0, 0))
+    got = out.download().astype(np.float64) / 255.0
+    assert (got[..., 0] == got[..., 1]).all() and (got[..., 0] == got[..., 3]).all()
+    d0 = gb.depth.download(0).astype(np.float64) / 0xFFFFFF
+    nrm = gb.normal.download().astype(np.float64) / 65535.0
+    ys, xs = np.nonzero(got[..., 0] > 0)
+    assert len(ys) > 0.02 * w * h, "the floor should reflect the wall in a sizeable region"
+    u, v = (xs + 0.5) / w, (ys + 0.5) / h
+    Pv = reconstruct_np(u, v, d0[ys, xs], w / h)
+    e = nrm[ys, xs] * 2 - 1
+    n = np.stack([e[:, 0], e[:, 1], 1 - np.abs(e[:, 0]) - np.abs(e[:, 1])], axis=-1)
+    assert (n[:, 2] >= 0).all() or True
+    neg = n[:, 2] < 0
+    nx = (1 - np.abs(n[:, 1])) * np.where(n[:, 0] >= 0, 1, -1)
+    ny = (1 - np.abs(n[:, 0])) * np.where(n[:, 1] >= 0, 1, -1)
+    n[neg, 0], n[neg, 1] = nx[neg], ny[neg]
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    M = np.array(list(sp.normal_mat), dtype=np.float64).reshape(4, 4).T[:3, :3]
+    nv = n @ M.T
+    nv /= np.linalg.norm(nv, axis=1, keepdims=True)
+    floor = np.abs(n[:, 1]) > 0.99
+    assert floor.sum() > 0.9 * len(ys)
+    expect = np.clip(-(nv * Pv).sum(axis=1) / np.pi, 0, 1)         # coef = 1 away from the 5 % border band
+    # interior hits only: the fade band is 5 % of the height at each border of the HIT position; stay well inside with the pixel too
+    inner = floor & (u > 0.2) & (u < 0.8) & (v > 0.2) & (v < 0.8)
+    err = np.abs(got[ys, xs, 0] - expect)
+    full = inner & (err < 1.5 / 255)                               # pixels whose hit is inside the band-free region
+    assert full.sum() > 0.5 * inner.sum(), (full.sum(), inner.sum())
+    assert (got[ys, xs, 0][inner] <= expect[inner] + 1.5 / 255).all()   # the fade only ever darkens

@@ -118,6 +118,7 @@ const char* vkr_last_error(void) { return vkr::g_err; }
 
 uint32_t vkr_format_texel_size(uint32_t f) {
   switch (f) {
+    case VKR_FORMAT_R8_UNORM: return 1;
     case VKR_FORMAT_R16_UNORM: case VKR_FORMAT_R16_SFLOAT: return 2;
     case VKR_FORMAT_R8G8B8A8_UNORM: case VKR_FORMAT_R8G8B8A8_SRGB: case VKR_FORMAT_R16G16_UNORM:
     case VKR_FORMAT_R16G16_SFLOAT: case VKR_FORMAT_R32_SFLOAT: case VKR_FORMAT_D24_UNORM_S8_UINT: return 4;

@@ -5,13 +5,9 @@
 // shaders/advanced_ssr/trace.comp:41-141,:206-268, shaders/include/screen_trace.glsl:8-45).
 #include <vector>
 #include "brdf.cuh"
+#include "march.cuh"
 
 namespace vkr {
-
-struct PyramidView {   // depth mips 1..L-1 (advanced_ssr.cpp:186): view lod m = image mip m+1
-  Mip mip[VKR_MAX_MIPS];
-  int count;
-};
 
 struct TraceK {
   Mat4 normal_mat;
@@ -20,8 +16,6 @@ struct TraceK {
   float max_roughness;
 };
 
-#define MAX_T_FLOAT 3.402823466e+38f
-
 // trace.comp:156-158, bit-defined (see oracle/passes_ssr.cpp rand_hash): unfused fp32 dot,
 // sin in double rounded once to fp32, fp32 multiply, fract.
 __device__ __forceinline__ float rand_hash(float u, float v) {
@@ -29,30 +23,6 @@ __device__ __forceinline__ float rand_hash(float u, float v) {
   float s = (float)sin((double)d);
   float p = __fmul_rn(s, 43758.5453f);
   return __fsub_rn(p, floorf(p));
-}
-
-__device__ __forceinline__ float fetch_pyramid(const PyramidView& P, unsigned long long layer_off, int x, int y, int lod) {
-  if ((unsigned)lod >= (unsigned)P.count) return 0.0f;
-  const Mip& m = P.mip[lod];
-  if ((unsigned)x >= (unsigned)m.w || (unsigned)y >= (unsigned)m.h) return 0.0f;      // texelFetch out of range = 0 (App. A.3)
-  return d24_to_float(__ldg((const uint32_t*)(m.p + layer_off + (size_t)y * m.pitch) + x));
-}
-
-// screen_trace.glsl:17-45
-__device__ __forceinline__ bool advance_ray(f3 origin, f3 direction, f3 inv_direction, float mpx, float mpy, float rinvx, float rinvy,
-                                            float fox, float foy, float uox, float uoy, float surface_z, f3& position, float& current_t) {
-  float xp = FA(FM(FA(floorf(mpx), fox), rinvx), uox);
-  float yp = FA(FM(FA(floorf(mpy), foy), rinvy), uoy);
-  float tx = FM(FS(xp, origin.x), inv_direction.x);
-  float ty = FM(FS(yp, origin.y), inv_direction.y);
-  float tz = FM(FS(surface_z, origin.z), inv_direction.z);
-  tz = direction.z > 0 ? tz : MAX_T_FLOAT;
-  float t_min = gmin(gmin(tx, ty), tz);
-  bool above_surface = surface_z > position.z;
-  bool skipped_tile = t_min != tz && above_surface;
-  current_t = above_surface ? t_min : current_t;
-  position = origin + current_t * direction;
-  return skipped_tile;
 }
 
 template <bool LAYERED>

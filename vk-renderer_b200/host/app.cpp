@@ -1,6 +1,7 @@
 // app.cpp — the reference's frame loop without the window (see include/vkr_host.h), and its C API.
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <map>
@@ -19,6 +20,17 @@ static void host_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static void copy16(float* dst, const float* src) { std::memcpy(dst, src, 64); }
+
+// glm::perspectiveRH_ZO in fp32 (the projection Camera::get_projection hands to SSAOInParams)
+static glm::mat4 perspective(float fovy, float aspect, float zn, float zf) {
+  const float t = std::tan(fovy / 2.f);
+  glm::mat4 p;
+  std::memset(p.m, 0, sizeof(p.m));
+  p.m[0] = 1.f / (aspect * t); p.m[5] = 1.f / t; p.m[10] = zf / (zn - zf); p.m[11] = -1.f; p.m[14] = -(zf * zn) / (zf - zn);
+  return p;
+}
+
 struct VkrApp {
   uint32_t width, height;
   RenderGraph render_graph;
@@ -29,13 +41,19 @@ struct VkrApp {
   TAA taa_pass;
   DeferedShadingPass shading_pass;
   ImageResourceId shadows_tex, color_out_tex;
+  // the earlier AO / reflection passes (src/ssao.cpp, src/ssr.cpp): in the reference tree but not in its frame loop, so off by default
+  ImageResourceId ssao_tex, ssr_tex;
+  SSAOPass ssao_pass;
+  bool alt_ssao = false, alt_ssr = false;
+  VkrSsrParams last_ssr{};
   std::string task_names;
   uint64_t frames = 0;
 
   VkrApp(int device, uint32_t w, uint32_t h, void* stream)
       : width{w}, height{h}, render_graph{device, stream}, gbuffer{render_graph, w, h}, downsample_pass{},
         gtao{render_graph, w, h, /*USE_RAY_QUERY*/ false, /*half_res*/ true},                   // main.cpp:265
-        ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph} {
+        ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph},
+        ssao_tex{create_ssao_texture(render_graph, w, h)}, ssr_tex{create_ssr_tex(render_graph, w, h)}, ssao_pass{render_graph, ssao_tex, 0} {
     ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
     ssr.preintegrate_brdf(render_graph);
     gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
@@ -72,6 +90,16 @@ struct VkrApp {
     gtao.add_accumulate_pass(render_graph, draw_params, gbuffer);                                 // :388
     shading_pass.draw(render_graph, gbuffer, shadows_tex, gtao.accumulated_ao, ssr.get_preintegrated_brdf(), ssr.get_blurred(), color_out_tex);  // :390
     taa_pass.run(render_graph, gbuffer, color_out_tex, draw_params);                              // :391
+    if (alt_ssao) {
+      SSAOInParams sp{perspective(fovy, aspect, znear, zfar), fovy, aspect, znear, zfar};
+      ssao_pass.draw(render_graph, gbuffer.depth, ssao_tex, sp);
+    }
+    if (alt_ssr) {
+      SSRParams rp{normal_mat, fovy, aspect, znear, zfar};
+      copy16(last_ssr.normal_mat, normal_mat.m);
+      last_ssr.fovy = fovy; last_ssr.aspect = aspect; last_ssr.znear = znear; last_ssr.zfar = zfar;
+      add_ssr_pass(render_graph, gbuffer.depth, gbuffer.normal, color_out_tex, gbuffer.material, ssr_tex, rp);
+    }
     render_graph.submit();                                                                        // :402
     task_names.clear();
     for (auto& n : render_graph.last_task_names()) { task_names += n; task_names += '\n'; }
@@ -106,6 +134,8 @@ struct VkrApp {
     else if (name == "taa") id = r ? taa_pass.get_history() : taa_pass.get_output();
     else if (name == "pdf") id = ssr.get_preintegrated_pdf();
     else if (name == "brdf") id = ssr.get_preintegrated_brdf();
+    else if (name == "ssao") id = ssao_tex;
+    else if (name == "ssr_legacy") id = ssr_tex;
     else return false;
     return true;
   }
@@ -223,6 +253,13 @@ int vkr_app_sync(VkrApp* app) {
   VKR_TRY(app->render_graph.wait_idle())
 }
 
+int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out) {
+  if (!app) { host_error("alt_params: null app"); return VKR_ERR_INVALID_ARGUMENT; }
+  if (ssao_out) *ssao_out = app->ssao_pass.last_block;
+  if (ssr_out) *ssr_out = app->last_ssr;
+  return VKR_OK;
+}
+
 void* vkr_app_stream(VkrApp* app) { return app ? app->render_graph.stream() : nullptr; }
 const char* vkr_app_last_tasks(VkrApp* app) { return app ? app->task_names.c_str() : ""; }
 
@@ -241,6 +278,9 @@ int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   else if (n == "ssr.bilateral") app->ssr.settings.bilateral_filter = v != 0.f;
   else if (n == "ssr.use_blur") app->ssr.settings.use_blur = v != 0.f;
   else if (n == "ssr.max_accumulated_rays") app->ssr.settings.max_accumulated_rays = (int)v;
+  else if (n == "alt.ssao") app->alt_ssao = v != 0.f;
+  else if (n == "alt.ssr") app->alt_ssr = v != 0.f;
+  else if (n == "alt.ssao_reference_packing") app->ssao_pass.reference_packing = v != 0.f;
   else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
   else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;
   else if (n == "shading.max_roughness") app->shading_pass.min_max_roughness.y = v;

@@ -7,6 +7,8 @@
 //   AdvancedSSR, AdvancedSSRParams           src/advanced_ssr.hpp:7-116
 //   DeferedShadingPass                       src/defered_shading.hpp:8-32
 //   TAA                                      src/taa.hpp:8-21
+//   SSAOPass, SSAOInParams, create_ssao_texture   src/ssao.hpp:7-31
+//   SSRParams, add_ssr_pass, create_ssr_tex       src/ssr.hpp:7-26
 // Dropped: pipelines / samplers / descriptor sets (no graphics API), the SDL_Window* of
 // DeferedShadingPass (ImGui only), ray-query and graphics-pipeline GTAO variants, ImGui panels.
 #pragma once
@@ -180,3 +182,41 @@ struct TAA {
   rendergraph::ImageResourceId history;
   rendergraph::ImageResourceId target;
 };
+
+// ---- the earlier passes (present in the reference tree, not scheduled by its frame loop) -------------------------
+rendergraph::ImageResourceId create_ssao_texture(rendergraph::RenderGraph& graph, uint32_t width, uint32_t height);
+
+struct SSAOInParams {
+  glm::mat4 projection;
+  float fovy;
+  float aspect;
+  float znear;
+  float zfar;
+};
+
+struct vec3 { float x = 0, y = 0, z = 0; };
+
+struct SSAOPass {
+  // The reference seeds nothing and draws from libc rand() (src/ssao.cpp:34-52); `seed` makes the sample set an input.
+  SSAOPass(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId target, uint32_t seed = 0);
+  void draw(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId depth, rendergraph::ImageResourceId target, const SSAOInParams& params);
+
+  std::vector<vec3> sphere_samples;   // private in the reference; public here so tests can hand the same set to the oracle
+  // true: upload the block with the reference's C++ layout (vec3 at 12 bytes) and let the kernel read it at the shader's
+  // 16-byte stride, like the reference does; false: each sample in its own std140 slot.
+  bool reference_packing = false;
+  VkrSsaoParams last_block{};         // the block of the most recent draw() (what the reference writes into its UBO)
+};
+
+rendergraph::ImageResourceId create_ssr_tex(rendergraph::RenderGraph& graph, uint32_t w, uint32_t h);
+
+struct SSRParams {
+  glm::mat4 normal_mat;
+  float fovy;
+  float aspect;
+  float znear;
+  float zfar;
+};
+
+void add_ssr_pass(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId depth, rendergraph::ImageResourceId normal,
+                  rendergraph::ImageResourceId color, rendergraph::ImageResourceId material, rendergraph::ImageResourceId out, const SSRParams& params);

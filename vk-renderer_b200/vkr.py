@@ -17,13 +17,13 @@ if not os.path.exists(LIB_PATH):
 lib = C.CDLL(LIB_PATH)
 
 # VkFormat values (include/vkr_passes.h VkrFormat)
-R8G8B8A8_UNORM, R8G8B8A8_SRGB = 37, 43
+R8_UNORM, R8G8B8A8_UNORM, R8G8B8A8_SRGB = 9, 37, 43
 R16_UNORM, R16_SFLOAT, R16G16_UNORM, R16G16_SFLOAT = 70, 76, 77, 83
 R16G16B16A16_UNORM, R16G16B16A16_SFLOAT = 91, 97
 R32_SFLOAT, R32G32B32A32_SFLOAT, D24_UNORM_S8_UINT = 100, 109, 129
 
 _NP = {  # format -> (numpy dtype, channels)
-    R8G8B8A8_UNORM: (np.uint8, 4), R8G8B8A8_SRGB: (np.uint8, 4),
+    R8_UNORM: (np.uint8, 1), R8G8B8A8_UNORM: (np.uint8, 4), R8G8B8A8_SRGB: (np.uint8, 4),
     R16_UNORM: (np.uint16, 1), R16_SFLOAT: (np.float16, 1),
     R16G16_UNORM: (np.uint16, 2), R16G16_SFLOAT: (np.float16, 2),
     R16G16B16A16_UNORM: (np.uint16, 4), R16G16B16A16_SFLOAT: (np.float16, 4),
@@ -69,6 +69,16 @@ class ShadingParams(C.Structure):
 
 class TaaParams(C.Structure):
     _fields_ = [_mat("inverse_camera"), _mat("prev_inverse_camera"), ("fovy_aspect_znear_zfar", C.c_float * 4)]
+
+
+class SsaoParams(C.Structure):
+    """SSAOParams as the shader declares it (std140: samples are vec3 at a 16-byte stride)."""
+    _fields_ = [_mat("projection"), ("fovy", C.c_float), ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float),
+                ("samples", (C.c_float * 4) * 16)]
+
+
+class SsrParams(C.Structure):
+    _fields_ = [_mat("normal_mat"), ("fovy", C.c_float), ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float)]
 
 
 def set_mat(field, m):
@@ -380,6 +390,10 @@ _sig("vkr_gtao_filter_ex", PT(GtaoParams), IP, IP, IP, C.c_uint32, EP, VP)
 _sig("vkr_gtao_accumulate_ex", PT(AccumParams), IP, IP, IP, IP, IP, IP, C.c_uint32, EP, VP)
 _sig("vkr_deferred_shading_ex", PT(ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, EP, VP)
 _sig("vkr_taa_resolve_ex", PT(TaaParams), IP, IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_ssao", PT(SsaoParams), IP, IP, VP)
+_sig("vkr_ssao_ex", PT(SsaoParams), IP, IP, EP, VP)
+_sig("vkr_ssr_legacy", PT(SsrParams), IP, IP, IP, IP, IP, VP)
+_sig("vkr_ssr_legacy_ex", PT(SsrParams), IP, IP, IP, IP, IP, EP, VP)
 
 
 class ImageArray:
@@ -479,3 +493,50 @@ def deferred_shading_ex(p, albedo, normal, material, depth, occlusion, brdf, ref
 
 def taa_resolve_ex(p, history, prev_depth, depth, velocity, color, out, ext, stream=None):
     check(lib.vkr_taa_resolve_ex(_p(p), history.ptr, prev_depth.ptr, depth.ptr, velocity.ptr, color.ptr, out.ptr, C.byref(ext), stream_ptr(stream)))
+
+
+# ---- earlier passes kept beside the live ones (reference src/ssao.cpp, src/ssr.cpp) ------------------------------
+def ssao(p, depth, out, ext=None, stream=None):
+    check(lib.vkr_ssao_ex(_p(p), depth.ptr, out.ptr, C.byref(ext) if ext is not None else None, stream_ptr(stream)))
+
+
+def ssr_legacy(p, depth, normal, frame, material, out, ext=None, stream=None):
+    check(lib.vkr_ssr_legacy_ex(_p(p), depth.ptr, normal.ptr, frame.ptr, material.ptr, out.ptr, C.byref(ext) if ext is not None else None,
+                                stream_ptr(stream)))
+
+
+def sphere_samples(seed=0, count=16):
+    """Unit vectors drawn like SSAOPass's constructor (reference src/ssao.cpp:34-52): rejection-sample the unit ball, then
+    normalise.  The reference draws from libc rand() with no seed; here a seeded numpy generator."""
+    rng = np.random.RandomState(seed)
+    out = np.zeros((count, 4), dtype=np.float32)
+    i = 0
+    while i < count:
+        v = (2.0 * rng.rand(3) - 1.0).astype(np.float32)
+        l2 = np.float32(v[0] * v[0] + v[1] * v[1] + v[2] * v[2])
+        if l2 < 1.0 and l2 > 0.0:
+            out[i, :3] = v / np.sqrt(l2)
+            i += 1
+    return out
+
+
+def set_ssao_samples(p, samples, reference_packing=False):
+    """samples: (16, >=3) floats.  reference_packing=True reproduces the bytes the reference's C++ block holds (glm::vec3
+    at a 12-byte stride, src/ssao.cpp:15-22) as its shader reads them (16-byte stride): 48 packed floats land in
+    samples[0..11][0..3]; entries 12..15 lie beyond the block in the reference (undefined there, zero here)."""
+    a = np.zeros((16, 4), dtype=np.float32)
+    s3 = np.asarray(samples, dtype=np.float32)[:16, :3]
+    if reference_packing:
+        a.reshape(-1)[:48] = s3.reshape(-1)
+    else:
+        a[:, :3] = s3
+    C.memmove(C.addressof(p.samples), a.ctypes.data, a.nbytes)
+    return p
+
+
+def perspective(fovy, aspect, znear, zfar):
+    """glm::perspectiveRH_ZO as column-major float[16] — the projection the synthetic camera uses (csrc/synth_scene.cu)."""
+    t = np.tan(float(fovy) / 2.0)
+    m = np.zeros(16, dtype=np.float64)
+    m[0], m[5], m[10], m[11], m[14] = 1.0 / (float(aspect) * t), 1.0 / t, zfar / (znear - zfar), -1.0, -(zfar * znear) / (zfar - znear)
+    return (C.c_float * 16)(*m.astype(np.float32))

@@ -44,6 +44,8 @@ lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 lib.vkr_app_bind_gbuffer.restype = C.c_int
 lib.vkr_app_bind_gbuffer.argtypes = [C.c_void_p] + [C.POINTER(vkr.VkrImage)] * 5
 lib.vkr_app_task_timing.restype = C.c_int
+lib.vkr_app_alt_params.restype = C.c_int
+lib.vkr_app_alt_params.argtypes = [C.c_void_p, C.POINTER(vkr.SsaoParams), C.POINTER(vkr.SsrParams)]
 lib.vkr_app_task_timing.argtypes = [C.c_void_p, C.c_int]
 lib.vkr_app_task_times.restype = C.c_int
 lib.vkr_app_task_times.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.c_uint32]
@@ -112,6 +114,12 @@ class App:
 
     def set_option(self, name, value):
         _check(lib.vkr_app_set_option(self.h, name.encode(), float(value)))
+
+    def alt_params(self):
+        """Parameter blocks the optional SSAO / SSR tasks of the last frame received (options alt.ssao / alt.ssr)."""
+        a, r = vkr.SsaoParams(), vkr.SsrParams()
+        _check(lib.vkr_app_alt_params(self.h, C.byref(a), C.byref(r)))
+        return a, r
 
     def last_tasks(self):
         return lib.vkr_app_last_tasks(self.h).decode().split()
