@@ -56,7 +56,8 @@ int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao
 
 /* Descriptor of a named image AS OF THE LAST RENDERED FRAME (the ping-pong remaps are undone in the
  * lookup): albedo normal material velocity depth prev_depth dn dv rays raw filtered accumulated_ao
- * reflections blurred color taa pdf brdf ssao ssr_legacy. */
+ * reflections blurred color taa pdf brdf ssao ssr_legacy
+ * st_raw st_filtered st_accumulated. */
 int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out);
 /* Asynchronous device->host copy of the whole allocation of a named image (all mips). */
 int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes);
@@ -67,6 +68,8 @@ const char* vkr_app_last_tasks(VkrApp* app);
 /* The parameter blocks the optional "SSAO" / "SSR" tasks of the last frame were given (options alt.ssao / alt.ssr; the
  * passes of reference src/ssao.cpp and src/ssr.cpp, which the reference's frame loop does not schedule). */
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out);
+/* Likewise for the "ScreenTrace" task (option alt.screen_trace; reference src/screen_trace.cpp). */
+int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out);
 /* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the
  * whole DownsamplePass instead of the per-task calls. */
 int vkr_app_set_option(VkrApp* app, const char* name, float value);

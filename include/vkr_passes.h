@@ -142,6 +142,14 @@ typedef struct VkrSsrParams {
   float fovy, aspect, znear, zfar;
 } VkrSsrParams;
 
+/* ScreenSpaceTrace: GpuParams of add_main_pass (reference src/screen_trace.cpp:31-39).  random_offset and the random part
+ * of angle_offset come from the pass's std::default_random_engine in the reference (:49-54); here they are inputs. */
+typedef struct VkrScreenTraceParams {
+  float normal_mat[16];
+  float random_offset, angle_offset;
+  float fovy, aspect, znear, zfar;
+} VkrScreenTraceParams;
+
 /* ---- extended launches: array layers and row windows ------------------------------------
  * Every pass entry has an `_ex` twin taking a VkrLaunchExt (NULL = the plain call):
  *  - layers > 1: each VkrImage argument describes layer 0 of an array image whose layers lie
@@ -258,6 +266,18 @@ int vkr_ssao(const VkrSsaoParams* p, const VkrImage* depth, const VkrImage* out_
 int vkr_ssr_legacy(const VkrSsrParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* frame,
                    const VkrImage* material, const VkrImage* out_reflection, void* stream);
 
+/* Tasks "ScreenTrace", "ScreenTraceFilter", "ScreenTraceAccumulate" (reference src/screen_trace.cpp:23-99, :101-139,
+ * :141-180; shaders/screen_trace/{trace,filter,accumulate}.comp).  depth / prev_depth: mip 0 is read; color = the lit frame
+ * (R8G8B8A8_SRGB or R16G16B16A16_SFLOAT); raw / filtered / accumulated are R16G16B16A16_SFLOAT (:4-9), accumulated is
+ * read-modify-write.  Like the reference's dispatches, only floor(W/8) x floor(H/8) tiles (main) and
+ * floor(W/8)*8 x floor(H/4)*4 pixels (filter, accumulate) are written.  The tile exchange of trace.comp:305-306 (no
+ * barrier() in the reference) is executed as if barriered; sky pixels publish "no hit" (csrc/screen_trace.cu header). */
+int vkr_screen_trace_main(const VkrScreenTraceParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* color,
+                          const VkrImage* material, const VkrImage* out_raw, void* stream);
+int vkr_screen_trace_filter(float znear, float zfar, const VkrImage* raw, const VkrImage* depth, const VkrImage* out_filtered, void* stream);
+int vkr_screen_trace_accumulate(const float* fovy_aspect_znear_zfar, const VkrImage* depth, const VkrImage* prev_depth,
+                                const VkrImage* filtered, const VkrImage* accumulated, void* stream);
+
 /* ---- _ex twins (see VkrLaunchExt) ---------------------------------------------------- */
 int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity, const VkrImage* out_normal,
                      const VkrImage* out_velocity, const VkrLaunchExt* ext, void* stream);
@@ -287,6 +307,12 @@ int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history, const Vkr
 int vkr_ssao_ex(const VkrSsaoParams* p, const VkrImage* depth, const VkrImage* out_occlusion, const VkrLaunchExt* ext, void* stream);
 int vkr_ssr_legacy_ex(const VkrSsrParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* frame,
                       const VkrImage* material, const VkrImage* out_reflection, const VkrLaunchExt* ext, void* stream);
+int vkr_screen_trace_main_ex(const VkrScreenTraceParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* color,
+                             const VkrImage* material, const VkrImage* out_raw, const VkrLaunchExt* ext, void* stream);
+int vkr_screen_trace_filter_ex(float znear, float zfar, const VkrImage* raw, const VkrImage* depth, const VkrImage* out_filtered,
+                               const VkrLaunchExt* ext, void* stream);
+int vkr_screen_trace_accumulate_ex(const float* fovy_aspect_znear_zfar, const VkrImage* depth, const VkrImage* prev_depth,
+                                   const VkrImage* filtered, const VkrImage* accumulated, const VkrLaunchExt* ext, void* stream);
 
 #ifdef __cplusplus
 }

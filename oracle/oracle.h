@@ -98,6 +98,13 @@ typedef struct OrcSsrParams {
   float fovy, aspect, znear, zfar;
 } OrcSsrParams;
 
+/* GpuParams of ScreenSpaceTrace::add_main_pass (reference src/screen_trace.cpp:31-39). */
+typedef struct OrcScreenTraceParams {
+  float normal_mat[16];
+  float random_offset, angle_offset;
+  float fovy, aspect, znear, zfar;
+} OrcScreenTraceParams;
+
 void orc_set_threads(int n);
 int  orc_get_max_threads(void);
 
@@ -141,6 +148,13 @@ int orc_taa_resolve(const OrcTaaParams* p, const OrcImage* history, const OrcIma
 int orc_ssao(const OrcSsaoParams* p, const OrcImage* depth, const OrcImage* out_r8, int y0, int y1);
 int orc_ssr_legacy(const OrcSsrParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* frame,
                    const OrcImage* material, const OrcImage* out_rgba8, int y0, int y1);
+
+/* ScreenSpaceTrace: reference shaders/screen_trace/{trace,filter,accumulate}.comp */
+int orc_screen_trace_main(const OrcScreenTraceParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* color,
+                          const OrcImage* material, const OrcImage* out_raw, int y0, int y1);
+int orc_screen_trace_filter(float znear, float zfar, const OrcImage* raw, const OrcImage* depth, const OrcImage* out_filtered, int y0, int y1);
+int orc_screen_trace_accumulate(const float* fovy_aspect_znear_zfar, const OrcImage* depth, const OrcImage* prev_depth,
+                                const OrcImage* filtered, const OrcImage* accumulated, int y0, int y1);
 
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);

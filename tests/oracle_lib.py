@@ -57,6 +57,9 @@ _sig("orc_deferred_shading", C.POINTER(vkr.ShadingParams), IP, IP, IP, IP, IP, I
 _sig("orc_taa_resolve", C.POINTER(vkr.TaaParams), IP, IP, IP, IP, IP, IP, I, I)
 _sig("orc_ssao", C.POINTER(vkr.SsaoParams), IP, IP, I, I)
 _sig("orc_ssr_legacy", C.POINTER(vkr.SsrParams), IP, IP, IP, IP, IP, I, I)
+_sig("orc_screen_trace_main", C.POINTER(vkr.ScreenTraceParams), IP, IP, IP, IP, IP, I, I)
+_sig("orc_screen_trace_filter", C.c_float, C.c_float, IP, IP, IP, I, I)
+_sig("orc_screen_trace_accumulate", FP, IP, IP, IP, IP, I, I)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

@@ -160,3 +160,107 @@ def test_host_app_runs_the_alt_passes(cuda):
         assert (d > 1).mean() <= 1e-4 and (d > 0).mean() <= 1e-3
         oc.end_frame()
     app.close()
+
+
+# ---- ScreenSpaceTrace (reference src/screen_trace.cpp) -------------------------------------------------------------------
+def _st_params(P, angle=0.3, rnd=0.37):
+    p = vkr.ScreenTraceParams()
+    C.memmove(p.normal_mat, P["trace"].normal_mat, 64)
+    p.random_offset, p.angle_offset = rnd, angle
+    p.fovy, p.aspect, p.znear, p.zfar = P["trace"].fovy, P["trace"].aspect, P["trace"].znear, P["trace"].zfar
+    return p
+
+
+def _st_compare(got, ref):
+    """fp16 RGBA: a march that breaks / hits one sample earlier on a last-place difference changes the pixel (and its 3x3
+    tile neighbours' gather) visibly, so the bar is a fraction of pixels: |diff| <= 2e-3 on >= 99.9 %."""
+    g, r = got.astype(np.float32), ref.astype(np.float32)
+    assert (np.isnan(g) == np.isnan(r)).mean() >= 0.9999
+    d = np.abs(np.nan_to_num(g) - np.nan_to_num(r)).max(axis=-1)
+    return float((d > 2e-3).mean()), float(d.max())
+
+
+@pytest.mark.parametrize("w,h,color_name", [(320, 180, "color"), (250, 132, "taa"), (1280, 720, "color")])
+def test_screen_trace_chain_matches_oracle(cuda, w, h, color_name):
+    import torch
+    imgs, P = _oracle_frame(w, h, frames=2)
+    p = _st_params(P)
+    F = vkr.R16G16B16A16_SFLOAT
+    ref = {k: vkr.Image(w, h, F, device="cpu") for k in ("raw", "filtered", "acc")}
+    got = {k: vkr.Image(w, h, F) for k in ("raw", "filtered", "acc")}
+    dev = {k: imgs[k].clone_to("cuda") for k in ("depth", "prev_depth", "normal", "material", color_name)}
+    cam = np.array([p.fovy, p.aspect, p.znear, p.zfar], dtype=np.float32)
+    for it in range(2):                                    # second iteration accumulates over the first (static camera -> blends)
+        orc.ok(orc.lib.orc_screen_trace_main(C.byref(p), imgs["depth"].ptr, imgs["normal"].ptr, imgs[color_name].ptr, imgs["material"].ptr, ref["raw"].ptr, 0, 0))
+        orc.ok(orc.lib.orc_screen_trace_filter(p.znear, p.zfar, ref["raw"].ptr, imgs["depth"].ptr, ref["filtered"].ptr, 0, 0))
+        prev = imgs["depth"] if it else imgs["prev_depth"]
+        orc.ok(orc.lib.orc_screen_trace_accumulate(orc.fptr(cam), imgs["depth"].ptr, prev.ptr, ref["filtered"].ptr, ref["acc"].ptr, 0, 0))
+        vkr.screen_trace_main(p, dev["depth"], dev["normal"], dev[color_name], dev["material"], got["raw"])
+        vkr.screen_trace_filter(p.znear, p.zfar, got["raw"], dev["depth"], got["filtered"])
+        vkr.screen_trace_accumulate(cam, dev["depth"], dev["depth"] if it else dev["prev_depth"], got["filtered"], got["acc"])
+        torch.cuda.synchronize()
+        r = ref["raw"].download().astype(np.float32)
+        assert (r[..., 3] > 0.05).mean() > 0.5 and (r[..., :3].max(axis=-1) > 0).mean() > 0.01, "AO and gathered colour should both be populated"
+        for k in ("raw", "filtered", "acc"):
+            frac, dmax = _st_compare(got[k].download(), ref[k].download())
+            assert frac <= 1e-3, (it, k, frac, dmax)
+    # the filter and the accumulation alone, on identical inputs, are exact arithmetic: bit-identical fp16
+    got["raw"].buf.copy_(ref["raw"].buf)
+    vkr.screen_trace_filter(p.znear, p.zfar, got["raw"], dev["depth"], got["filtered"])
+    torch.cuda.synchronize()
+    a, b = got["filtered"].download().view(np.uint16), ref["filtered"].download().view(np.uint16)
+    assert (a != b).mean() <= 1e-5, (a != b).sum()
+
+
+def test_screen_trace_row_windows(cuda):
+    import torch
+    w, h = 256, 160
+    imgs, P = _oracle_frame(w, h)
+    p = _st_params(P)
+    F = vkr.R16G16B16A16_SFLOAT
+    dev = {k: imgs[k].clone_to("cuda") for k in ("depth", "prev_depth", "normal", "material", "color")}
+    cam = np.array([p.fovy, p.aspect, p.znear, p.zfar], dtype=np.float32)
+    whole = {k: vkr.Image(w, h, F) for k in ("raw", "filtered", "acc")}
+    part = {k: vkr.Image(w, h, F) for k in ("raw", "filtered", "acc")}
+    vkr.screen_trace_main(p, dev["depth"], dev["normal"], dev["color"], dev["material"], whole["raw"])
+    vkr.screen_trace_filter(p.znear, p.zfar, whole["raw"], dev["depth"], whole["filtered"])
+    vkr.screen_trace_accumulate(cam, dev["depth"], dev["depth"], whole["filtered"], whole["acc"])
+    mid = (h // 2) // vkr.ROW_ALIGN * vkr.ROW_ALIGN
+    for rows in ((0, mid), (mid, h)):
+        vkr.screen_trace_main(p, dev["depth"], dev["normal"], dev["color"], dev["material"], part["raw"], ext=vkr.make_ext([], rows=rows))
+    for rows in ((0, mid), (mid, h)):
+        vkr.screen_trace_filter(p.znear, p.zfar, part["raw"], dev["depth"], part["filtered"], ext=vkr.make_ext([], rows=rows))
+    for rows in ((0, mid), (mid, h)):
+        vkr.screen_trace_accumulate(cam, dev["depth"], dev["depth"], part["filtered"], part["acc"], ext=vkr.make_ext([], rows=rows))
+    torch.cuda.synchronize()
+    for k in whole:
+        assert torch.equal(whole[k].buf, part[k].buf), k
+
+
+def test_host_app_runs_screen_trace(cuda):
+    w, h = 320, 176
+    scene = vkr.synth_scene(0, 32)
+    app = vkr_host.App(w, h, device=0)
+    app.set_option("alt.screen_trace", 1)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=1024)
+    F = vkr.R16G16B16A16_SFLOAT
+    ref = {k: vkr.Image(w, h, F, device="cpu") for k in ("raw", "filtered", "acc")}
+    for f in range(2):
+        dp = vkr.synth_camera(0, f, w, h, True)
+        P = oc.begin_frame(scene)
+        app.upload_gbuffer(oc.gb)
+        app.render_frame(dp, chain.angle_jitter(f))
+        oc.passes(P)
+        im = oc.images()
+        assert app.last_tasks()[-3:] == ["ScreenTrace", "ScreenTraceFilter", "ScreenTraceAccumulate"]
+        p = app.screen_trace_params()
+        color_dev = app.readback("color")
+        cam = np.array([p.fovy, p.aspect, p.znear, p.zfar], dtype=np.float32)
+        orc.ok(orc.lib.orc_screen_trace_main(C.byref(p), im["depth"].ptr, im["normal"].ptr, color_dev.ptr, im["material"].ptr, ref["raw"].ptr, 0, 0))
+        orc.ok(orc.lib.orc_screen_trace_filter(p.znear, p.zfar, ref["raw"].ptr, im["depth"].ptr, ref["filtered"].ptr, 0, 0))
+        orc.ok(orc.lib.orc_screen_trace_accumulate(orc.fptr(cam), im["depth"].ptr, im["prev_depth"].ptr, ref["filtered"].ptr, ref["acc"].ptr, 0, 0))
+        for k, name in (("raw", "st_raw"), ("filtered", "st_filtered"), ("acc", "st_accumulated")):
+            frac, dmax = _st_compare(app.readback(name).download(), ref[k].download())
+            assert frac <= 1e-3, (f, k, frac, dmax)
+        oc.end_frame()
+    app.close()

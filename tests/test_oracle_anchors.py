@@ -300,3 +300,68 @@ def test_ssr_legacy_floor_reflects_a_constant_frame_with_ggx_weight():
     full = inner & (err < 1.5 / 255)                               # pixels whose hit is inside the band-free region
     assert full.sum() > 0.5 * inner.sum(), (full.sum(), inner.sum())
     assert (got[ys, xs, 0][inner] <= expect[inner] + 1.5 / 255).all()   # the fade only ever darkens
+
+
+# ---- (viii) ScreenSpaceTrace ------------------------------------------------------------------------------------
+def _st_params(aspect, angle=0.125, rnd=0.3):
+    p = vkr.ScreenTraceParams()
+    C.memmove(p.normal_mat, ident16(), 64)
+    p.random_offset, p.angle_offset = rnd, angle
+    p.fovy, p.aspect, p.znear, p.zfar = FOVY, aspect, ZN, ZF
+    return p
+
+
+def test_screen_trace_flat_plane_is_unoccluded_and_gathers_nothing():
+    """Fronto-parallel plane: every depth sample lies in the tangent plane, so h_cos = 0, h = pi/2 and
+    a = 2 * 0.25 * (1 - cos(pi)) = 1; the ray leaves the surface towards the camera and never hits (trace.comp:262-287)."""
+    w, h = 200, 100                                        # not multiples of 8: the last columns / rows stay untouched
+    gb, _ = flat_gbuffer(w, h, -5.0)
+    d = gb.depth.download(0)
+    d[:9, :] = 0xFFFFFF                                    # sky strip (the bilinear footprint of row 9 still touches it)
+    gb.depth.upload(d, 0)
+    color = vkr.Image(w, h, vkr.R8G8B8A8_SRGB, device="cpu")
+    color.upload(np.full((h, w, 4), 200, dtype=np.uint8))
+    raw = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    raw.upload(np.full((h, w, 4), 7.0, dtype=np.float16))
+    orc.ok(orc.lib.orc_screen_trace_main(C.byref(_st_params(w / h)), gb.depth.ptr, gb.normal.ptr, color.ptr, gb.material.ptr, raw.ptr, 0, 0))
+    out = raw.download().astype(np.float32)
+    cw, ch = w // 8 * 8, h // 8 * 8
+    assert (out[ch:, :] == 7.0).all() and (out[:, cw:] == 7.0).all()          # outside the dispatched tiles
+    assert (out[:8, :cw] == [0, 0, 0, 1]).all()                                # sky
+    body = out[16:ch, :cw]
+    assert (body[..., :3] == 0).all()
+    assert np.abs(body[..., 3] - 1.0).max() < 2e-3, np.abs(body[..., 3] - 1.0).max()
+
+
+def test_screen_trace_filter_and_accumulate_fixed_points():
+    """filter.comp: constant raw over a constant-depth plane stays constant in the interior.  View-space z is negative, so
+    the weight 1 - |dz| / (0.1 z) GROWS with the depth difference (:31, as written in the reference): out-of-image taps
+    (depth 0, raw 0) get weight 1 + 4.95/0.5 = 10.9 and dilute the two border rows / columns towards 0.
+    accumulate.comp: identical depth and prev_depth blend 5 % per frame -> c (1 - 0.95^k); a changed depth or a sky
+    prev_depth takes the new value."""
+    w, h = 64, 32
+    gb, k = flat_gbuffer(w, h, -5.0)
+    raw = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    raw.upload(np.full((h, w, 4), 0.5, dtype=np.float16))
+    filt = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    orc.ok(orc.lib.orc_screen_trace_filter(ZN, ZF, raw.ptr, gb.depth.ptr, filt.ptr, 0, 0))
+    f = filt.download().astype(np.float32)
+    assert (f[2:-1, 2:-1] == 0.5).all()
+    assert (f[:2] < 0.5).all() and (f[-1] < 0.5).all() and (f[:, :2] < 0.5).all() and (f[:, -1] < 0.5).all()
+    edge = 0.5 * 12 / (12 + 4 * np.float32(10.9))           # a top-row interior pixel: 4 of its 16 taps are out of the image
+    assert abs(f[1, 10, 0] - edge) < 2e-3, (f[1, 10, 0], edge)
+    filt.upload(np.full((h, w, 4), 0.5, dtype=np.float16))
+    acc = vkr.Image(w, h, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    pd = gb.prev_depth.download(0)
+    pd[:4, :] = k + 1000                                   # moved surface
+    pd[4:8, :] = 0xFFFFFF                                  # sky last frame
+    gb.prev_depth.upload(pd, 0)
+    cam = f32(FOVY, w / h, ZN, ZF)
+    want = 0.0
+    for it in range(5):
+        orc.ok(orc.lib.orc_screen_trace_accumulate(orc.fptr(cam), gb.depth.ptr, gb.prev_depth.ptr, filt.ptr, acc.ptr, 0, 0))
+        want = float(np.float16(np.float32(want) * np.float32(1 - 0.05) + np.float32(0.5) * np.float32(0.05)))
+        a = acc.download().astype(np.float32)
+        assert (a[:8] == 0.5).all()
+        assert np.abs(a[8:] - want).max() <= 1e-3, (it, a[8:].max(), want)
+    assert abs(want - 0.5 * (1 - 0.95 ** 5)) < 2e-3

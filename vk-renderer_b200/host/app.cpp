@@ -44,7 +44,8 @@ struct VkrApp {
   // the earlier AO / reflection passes (src/ssao.cpp, src/ssr.cpp): in the reference tree but not in its frame loop, so off by default
   ImageResourceId ssao_tex, ssr_tex;
   SSAOPass ssao_pass;
-  bool alt_ssao = false, alt_ssr = false;
+  ScreenSpaceTrace screen_trace;
+  bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false;
   VkrSsrParams last_ssr{};
   std::string task_names;
   uint64_t frames = 0;
@@ -53,7 +54,8 @@ struct VkrApp {
       : width{w}, height{h}, render_graph{device, stream}, gbuffer{render_graph, w, h}, downsample_pass{},
         gtao{render_graph, w, h, /*USE_RAY_QUERY*/ false, /*half_res*/ true},                   // main.cpp:265
         ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph},
-        ssao_tex{create_ssao_texture(render_graph, w, h)}, ssr_tex{create_ssr_tex(render_graph, w, h)}, ssao_pass{render_graph, ssao_tex, 0} {
+        ssao_tex{create_ssao_texture(render_graph, w, h)}, ssr_tex{create_ssr_tex(render_graph, w, h)}, ssao_pass{render_graph, ssao_tex, 0},
+        screen_trace{render_graph, w, h} {
     ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
     ssr.preintegrate_brdf(render_graph);
     gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
@@ -100,6 +102,14 @@ struct VkrApp {
       last_ssr.fovy = fovy; last_ssr.aspect = aspect; last_ssr.znear = znear; last_ssr.zfar = zfar;
       add_ssr_pass(render_graph, gbuffer.depth, gbuffer.normal, color_out_tex, gbuffer.material, ssr_tex, rp);
     }
+    if (alt_screen_trace) {
+      ScreenTraceParams tp{normal_mat, fovy, aspect, znear, zfar};
+      screen_trace.next_angle_random = angle_jitter + 0.5f;        // the same uniform the GTAO angle uses this frame
+      screen_trace.next_random_offset = 0.25f * (float)(frames & 3);
+      screen_trace.add_main_pass(render_graph, tp, gbuffer.depth, gbuffer.normal, color_out_tex, gbuffer.material);
+      screen_trace.add_filter_pass(render_graph, tp, gbuffer.depth);
+      screen_trace.add_accumulate_pass(render_graph, tp, gbuffer.depth, gbuffer.prev_depth);
+    }
     render_graph.submit();                                                                        // :402
     task_names.clear();
     for (auto& n : render_graph.last_task_names()) { task_names += n; task_names += '\n'; }
@@ -136,6 +146,9 @@ struct VkrApp {
     else if (name == "brdf") id = ssr.get_preintegrated_brdf();
     else if (name == "ssao") id = ssao_tex;
     else if (name == "ssr_legacy") id = ssr_tex;
+    else if (name == "st_raw") id = screen_trace.raw;
+    else if (name == "st_filtered") id = screen_trace.filtered;
+    else if (name == "st_accumulated") id = screen_trace.accumulated;
     else return false;
     return true;
   }
@@ -253,6 +266,12 @@ int vkr_app_sync(VkrApp* app) {
   VKR_TRY(app->render_graph.wait_idle())
 }
 
+int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out) {
+  if (!app || !out) { host_error("screen_trace_params: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  *out = app->screen_trace.last_block;
+  return VKR_OK;
+}
+
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out) {
   if (!app) { host_error("alt_params: null app"); return VKR_ERR_INVALID_ARGUMENT; }
   if (ssao_out) *ssao_out = app->ssao_pass.last_block;
@@ -280,6 +299,7 @@ int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   else if (n == "ssr.max_accumulated_rays") app->ssr.settings.max_accumulated_rays = (int)v;
   else if (n == "alt.ssao") app->alt_ssao = v != 0.f;
   else if (n == "alt.ssr") app->alt_ssr = v != 0.f;
+  else if (n == "alt.screen_trace") app->alt_screen_trace = v != 0.f;
   else if (n == "alt.ssao_reference_packing") app->ssao_pass.reference_packing = v != 0.f;
   else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
   else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;

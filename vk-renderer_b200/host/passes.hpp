@@ -9,6 +9,7 @@
 //   TAA                                      src/taa.hpp:8-21
 //   SSAOPass, SSAOInParams, create_ssao_texture   src/ssao.hpp:7-31
 //   SSRParams, add_ssr_pass, create_ssr_tex       src/ssr.hpp:7-26
+//   ScreenSpaceTrace, ScreenTraceParams            src/screen_trace.hpp:8-51
 // Dropped: pipelines / samplers / descriptor sets (no graphics API), the SDL_Window* of
 // DeferedShadingPass (ImGui only), ray-query and graphics-pipeline GTAO variants, ImGui panels.
 #pragma once
@@ -220,3 +221,33 @@ struct SSRParams {
 
 void add_ssr_pass(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId depth, rendergraph::ImageResourceId normal,
                   rendergraph::ImageResourceId color, rendergraph::ImageResourceId material, rendergraph::ImageResourceId out, const SSRParams& params);
+
+struct ScreenTraceParams {
+  glm::mat4 normal_mat;
+  float fovy;
+  float aspect;
+  float znear;
+  float zfar;
+};
+
+struct ScreenSpaceTrace {
+  ScreenSpaceTrace(rendergraph::RenderGraph& graph, uint32_t width, uint32_t height);
+
+  void add_main_pass(rendergraph::RenderGraph& graph, const ScreenTraceParams& params, rendergraph::ImageResourceId depth,
+                     rendergraph::ImageResourceId normal, rendergraph::ImageResourceId color, rendergraph::ImageResourceId material);
+  void add_filter_pass(rendergraph::RenderGraph& graph, const ScreenTraceParams& params, rendergraph::ImageResourceId depth);
+  void add_accumulate_pass(rendergraph::RenderGraph& graph, const ScreenTraceParams& params, rendergraph::ImageResourceId depth,
+                           rendergraph::ImageResourceId prev_depth);
+
+  rendergraph::ImageResourceId raw;
+  rendergraph::ImageResourceId filtered;
+  rendergraph::ImageResourceId accumulated;
+
+  // The reference draws both from std::default_random_engine inside add_main_pass (src/screen_trace.cpp:49-54); here the
+  // two uniforms in [0,1) of the next call are inputs so runs are reproducible.
+  float next_angle_random = 0.5f, next_random_offset = 0.f;
+  VkrScreenTraceParams last_block{};   // the block of the most recent add_main_pass()
+
+ private:
+  uint32_t frame_count = 0;
+};

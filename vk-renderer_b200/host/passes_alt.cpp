@@ -88,3 +88,68 @@ void add_ssr_pass(RenderGraph& graph, ImageResourceId depth, ImageResourceId nor
                                resources.get_image(input.material), resources.get_image(input.rt), cmd.stream), "SSR");
     });
 }
+
+// ---- ScreenSpaceTrace (reference src/screen_trace.cpp) ----------------------------------------------------------
+ScreenSpaceTrace::ScreenSpaceTrace(RenderGraph& graph, uint32_t width, uint32_t height) {                         // :3-21
+  gpu::ImageInfo info; info.format = VKR_FORMAT_R16G16B16A16_SFLOAT; info.width = width; info.height = height;
+  raw = graph.create_image(info);
+  filtered = graph.create_image(info);
+  accumulated = graph.create_image(info);
+}
+
+void ScreenSpaceTrace::add_main_pass(RenderGraph& graph, const ScreenTraceParams& params, ImageResourceId depth, ImageResourceId normal,
+                                     ImageResourceId color, ImageResourceId material) {
+  struct PassData { ImageViewId out, depth, norm, color, material; };
+  const float angle_offsets[]{60.f, 300.f, 180.f, 240.f, 120.f, 0.f, 300.f, 60.f, 180.f, 120.f, 240.f, 0.f};       // :47-54
+  float base_angle = angle_offsets[frame_count % (sizeof(angle_offsets) / sizeof(float))] / 360.f;
+  base_angle += next_angle_random - 0.5f;
+  frame_count += 1;
+  VkrScreenTraceParams block{};
+  copy_mat(block.normal_mat, params.normal_mat);
+  block.random_offset = next_random_offset; block.angle_offset = base_angle;
+  block.fovy = params.fovy; block.aspect = params.aspect; block.znear = params.znear; block.zfar = params.zfar;
+  last_block = block;
+  graph.add_task<PassData>("ScreenTrace",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, 0, 1, 0, 1);
+      input.norm = builder.sample_image(normal);
+      input.color = builder.sample_image(color);
+      input.material = builder.sample_image(material);
+      input.out = builder.use_storage_image(raw, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_screen_trace_main(&block, resources.get_image(input.depth), resources.get_image(input.norm), resources.get_image(input.color),
+                                      resources.get_image(input.material), resources.get_image(input.out), cmd.stream), "ScreenTrace");
+    });
+}
+
+void ScreenSpaceTrace::add_filter_pass(RenderGraph& graph, const ScreenTraceParams& params, ImageResourceId depth) {
+  struct PassData { ImageViewId depth, raw, filtered; };
+  const float znear = params.znear, zfar = params.zfar;                                                            // :117
+  graph.add_task<PassData>("ScreenTraceFilter",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, 0, 1, 0, 1);
+      input.raw = builder.sample_image(raw);
+      input.filtered = builder.use_storage_image(filtered, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_screen_trace_filter(znear, zfar, resources.get_image(input.raw), resources.get_image(input.depth), resources.get_image(input.filtered),
+                                        cmd.stream), "ScreenTraceFilter");
+    });
+}
+
+void ScreenSpaceTrace::add_accumulate_pass(RenderGraph& graph, const ScreenTraceParams& params, ImageResourceId depth, ImageResourceId prev_depth) {
+  struct PassData { ImageViewId depth, prev_depth, filtered, accum; };
+  struct Pc { float v[4]; } pc{{params.fovy, params.aspect, params.znear, params.zfar}};                           // :160
+  graph.add_task<PassData>("ScreenTraceAccumulate",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, 0, 1, 0, 1);
+      input.prev_depth = builder.sample_image(prev_depth, 0, 1, 0, 1);
+      input.filtered = builder.sample_image(filtered);
+      input.accum = builder.use_storage_image(accumulated, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_screen_trace_accumulate(pc.v, resources.get_image(input.depth), resources.get_image(input.prev_depth), resources.get_image(input.filtered),
+                                            resources.get_image(input.accum), cmd.stream), "ScreenTraceAccumulate");
+    });
+}

@@ -77,6 +77,11 @@ class SsaoParams(C.Structure):
                 ("samples", (C.c_float * 4) * 16)]
 
 
+class ScreenTraceParams(C.Structure):
+    _fields_ = [_mat("normal_mat"), ("random_offset", C.c_float), ("angle_offset", C.c_float), ("fovy", C.c_float), ("aspect", C.c_float),
+                ("znear", C.c_float), ("zfar", C.c_float)]
+
+
 class SsrParams(C.Structure):
     _fields_ = [_mat("normal_mat"), ("fovy", C.c_float), ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float)]
 
@@ -390,6 +395,9 @@ _sig("vkr_gtao_filter_ex", PT(GtaoParams), IP, IP, IP, C.c_uint32, EP, VP)
 _sig("vkr_gtao_accumulate_ex", PT(AccumParams), IP, IP, IP, IP, IP, IP, C.c_uint32, EP, VP)
 _sig("vkr_deferred_shading_ex", PT(ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, EP, VP)
 _sig("vkr_taa_resolve_ex", PT(TaaParams), IP, IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_screen_trace_main_ex", PT(ScreenTraceParams), IP, IP, IP, IP, IP, EP, VP)
+_sig("vkr_screen_trace_filter_ex", C.c_float, C.c_float, IP, IP, IP, EP, VP)
+_sig("vkr_screen_trace_accumulate_ex", PT(C.c_float), IP, IP, IP, IP, EP, VP)
 _sig("vkr_ssao", PT(SsaoParams), IP, IP, VP)
 _sig("vkr_ssao_ex", PT(SsaoParams), IP, IP, EP, VP)
 _sig("vkr_ssr_legacy", PT(SsrParams), IP, IP, IP, IP, IP, VP)
@@ -503,6 +511,23 @@ def ssao(p, depth, out, ext=None, stream=None):
 def ssr_legacy(p, depth, normal, frame, material, out, ext=None, stream=None):
     check(lib.vkr_ssr_legacy_ex(_p(p), depth.ptr, normal.ptr, frame.ptr, material.ptr, out.ptr, C.byref(ext) if ext is not None else None,
                                 stream_ptr(stream)))
+
+
+def _e(ext):
+    return C.byref(ext) if ext is not None else None
+
+
+def screen_trace_main(p, depth, normal, color, material, raw, ext=None, stream=None):
+    check(lib.vkr_screen_trace_main_ex(_p(p), depth.ptr, normal.ptr, color.ptr, material.ptr, raw.ptr, _e(ext), stream_ptr(stream)))
+
+
+def screen_trace_filter(znear, zfar, raw, depth, filtered, ext=None, stream=None):
+    check(lib.vkr_screen_trace_filter_ex(znear, zfar, raw.ptr, depth.ptr, filtered.ptr, _e(ext), stream_ptr(stream)))
+
+
+def screen_trace_accumulate(fovy_aspect_znear_zfar, depth, prev_depth, filtered, accumulated, ext=None, stream=None):
+    f4 = (C.c_float * 4)(*fovy_aspect_znear_zfar)
+    check(lib.vkr_screen_trace_accumulate_ex(f4, depth.ptr, prev_depth.ptr, filtered.ptr, accumulated.ptr, _e(ext), stream_ptr(stream)))
 
 
 def sphere_samples(seed=0, count=16):

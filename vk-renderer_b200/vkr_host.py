@@ -44,6 +44,8 @@ lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 lib.vkr_app_bind_gbuffer.restype = C.c_int
 lib.vkr_app_bind_gbuffer.argtypes = [C.c_void_p] + [C.POINTER(vkr.VkrImage)] * 5
 lib.vkr_app_task_timing.restype = C.c_int
+lib.vkr_app_screen_trace_params.restype = C.c_int
+lib.vkr_app_screen_trace_params.argtypes = [C.c_void_p, C.POINTER(vkr.ScreenTraceParams)]
 lib.vkr_app_alt_params.restype = C.c_int
 lib.vkr_app_alt_params.argtypes = [C.c_void_p, C.POINTER(vkr.SsaoParams), C.POINTER(vkr.SsrParams)]
 lib.vkr_app_task_timing.argtypes = [C.c_void_p, C.c_int]
@@ -120,6 +122,11 @@ class App:
         a, r = vkr.SsaoParams(), vkr.SsrParams()
         _check(lib.vkr_app_alt_params(self.h, C.byref(a), C.byref(r)))
         return a, r
+
+    def screen_trace_params(self):
+        p = vkr.ScreenTraceParams()
+        _check(lib.vkr_app_screen_trace_params(self.h, C.byref(p)))
+        return p
 
     def last_tasks(self):
         return lib.vkr_app_last_tasks(self.h).decode().split()
