@@ -57,7 +57,7 @@ int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao
 /* Descriptor of a named image AS OF THE LAST RENDERED FRAME (the ping-pong remaps are undone in the
  * lookup): albedo normal material velocity depth prev_depth dn dv rays raw filtered accumulated_ao
  * reflections blurred color taa pdf brdf ssao ssr_legacy
- * st_raw st_filtered st_accumulated. */
+ * st_raw st_filtered st_accumulated gv_raw gv_filtered gv_output gv_deinterleaved (layer 0). */
 int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out);
 /* Asynchronous device->host copy of the whole allocation of a named image (all mips). */
 int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes);
@@ -68,6 +68,9 @@ const char* vkr_app_last_tasks(VkrApp* app);
 /* The parameter blocks the optional "SSAO" / "SSR" tasks of the last frame were given (options alt.ssao / alt.ssr; the
  * passes of reference src/ssao.cpp and src/ssr.cpp, which the reference's frame loop does not schedule). */
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out);
+/* Host-side state of the last frame by name: "gtao.angle_offset", "gv.angle_offset" (the angle push constants of the live GTAO
+ * and of the variant object behind option alt.gtao_variants). */
+int vkr_app_get_value(VkrApp* app, const char* name, float* out);
 /* Likewise for the "ScreenTrace" task (option alt.screen_trace; reference src/screen_trace.cpp). */
 int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out);
 /* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the

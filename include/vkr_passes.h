@@ -278,6 +278,24 @@ int vkr_screen_trace_filter(float znear, float zfar, const VkrImage* raw, const 
 int vkr_screen_trace_accumulate(const float* fovy_aspect_znear_zfar, const VkrImage* depth, const VkrImage* prev_depth,
                                 const VkrImage* filtered, const VkrImage* accumulated, void* stream);
 
+/* GTAO variants beside the live compute path.  p->angle_offset is the push constant; the MIS fields of VkrGtaoParams are not
+ * read.  `ext` (may be NULL) selects a row window; array layers are not supported by these four.
+ * Task "GTAO" (reference src/gtao.cpp:349-413 add_main_pass_graphics, gtao/main.frag): every pixel of raw, 1 slice x 20 taps;
+ * writes (occlusion, 0, 0, 1) — the reference's float fragment output leaves .gba of the RGBA16F attachment undefined. */
+int vkr_gtao_main_graphics(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* raw, uint32_t depth_lod,
+                           const VkrLaunchExt* ext, void* stream);
+/* Task "GTAO_deinterleave" (:445-472, gtao_opt/deinterleave.comp): out_array = R32_SFLOAT, 4^pattern_n layers layer_stride bytes
+ * apart.  As in the reference the dispatch covers the OUTPUT extent, so only that corner of the depth level is scattered. */
+int vkr_gtao_deinterleave(const VkrImage* depth, uint32_t depth_lod, const VkrImage* out_array, uint64_t layer_stride, int pattern_n, void* stream);
+/* Task "GTAO_deinterleaved" (:474-526, gtao_opt/main_deinterleaved.comp) for ONE array layer; the reference loops over the
+ * layers of its output image (one).  Invocation i of the dispatch over raw's extent writes pixel 2^n * i + layer offset. */
+int vkr_gtao_main_deinterleaved(const VkrGtaoParams* p, const VkrImage* depth_array, uint64_t layer_stride, const VkrImage* normal,
+                                const VkrImage* raw, int pattern_n, uint32_t layer, const VkrLaunchExt* ext, void* stream);
+/* Task "GTAO_reproject" (:241-284, gtao/reproject.comp in its STATIC_REPROJECT mode: the matrix of GTAOReprojection is unused).
+ * gtao = filtered, prev_gtao = prev_frame, out = output, all R16_SFLOAT. */
+int vkr_gtao_reproject(const float* fovy_aspect_znear_zfar, const VkrImage* depth, const VkrImage* prev_depth, uint32_t depth_lod,
+                       const VkrImage* gtao, const VkrImage* prev_gtao, const VkrImage* out, const VkrLaunchExt* ext, void* stream);
+
 /* ---- _ex twins (see VkrLaunchExt) ---------------------------------------------------- */
 int vkr_hiz_build_ex(const VkrImage* depth, const VkrImage* normal, const VkrImage* velocity, const VkrImage* out_normal,
                      const VkrImage* out_velocity, const VkrLaunchExt* ext, void* stream);

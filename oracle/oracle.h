@@ -156,6 +156,15 @@ int orc_screen_trace_filter(float znear, float zfar, const OrcImage* raw, const 
 int orc_screen_trace_accumulate(const float* fovy_aspect_znear_zfar, const OrcImage* depth, const OrcImage* prev_depth,
                                 const OrcImage* filtered, const OrcImage* accumulated, int y0, int y1);
 
+/* GTAO variants: reference shaders/gtao/{main.frag,reproject.comp}, shaders/gtao_opt/{deinterleave,main_deinterleaved}.comp.
+ * p->angle_offset is the push constant; the other OrcGtaoParams extras are ignored.  Array images: layer l at base + l * layer_stride. */
+int orc_gtao_main_graphics(const OrcGtaoParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* raw, uint32_t depth_lod, int y0, int y1);
+int orc_gtao_deinterleave(const OrcImage* depth, uint32_t depth_lod, const OrcImage* out_r32f_array, uint64_t layer_stride, int pattern_step);
+int orc_gtao_main_deinterleaved(const OrcGtaoParams* p, const OrcImage* depth_array, uint64_t layer_stride, const OrcImage* normal,
+                                const OrcImage* raw, int pattern_n, uint32_t layer, int y0, int y1);
+int orc_gtao_reproject(const float* fovy_aspect_znear_zfar, const OrcImage* depth, const OrcImage* prev_depth, uint32_t depth_lod,
+                       const OrcImage* gtao, const OrcImage* prev_gtao, const OrcImage* out, int y0, int y1);
+
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);
 void orc_probe_decode_normal(const float* uv2, float* out3);

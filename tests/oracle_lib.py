@@ -60,6 +60,10 @@ _sig("orc_ssr_legacy", C.POINTER(vkr.SsrParams), IP, IP, IP, IP, IP, I, I)
 _sig("orc_screen_trace_main", C.POINTER(vkr.ScreenTraceParams), IP, IP, IP, IP, IP, I, I)
 _sig("orc_screen_trace_filter", C.c_float, C.c_float, IP, IP, IP, I, I)
 _sig("orc_screen_trace_accumulate", FP, IP, IP, IP, IP, I, I)
+_sig("orc_gtao_main_graphics", C.POINTER(vkr.GtaoParams), IP, IP, IP, U, I, I)
+_sig("orc_gtao_deinterleave", IP, U, IP, C.c_uint64, I)
+_sig("orc_gtao_main_deinterleaved", C.POINTER(vkr.GtaoParams), IP, C.c_uint64, IP, IP, I, U, I, I)
+_sig("orc_gtao_reproject", FP, IP, IP, U, IP, IP, IP, I, I)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

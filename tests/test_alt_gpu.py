@@ -264,3 +264,108 @@ def test_host_app_runs_screen_trace(cuda):
             assert frac <= 1e-3, (f, k, frac, dmax)
         oc.end_frame()
     app.close()
+
+
+# ---- GTAO variants (reference src/gtao.cpp:241-284,:349-413,:445-526) ----------------------------------------------------
+def _gv_params(P, angle=0.21):
+    p = vkr.GtaoParams()
+    C.memmove(p.normal_mat, P["trace"].normal_mat, 64)
+    p.fovy, p.aspect, p.znear, p.zfar, p.angle_offset = P["trace"].fovy, P["trace"].aspect, P["trace"].znear, P["trace"].zfar, angle
+    return p
+
+
+def _ao_compare(got, ref):
+    """fp16 AO: |diff| <= 2e-3 except where a thickness break flipped on a last-place difference; returns that fraction."""
+    g, r = got.astype(np.float32), ref.astype(np.float32)
+    assert (np.isnan(g) == np.isnan(r)).mean() >= 0.9999
+    d = np.abs(np.nan_to_num(g) - np.nan_to_num(r))
+    return float((d > 2e-3).mean()), float(d.max())
+
+
+@pytest.mark.parametrize("w,h", [(320, 180), (1280, 720)])
+def test_gtao_variants_match_oracle(cuda, w, h):
+    import torch
+    imgs, P = _oracle_frame(w, h, frames=2)
+    p = _gv_params(P)
+    w2, h2 = w // 2, h // 2
+    dev = {k: imgs[k].clone_to("cuda") for k in ("depth", "prev_depth", "normal")}
+    # graphics main
+    ref_raw, got_raw = vkr.Image(w2, h2, vkr.R16G16B16A16_SFLOAT, device="cpu"), vkr.Image(w2, h2, vkr.R16G16B16A16_SFLOAT)
+    orc.ok(orc.lib.orc_gtao_main_graphics(C.byref(p), imgs["depth"].ptr, imgs["normal"].ptr, ref_raw.ptr, 1, 0, 0))
+    vkr.gtao_main_graphics(p, dev["depth"], dev["normal"], got_raw)
+    torch.cuda.synchronize()
+    r = ref_raw.download().astype(np.float32)
+    # (the variant's projected-normal angle uses normalize(end - pos) instead of the slice tangent: values above 1 and a few
+    #  NaN from acos of 1 + 1 ulp are what the formula gives)
+    assert 0.2 < np.nanmean(r[..., 0]) < 1.5 and np.nanstd(r[..., 0]) > 0.02 and np.isnan(r[..., 0]).mean() < 0.05
+    frac, dmax = _ao_compare(got_raw.download(), ref_raw.download())
+    assert frac <= 1e-3, (frac, dmax)
+    # deinterleave: pure data movement -> bit-exact
+    ref_arr = vkr.ImageArray(w2 // 4, h2 // 4, vkr.R32_SFLOAT, 1, layers=16, device="cpu")
+    got_arr = vkr.ImageArray(w2 // 4, h2 // 4, vkr.R32_SFLOAT, 1, layers=16)
+    orc.ok(orc.lib.orc_gtao_deinterleave(imgs["depth"].ptr, 1, ref_arr.ptr, ref_arr.layer_stride, 2))
+    vkr.gtao_deinterleave(dev["depth"], got_arr, 2)
+    torch.cuda.synchronize()
+    assert torch.equal(got_arr.buf.cpu(), ref_arr.buf)
+    assert (ref_arr.layer(5).download() > 0).any()
+    # deinterleaved main, two layers
+    for layer in (0, 6):
+        orc.ok(orc.lib.orc_gtao_main_deinterleaved(C.byref(p), ref_arr.ptr, ref_arr.layer_stride, imgs["normal"].ptr, ref_raw.ptr, 2, layer, 0, 0))
+        vkr.gtao_main_deinterleaved(p, got_arr, dev["normal"], got_raw, 2, layer)
+    torch.cuda.synchronize()
+    frac, dmax = _ao_compare(got_raw.download(), ref_raw.download())
+    assert frac <= 1e-3, (frac, dmax)
+    # reprojection: exact arithmetic -> bit-exact fp16
+    F = vkr.R16_SFLOAT
+    rng = np.random.default_rng(1)
+    ao_np, prev_np = rng.random((h2, w2)).astype(np.float16), rng.random((h2, w2)).astype(np.float16)
+    ao, prev, ref_out = vkr.Image(w2, h2, F, device="cpu"), vkr.Image(w2, h2, F, device="cpu"), vkr.Image(w2, h2, F, device="cpu")
+    ao.upload(ao_np); prev.upload(prev_np)
+    cam = np.array([p.fovy, p.aspect, p.znear, p.zfar], dtype=np.float32)
+    got_out = vkr.Image(w2, h2, F)
+    for pd_name in ("prev_depth", "depth"):              # a moving and a static previous frame
+        orc.ok(orc.lib.orc_gtao_reproject(orc.fptr(cam), imgs["depth"].ptr, imgs[pd_name].ptr, 1, ao.ptr, prev.ptr, ref_out.ptr, 0, 0))
+        vkr.gtao_reproject(cam, dev["depth"], dev[pd_name], ao.clone_to("cuda"), prev.clone_to("cuda"), got_out)
+        torch.cuda.synchronize()
+        assert np.array_equal(got_out.download().view(np.uint16), ref_out.download().view(np.uint16)), pd_name
+    assert (ref_out.download() != ao_np).mean() > 0.5    # static previous frame: most texels blended
+
+
+def test_host_app_runs_gtao_variants(cuda):
+    w, h = 320, 192
+    scene = vkr.synth_scene(0, 32)
+    app = vkr_host.App(w, h, device=0)
+    app.set_option("alt.gtao_variants", 1)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=1024)
+    w2, h2 = w // 2, h // 2
+    ref_raw = vkr.Image(w2, h2, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    ref_filt, ref_prev, ref_out = [vkr.Image(w2, h2, vkr.R16_SFLOAT, device="cpu") for _ in range(3)]
+    ref_arr = vkr.ImageArray(w2 // 4, h2 // 4, vkr.R32_SFLOAT, 1, layers=16, device="cpu")
+    for f in range(2):
+        dp = vkr.synth_camera(0, f, w, h, True)
+        P = oc.begin_frame(scene)
+        app.upload_gbuffer(oc.gb)
+        app.render_frame(dp, chain.angle_jitter(f))
+        oc.passes(P)
+        im = oc.images()
+        assert app.last_tasks()[-5:] == ["GTAO", "GTAO_filter", "GTAO_reproject", "GTAO_deinterleave", "GTAO_deinterleaved"]
+        # the variant object draws two angles per frame from the table (graphics main, then deinterleaved main)
+        jit = np.float32(chain.angle_jitter(f))
+        ang = [float(np.float32(np.float32(chain.ANGLE_TABLE[(2 * f + i) % 12]) / np.float32(360.0)) + jit) for i in range(2)]
+        assert app.get_value("gv.angle_offset") == ang[1]
+        p = _gv_params(P, ang[0])
+        cam = np.array([p.fovy, p.aspect, p.znear, p.zfar], dtype=np.float32)
+        orc.ok(orc.lib.orc_gtao_main_graphics(C.byref(p), im["depth"].ptr, im["normal"].ptr, ref_raw.ptr, 1, 0, 0))
+        orc.ok(orc.lib.orc_gtao_filter(C.byref(p), im["depth"].ptr, ref_raw.ptr, ref_filt.ptr, 1, 0, 0))
+        orc.ok(orc.lib.orc_gtao_reproject(orc.fptr(cam), im["depth"].ptr, im["prev_depth"].ptr, 1, ref_filt.ptr, ref_prev.ptr, ref_out.ptr, 0, 0))
+        for name, ref in (("gv_filtered", ref_filt), ("gv_output", ref_out)):
+            frac, dmax = _ao_compare(app.readback(name).download(), ref.download())
+            assert frac <= 2e-3, (f, name, frac, dmax)
+        p2 = _gv_params(P, ang[1])
+        orc.ok(orc.lib.orc_gtao_deinterleave(im["depth"].ptr, 1, ref_arr.ptr, ref_arr.layer_stride, 2))
+        orc.ok(orc.lib.orc_gtao_main_deinterleaved(C.byref(p2), ref_arr.ptr, ref_arr.layer_stride, im["normal"].ptr, ref_raw.ptr, 2, 0, 0, 0))
+        frac, dmax = _ao_compare(app.readback("gv_raw").download(), ref_raw.download())    # graphics raw with layer 0's sparse overwrite
+        assert frac <= 2e-3, (f, "gv_raw", frac, dmax)
+        ref_prev, ref_out = ref_out, ref_prev                                   # main.cpp:417 remap(output, prev_frame)
+        oc.end_frame()
+    app.close()

@@ -365,3 +365,57 @@ def test_screen_trace_filter_and_accumulate_fixed_points():
         assert (a[:8] == 0.5).all()
         assert np.abs(a[8:] - want).max() <= 1e-3, (it, a[8:].max(), want)
     assert abs(want - 0.5 * (1 - 0.95 ** 5)) < 2e-3
+
+
+# ---- (ix) GTAO variants -----------------------------------------------------------------------------------------
+def test_gtao_graphics_plane_and_deinterleave_layout():
+    """main.frag on a fronto-parallel plane: like anchor (iii) the slice integral is 1 at the view axis; sky returns 1.
+    deinterleave.comp: texel (x, y) of the dispatched corner lands in layer ((y & 3) << 2) + (x & 3) at (x >> 2, y >> 2)."""
+    w, h = 2048, 1024
+    gb, _ = flat_gbuffer(w, h, -5.0)
+    d = gb.depth.download(1)
+    d[:8, :] = 0xFFFFFF
+    gb.depth.upload(d, 1)
+    raw = vkr.Image(w // 2, h // 2, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    p = vkr.GtaoParams()
+    C.memmove(p.normal_mat, ident16(), 64)
+    p.fovy, p.aspect, p.znear, p.zfar, p.angle_offset = FOVY, w / h, ZN, ZF, 0.125
+    orc.ok(orc.lib.orc_gtao_main_graphics(C.byref(p), gb.depth.ptr, gb.normal.ptr, raw.ptr, 1, 0, 0))
+    out = raw.download().astype(np.float32)
+    cy, cx = h // 4, w // 4
+    centre = out[cy - 2:cy + 2, cx - 2:cx + 2, 0]
+    assert np.abs(centre - 1.0).max() < 1.2e-2, centre
+    assert (out[:3, :, 0] == 1.0).all() and (out[..., 1] == 0).all() and (out[..., 3] == 1).all()
+
+    # deinterleave: a depth level holding its own texel index
+    w2, h2 = 256, 128
+    depth = vkr.Image(2 * w2, 2 * h2, vkr.D24_UNORM_S8_UINT, 2, device="cpu")
+    idx = (np.arange(h2)[:, None] * w2 + np.arange(w2)[None, :]).astype(np.uint32)
+    depth.upload(idx, 1)
+    arr = vkr.ImageArray(w2 // 4, h2 // 4, vkr.R32_SFLOAT, 1, layers=16, device="cpu")
+    orc.ok(orc.lib.orc_gtao_deinterleave(depth.ptr, 1, arr.ptr, arr.layer_stride, 2))
+    cw, ch = (w2 // 4) // 8 * 8, (h2 // 4) // 4 * 4                      # the dispatch covers the OUTPUT extent (gtao.cpp:468)
+    for layer in (0, 5, 15):
+        got = arr.layer(layer).download()
+        ly, lx = layer >> 2, layer & 3
+        want = np.zeros_like(got)
+        ys, xs = np.arange(ly, ch, 4), np.arange(lx, cw, 4)
+        want[:len(ys), :len(xs)] = (idx[np.ix_(ys, xs)].astype(np.float64) / 0xFFFFFF).astype(np.float32)
+        assert np.array_equal(got, want), layer
+
+
+def test_gtao_reproject_blends_only_static_texels():
+    w2, h2 = 64, 32
+    gb, k = flat_gbuffer(2 * w2, 2 * h2, -5.0)
+    pd = gb.prev_depth.download(1)
+    pd[:4] = k + 1000
+    pd[4:8] = 0xFFFFFF
+    gb.prev_depth.upload(pd, 1)
+    ao, prev, out = [vkr.Image(w2, h2, vkr.R16_SFLOAT, device="cpu") for _ in range(3)]
+    ao.upload(np.full((h2, w2), 0.5, dtype=np.float16))
+    prev.upload(np.full((h2, w2), 1.0, dtype=np.float16))
+    cam = f32(FOVY, 2.0, ZN, ZF)
+    orc.ok(orc.lib.orc_gtao_reproject(orc.fptr(cam), gb.depth.ptr, gb.prev_depth.ptr, 1, ao.ptr, prev.ptr, out.ptr, 0, 0))
+    o = out.download().astype(np.float32)
+    assert (o[:8] == 0.5).all()                                             # moved or sky last frame: the new value
+    assert np.abs(o[8:] - (1.0 * 0.95 + 0.5 * 0.05)).max() < 1e-3           # mix(prev, new, 0.05)

@@ -45,7 +45,8 @@ struct VkrApp {
   ImageResourceId ssao_tex, ssr_tex;
   SSAOPass ssao_pass;
   ScreenSpaceTrace screen_trace;
-  bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false;
+  GTAO gtao_alt;     // a second GTAO object so the variants do not disturb the live chain's images
+  bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false, alt_gtao_variants = false;
   VkrSsrParams last_ssr{};
   std::string task_names;
   uint64_t frames = 0;
@@ -55,7 +56,7 @@ struct VkrApp {
         gtao{render_graph, w, h, /*USE_RAY_QUERY*/ false, /*half_res*/ true},                   // main.cpp:265
         ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph},
         ssao_tex{create_ssao_texture(render_graph, w, h)}, ssr_tex{create_ssr_tex(render_graph, w, h)}, ssao_pass{render_graph, ssao_tex, 0},
-        screen_trace{render_graph, w, h} {
+        screen_trace{render_graph, w, h}, gtao_alt{render_graph, w, h, false, true, 2} {
     ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
     ssr.preintegrate_brdf(render_graph);
     gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
@@ -110,12 +111,22 @@ struct VkrApp {
       screen_trace.add_filter_pass(render_graph, tp, gbuffer.depth);
       screen_trace.add_accumulate_pass(render_graph, tp, gbuffer.depth, gbuffer.prev_depth);
     }
+    if (alt_gtao_variants) {
+      gtao_alt.angle_jitter = angle_jitter;
+      gtao_alt.add_main_pass_graphics(render_graph, gtao_params, gbuffer.depth, gbuffer.normal);
+      gtao_alt.add_filter_pass(render_graph, gtao_params, gbuffer.depth);
+      GTAOReprojection rp{glm::mat4{}, fovy, aspect, znear, zfar};
+      gtao_alt.add_reprojection_pass(render_graph, rp, gbuffer.depth, gbuffer.prev_depth);
+      gtao_alt.deinterleave_depth(render_graph, gbuffer.depth);
+      gtao_alt.add_main_pass_deinterleaved(render_graph, gtao_params, gbuffer.normal);
+    }
     render_graph.submit();                                                                        // :402
     task_names.clear();
     for (auto& n : render_graph.last_task_names()) { task_names += n; task_names += '\n'; }
 
     render_graph.remap(gbuffer.depth, gbuffer.prev_depth);                                        // main.cpp:416-420
     render_graph.remap(gtao.output, gtao.prev_frame);
+    if (alt_gtao_variants) render_graph.remap(gtao_alt.output, gtao_alt.prev_frame);
     taa_pass.remap_targets(render_graph);
     ssr.remap_images(render_graph);
     gtao.remap(render_graph);
@@ -146,6 +157,10 @@ struct VkrApp {
     else if (name == "brdf") id = ssr.get_preintegrated_brdf();
     else if (name == "ssao") id = ssao_tex;
     else if (name == "ssr_legacy") id = ssr_tex;
+    else if (name == "gv_raw") id = gtao_alt.raw;
+    else if (name == "gv_filtered") id = gtao_alt.filtered;
+    else if (name == "gv_output") id = r ? gtao_alt.prev_frame : gtao_alt.output;
+    else if (name == "gv_deinterleaved") id = gtao_alt.deinterleaved_depth;
     else if (name == "st_raw") id = screen_trace.raw;
     else if (name == "st_filtered") id = screen_trace.filtered;
     else if (name == "st_accumulated") id = screen_trace.accumulated;
@@ -266,6 +281,15 @@ int vkr_app_sync(VkrApp* app) {
   VKR_TRY(app->render_graph.wait_idle())
 }
 
+int vkr_app_get_value(VkrApp* app, const char* name, float* out) {
+  if (!app || !name || !out) { host_error("get_value: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  std::string n = name;
+  if (n == "gtao.angle_offset") *out = app->gtao.last_angle_offset;
+  else if (n == "gv.angle_offset") *out = app->gtao_alt.last_angle_offset;
+  else { host_error("get_value: unknown value '%s'", name); return VKR_ERR_INVALID_ARGUMENT; }
+  return VKR_OK;
+}
+
 int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out) {
   if (!app || !out) { host_error("screen_trace_params: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
   *out = app->screen_trace.last_block;
@@ -300,6 +324,7 @@ int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   else if (n == "alt.ssao") app->alt_ssao = v != 0.f;
   else if (n == "alt.ssr") app->alt_ssr = v != 0.f;
   else if (n == "alt.screen_trace") app->alt_screen_trace = v != 0.f;
+  else if (n == "alt.gtao_variants") app->alt_gtao_variants = v != 0.f;
   else if (n == "alt.ssao_reference_packing") app->ssao_pass.reference_packing = v != 0.f;
   else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
   else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;

@@ -84,7 +84,7 @@ void DownsamplePass::run(RenderGraph& graph, ImageResourceId src_normals, ImageR
 }
 
 // ---- GTAO (reference src/gtao.cpp) ---------------------------------------------------------------
-GTAO::GTAO(RenderGraph& graph, uint32_t width, uint32_t height, bool use_ray_query, bool half_res, int) {
+GTAO::GTAO(RenderGraph& graph, uint32_t width, uint32_t height, bool use_ray_query, bool half_res, int pattern_n) : deinterleave_n{pattern_n} {
   if (use_ray_query) throw std::runtime_error{"GTAO: the ray-query variant needs a BVH and is out of scope"};
   if (half_res) { width /= 2; height /= 2; depth_lod = 1; }                                                     // :20-24
   auto mk = [&](uint32_t fmt) { gpu::ImageInfo i; i.format = fmt; i.width = width; i.height = height; return graph.create_image(i); };
@@ -94,6 +94,11 @@ GTAO::GTAO(RenderGraph& graph, uint32_t width, uint32_t height, bool use_ray_que
   output = mk(VKR_FORMAT_R16_SFLOAT);
   accumulated_ao = mk(VKR_FORMAT_R16G16_SFLOAT);                                                                // :37-39
   accumulated_history = mk(VKR_FORMAT_R16G16_SFLOAT);
+  if (pattern_n < 0 || pattern_n > 3) throw std::runtime_error{"GTAO: pattern_n outside 0..3"};
+  const uint32_t pattern_step = 1u << (uint32_t)pattern_n;                                                      // :41-47
+  gpu::ImageInfo di; di.format = VKR_FORMAT_R32_SFLOAT; di.width = width / pattern_step; di.height = height / pattern_step;
+  di.array_layers = pattern_step * pattern_step;
+  if (di.width && di.height) deinterleaved_depth = graph.create_image(di);
 }
 
 void GTAO::add_main_pass(RenderGraph& graph, const GTAOParams& params, ImageResourceId depth, ImageResourceId normal, ImageResourceId material,
@@ -102,6 +107,7 @@ void GTAO::add_main_pass(RenderGraph& graph, const GTAOParams& params, ImageReso
   const float angle_offsets[]{60.f, 300.f, 180.f, 240.f, 120.f, 0.f, 300.f, 60.f, 180.f, 120.f, 240.f, 0.f};     // :109
   float base_angle = angle_offsets[frame_count % (sizeof(angle_offsets) / sizeof(float))] / 360.f;
   base_angle += angle_jitter;                                                                                   // :111 (explicit input)
+  last_angle_offset = base_angle;
   VkrGtaoParams p{};
   copy_mat(p.normal_mat, params.normal_mat);
   p.fovy = params.fovy; p.aspect = params.aspect; p.znear = params.znear; p.zfar = params.zfar;
@@ -163,5 +169,90 @@ void GTAO::add_accumulate_pass(RenderGraph& graph, const DrawTAAParams& params, 
       vkr_check(vkr_gtao_accumulate(&p, resources.get_image(input.depth), resources.get_image(input.prev_depth), resources.get_image(input.gtao),
                                     resources.get_image(input.accumulated_ao), resources.get_image(input.velocity), resources.get_image(input.history),
                                     lod, cmd.stream), "GTAO_accumulate");
+    });
+}
+
+// ---- GTAO variants beside the live path (reference src/gtao.cpp:241-284,:349-413,:445-526) ----------------------
+static const float kGtaoAngles[]{60.f, 300.f, 180.f, 240.f, 120.f, 0.f, 300.f, 60.f, 180.f, 120.f, 240.f, 0.f};
+
+void GTAO::add_main_pass_graphics(RenderGraph& graph, const GTAOParams& params, ImageResourceId depth, ImageResourceId normal) {
+  struct PassData { ImageViewId rt, depth, norm; };
+  float base_angle = kGtaoAngles[frame_count % (sizeof(kGtaoAngles) / sizeof(float))] / 360.f;                   // :370-372
+  base_angle += angle_jitter;
+  frame_count += 1;
+  last_angle_offset = base_angle;
+  VkrGtaoParams p{};
+  copy_mat(p.normal_mat, params.normal_mat);
+  p.fovy = params.fovy; p.aspect = params.aspect; p.znear = params.znear; p.zfar = params.zfar;
+  p.angle_offset = base_angle;
+  const uint32_t lod = depth_lod;
+  graph.add_task<PassData>("GTAO",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, depth_lod, 1, 0, 1);
+      input.norm = builder.sample_image(normal);
+      input.rt = builder.use_color_attachment(raw, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_gtao_main_graphics(&p, resources.get_image(input.depth), resources.get_image(input.norm), resources.get_image(input.rt), lod, nullptr,
+                                       cmd.stream), "GTAO");
+    });
+}
+
+void GTAO::add_reprojection_pass(RenderGraph& graph, const GTAOReprojection& params, ImageResourceId depth, ImageResourceId prev_depth) {
+  struct PassData { ImageViewId out, gtao, prev_gtao, depth, prev_depth; };
+  struct Pc { float v[4]; } pc{{params.fovy, params.aspect, params.znear, params.zfar}};
+  const uint32_t lod = depth_lod;
+  graph.add_task<PassData>("GTAO_reproject",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, depth_lod, 1, 0, 1);
+      input.prev_depth = builder.sample_image(prev_depth, depth_lod, 1, 0, 1);
+      input.gtao = builder.sample_image(filtered);
+      input.prev_gtao = builder.sample_image(prev_frame);
+      input.out = builder.use_storage_image(output, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_gtao_reproject(pc.v, resources.get_image(input.depth), resources.get_image(input.prev_depth), lod, resources.get_image(input.gtao),
+                                   resources.get_image(input.prev_gtao), resources.get_image(input.out), nullptr, cmd.stream), "GTAO_reproject");
+    });
+}
+
+void GTAO::deinterleave_depth(RenderGraph& graph, ImageResourceId depth) {
+  struct PassData { ImageViewId depth, out; };
+  const uint32_t lod = depth_lod;
+  const int n = deinterleave_n;
+  const uint64_t stride = graph.layer_stride(deinterleaved_depth);
+  graph.add_task<PassData>("GTAO_deinterleave",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(depth, depth_lod, 1, 0, 1);
+      input.out = builder.use_storage_image(deinterleaved_depth, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_gtao_deinterleave(resources.get_image(input.depth), lod, resources.get_image(input.out), stride, n, cmd.stream), "GTAO_deinterleave");
+    });
+}
+
+void GTAO::add_main_pass_deinterleaved(RenderGraph& graph, const GTAOParams& params, ImageResourceId normal) {
+  struct PassData { ImageViewId out, depth, norm; };
+  float base_angle = kGtaoAngles[frame_count % (sizeof(kGtaoAngles) / sizeof(float))] / 360.f;                   // :493-495
+  base_angle += angle_jitter;
+  frame_count += 1;
+  last_angle_offset = base_angle;
+  VkrGtaoParams p{};
+  copy_mat(p.normal_mat, params.normal_mat);
+  p.fovy = params.fovy; p.aspect = params.aspect; p.znear = params.znear; p.zfar = params.zfar;
+  p.angle_offset = base_angle;
+  const int n = deinterleave_n;
+  const uint64_t stride = graph.layer_stride(deinterleaved_depth);
+  const uint32_t out_layers = graph.get_descriptor(raw).array_layers;                                            // :520 — the OUTPUT image's layers (1)
+  graph.add_task<PassData>("GTAO_deinterleaved",
+    [&](PassData& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(deinterleaved_depth);
+      input.norm = builder.sample_image(normal);
+      input.out = builder.use_storage_image(raw, 0, 0);
+    },
+    [=](PassData& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      for (uint32_t i = 0; i < out_layers; i++)
+        vkr_check(vkr_gtao_main_deinterleaved(&p, resources.get_image(input.depth), stride, resources.get_image(input.norm), resources.get_image(input.out), n, i,
+                                              nullptr, cmd.stream), "GTAO_deinterleaved");
     });
 }

@@ -75,6 +75,14 @@ struct GTAOParams {
   float zfar;
 };
 
+struct GTAOReprojection {
+  glm::mat4 camera_to_prev_frame;   // read only by the MATRIX_REPROJECT mode the reference compiles out (reproject.comp:4-7)
+  float fovy;
+  float aspect;
+  float znear;
+  float zfar;
+};
+
 struct GTAO {
   GTAO(rendergraph::RenderGraph& graph, uint32_t width, uint32_t height, bool use_ray_query, bool half_res = true, int pattern_n = 2);
 
@@ -82,6 +90,13 @@ struct GTAO {
                      rendergraph::ImageResourceId normal, rendergraph::ImageResourceId material, rendergraph::ImageResourceId preintegrated_pdf);
   void add_filter_pass(rendergraph::RenderGraph& graph, const GTAOParams& params, rendergraph::ImageResourceId depth);
   void add_accumulate_pass(rendergraph::RenderGraph& graph, const DrawTAAParams& params, const Gbuffer& gbuffer);
+  // the variants beside the live path (reference src/gtao.hpp:57-82); each advances the same frame_count / angle table
+  void add_main_pass_graphics(rendergraph::RenderGraph& graph, const GTAOParams& params, rendergraph::ImageResourceId depth,
+                              rendergraph::ImageResourceId normal);
+  void add_reprojection_pass(rendergraph::RenderGraph& graph, const GTAOReprojection& params, rendergraph::ImageResourceId depth,
+                             rendergraph::ImageResourceId prev_depth);
+  void deinterleave_depth(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId depth);
+  void add_main_pass_deinterleaved(rendergraph::RenderGraph& graph, const GTAOParams& params, rendergraph::ImageResourceId normal);
   void remap(rendergraph::RenderGraph& graph) { graph.remap(accumulated_history, accumulated_ao); }
 
   rendergraph::ImageResourceId raw;       // output of main pass
@@ -90,6 +105,8 @@ struct GTAO {
   rendergraph::ImageResourceId output;
   rendergraph::ImageResourceId accumulated_ao;
   rendergraph::ImageResourceId accumulated_history;
+  rendergraph::ImageResourceId deinterleaved_depth;   // R32F, (w >> n) x (h >> n), 4^n layers (gtao.cpp:41-47)
+  float last_angle_offset = 0.f;                       // push constant of the most recent main-pass variant
 
   // runtime settings (ImGui state in the reference, src/gtao.hpp:108-116)
   bool mis_gtao = true;
@@ -102,6 +119,7 @@ struct GTAO {
   float angle_jitter = 0.f;
 
  private:
+  int deinterleave_n = 2;
   uint32_t depth_lod = 0;
   uint32_t frame_count = 0;
 };

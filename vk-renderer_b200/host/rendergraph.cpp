@@ -72,9 +72,12 @@ ImageResourceId RenderGraph::create_image(const gpu::ImageInfo& info) {
   Slot s{};
   s.bytes = vkr_image_layout(info.width, info.height, info.format, info.mip_levels, &s.desc);
   if (s.bytes == 0) throw std::runtime_error("create_image: unsupported format / extent / mip count");
+  s.layers = info.array_layers ? info.array_layers : 1;
+  s.layer_stride = (s.bytes + 255) & ~(uint64_t)255;
+  const uint64_t total = s.layers > 1 ? s.layer_stride * s.layers : s.bytes;
   cuda_check(cudaSetDevice(device_), "cudaSetDevice");
-  cuda_check(cudaMalloc(&s.desc.base, s.bytes), "cudaMalloc(image)");
-  cuda_check(cudaMemsetAsync(s.desc.base, 0, s.bytes, (cudaStream_t)stream_), "cudaMemset(image)");
+  cuda_check(cudaMalloc(&s.desc.base, total), "cudaMalloc(image)");
+  cuda_check(cudaMemsetAsync(s.desc.base, 0, total, (cudaStream_t)stream_), "cudaMemset(image)");
   slots.push_back(s);
   allocations.push_back(s.desc.base);
   ImageResourceId id;
@@ -91,7 +94,13 @@ gpu::ImageInfo RenderGraph::get_descriptor(ImageResourceId id) const {
   const VkrImage& d = image(id);
   gpu::ImageInfo info;
   info.format = d.format; info.width = d.width; info.height = d.height; info.mip_levels = d.mip_count;
+  info.array_layers = slots[id.get_index()].layers;
   return info;
+}
+
+uint64_t RenderGraph::layer_stride(ImageResourceId id) const {
+  image(id);
+  return slots[id.get_index()].layer_stride;
 }
 
 void RenderGraph::remap(ImageResourceId src, ImageResourceId dst) {

@@ -143,6 +143,9 @@ struct RenderGraph {
 
   ImageResourceId create_image(const gpu::ImageInfo& info);  // zero-initialised device memory
   gpu::ImageInfo get_descriptor(ImageResourceId id) const;
+  // Array images (gpu::ImageInfo::array_layers, reference src/gpu/resource_info.hpp:11-19): layer l of slot `id` lies
+  // layer_stride(id) * l bytes after the descriptor's base.
+  uint64_t layer_stride(ImageResourceId id) const;
   void remap(ImageResourceId src, ImageResourceId dst);      // reference resources.cpp:89-91: swap slot contents
 
   // Point a slot at caller-owned device memory (same extent / format / mips): lets a resident input
@@ -161,7 +164,7 @@ struct RenderGraph {
   const std::vector<std::string>& last_task_names() const { return last_names; }
 
  private:
-  struct Slot { VkrImage desc; uint64_t bytes; };
+  struct Slot { VkrImage desc; uint64_t bytes; uint32_t layers = 1; uint64_t layer_stride = 0; };
   std::vector<Slot> slots;
   std::vector<void*> allocations;   // everything create_image() allocated (slots may be rebound / swapped)
   bool timing_ = false;

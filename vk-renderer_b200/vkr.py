@@ -398,6 +398,10 @@ _sig("vkr_taa_resolve_ex", PT(TaaParams), IP, IP, IP, IP, IP, IP, EP, VP)
 _sig("vkr_screen_trace_main_ex", PT(ScreenTraceParams), IP, IP, IP, IP, IP, EP, VP)
 _sig("vkr_screen_trace_filter_ex", C.c_float, C.c_float, IP, IP, IP, EP, VP)
 _sig("vkr_screen_trace_accumulate_ex", PT(C.c_float), IP, IP, IP, IP, EP, VP)
+_sig("vkr_gtao_main_graphics", PT(GtaoParams), IP, IP, IP, C.c_uint32, EP, VP)
+_sig("vkr_gtao_deinterleave", IP, C.c_uint32, IP, C.c_uint64, C.c_int, VP)
+_sig("vkr_gtao_main_deinterleaved", PT(GtaoParams), IP, C.c_uint64, IP, IP, C.c_int, C.c_uint32, EP, VP)
+_sig("vkr_gtao_reproject", PT(C.c_float), IP, IP, C.c_uint32, IP, IP, IP, EP, VP)
 _sig("vkr_ssao", PT(SsaoParams), IP, IP, VP)
 _sig("vkr_ssao_ex", PT(SsaoParams), IP, IP, EP, VP)
 _sig("vkr_ssr_legacy", PT(SsrParams), IP, IP, IP, IP, IP, VP)
@@ -528,6 +532,25 @@ def screen_trace_filter(znear, zfar, raw, depth, filtered, ext=None, stream=None
 def screen_trace_accumulate(fovy_aspect_znear_zfar, depth, prev_depth, filtered, accumulated, ext=None, stream=None):
     f4 = (C.c_float * 4)(*fovy_aspect_znear_zfar)
     check(lib.vkr_screen_trace_accumulate_ex(f4, depth.ptr, prev_depth.ptr, filtered.ptr, accumulated.ptr, _e(ext), stream_ptr(stream)))
+
+
+def gtao_main_graphics(p, depth, normal, raw, depth_lod=1, ext=None, stream=None):
+    check(lib.vkr_gtao_main_graphics(C.byref(p), depth.ptr, normal.ptr, raw.ptr, depth_lod, _e(ext), stream_ptr(stream)))
+
+
+def gtao_deinterleave(depth, out_array, pattern_n=2, depth_lod=1, stream=None):
+    """out_array: ImageArray of R32_SFLOAT with 4**pattern_n layers."""
+    check(lib.vkr_gtao_deinterleave(depth.ptr, depth_lod, out_array.ptr, out_array.layer_stride, pattern_n, stream_ptr(stream)))
+
+
+def gtao_main_deinterleaved(p, depth_array, normal, raw, pattern_n=2, layer=0, ext=None, stream=None):
+    check(lib.vkr_gtao_main_deinterleaved(C.byref(p), depth_array.ptr, depth_array.layer_stride, normal.ptr, raw.ptr, pattern_n, layer, _e(ext),
+                                          stream_ptr(stream)))
+
+
+def gtao_reproject(fovy_aspect_znear_zfar, depth, prev_depth, gtao, prev_gtao, out, depth_lod=1, ext=None, stream=None):
+    f4 = (C.c_float * 4)(*fovy_aspect_znear_zfar)
+    check(lib.vkr_gtao_reproject(f4, depth.ptr, prev_depth.ptr, depth_lod, gtao.ptr, prev_gtao.ptr, out.ptr, _e(ext), stream_ptr(stream)))
 
 
 def sphere_samples(seed=0, count=16):

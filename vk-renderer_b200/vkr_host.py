@@ -44,6 +44,8 @@ lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 lib.vkr_app_bind_gbuffer.restype = C.c_int
 lib.vkr_app_bind_gbuffer.argtypes = [C.c_void_p] + [C.POINTER(vkr.VkrImage)] * 5
 lib.vkr_app_task_timing.restype = C.c_int
+lib.vkr_app_get_value.restype = C.c_int
+lib.vkr_app_get_value.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float)]
 lib.vkr_app_screen_trace_params.restype = C.c_int
 lib.vkr_app_screen_trace_params.argtypes = [C.c_void_p, C.POINTER(vkr.ScreenTraceParams)]
 lib.vkr_app_alt_params.restype = C.c_int
@@ -122,6 +124,11 @@ class App:
         a, r = vkr.SsaoParams(), vkr.SsrParams()
         _check(lib.vkr_app_alt_params(self.h, C.byref(a), C.byref(r)))
         return a, r
+
+    def get_value(self, name):
+        v = C.c_float()
+        _check(lib.vkr_app_get_value(self.h, name.encode(), C.byref(v)))
+        return v.value
 
     def screen_trace_params(self):
         p = vkr.ScreenTraceParams()
