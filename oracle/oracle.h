@@ -105,6 +105,15 @@ typedef struct OrcScreenTraceParams {
   float fovy, aspect, znear, zfar;
 } OrcScreenTraceParams;
 
+/* Constants UBO of ProbeTracePass::run (reference src/probe_renderer.cpp:340-360). */
+typedef struct OrcProbeTraceParams {
+  float inverse_view[16];
+  float probe_min[4];
+  float probe_max[4];
+  uint32_t grid_size;
+  float fovy, aspect, znear, zfar;
+} OrcProbeTraceParams;
+
 void orc_set_threads(int n);
 int  orc_get_max_threads(void);
 
@@ -164,6 +173,14 @@ int orc_gtao_main_deinterleaved(const OrcGtaoParams* p, const OrcImage* depth_ar
                                 const OrcImage* raw, int pattern_n, uint32_t layer, int y0, int y1);
 int orc_gtao_reproject(const float* fovy_aspect_znear_zfar, const OrcImage* depth, const OrcImage* prev_depth, uint32_t depth_lod,
                        const OrcImage* gtao, const OrcImage* prev_gtao, const OrcImage* out, int y0, int y1);
+
+/* probe_renderer compute path: reference shaders/cube2oct/shader.comp, probe_downsample/shader.frag, trace_probe/shader.comp.
+ * Cube maps: face f at base + f * face_stride; probe arrays: layer l at base + l * layer_stride. */
+int orc_cube2oct(const OrcImage* cube_color, uint64_t color_face_stride, const OrcImage* cube_distance, uint64_t distance_face_stride,
+                 const OrcImage* oct_color_layer, const OrcImage* oct_depth_layer);
+int orc_probe_downsample(const OrcImage* probe_depth_layer);
+int orc_trace_probe(const OrcProbeTraceParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* probe_color,
+                    uint64_t color_layer_stride, const OrcImage* probe_depth, uint64_t depth_layer_stride, const OrcImage* out, int y0, int y1);
 
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);

@@ -64,6 +64,9 @@ _sig("orc_gtao_main_graphics", C.POINTER(vkr.GtaoParams), IP, IP, IP, U, I, I)
 _sig("orc_gtao_deinterleave", IP, U, IP, C.c_uint64, I)
 _sig("orc_gtao_main_deinterleaved", C.POINTER(vkr.GtaoParams), IP, C.c_uint64, IP, IP, I, U, I, I)
 _sig("orc_gtao_reproject", FP, IP, IP, U, IP, IP, IP, I, I)
+_sig("orc_cube2oct", IP, C.c_uint64, IP, C.c_uint64, IP, IP)
+_sig("orc_probe_downsample", IP)
+_sig("orc_trace_probe", C.POINTER(vkr.ProbeTraceParams), IP, IP, IP, C.c_uint64, IP, C.c_uint64, IP, I, I)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

@@ -18,7 +18,7 @@ def declared(header):
 
 
 @pytest.mark.parametrize("header,libname", [("vkr_passes.h", "libvkr_b200.so"), ("vkr_synth.h", "libvkr_b200.so"), ("vkr_host.h", "libvkr_host.so"),
-                                            ("vkr_peer.h", "libvkr_b200.so")])
+                                            ("vkr_peer.h", "libvkr_b200.so"), ("vkr_probe.h", "libvkr_b200.so")])
 def test_every_declared_symbol_is_exported(header, libname):
     if not os.path.exists(os.path.join(ROOT, "include", header)):
         pytest.skip(f"{header} not present")

@@ -419,3 +419,119 @@ def test_gtao_reproject_blends_only_static_texels():
     o = out.download().astype(np.float32)
     assert (o[:8] == 0.5).all()                                             # moved or sky last frame: the new value
     assert np.abs(o[8:] - (1.0 * 0.95 + 0.5 * 0.05)).max() < 1e-3           # mix(prev, new, 0.05)
+
+
+# ---- (x) probe path: cube -> octahedral, probe pyramid, probe trace -----------------------------------------------------
+def _oct_decode_np(u, v):
+    x, y = 2 * (u - 0.5), 2 * (v - 0.5)
+    z = 1 - np.abs(x) - np.abs(y)
+    fx = np.where(z < 0, (1 - np.abs(y)) * np.where(x >= 0, 1, -1), x)
+    fy = np.where(z < 0, (1 - np.abs(x)) * np.where(y >= 0, 1, -1), y)
+    d = np.stack([fx, fy, z], axis=-1)
+    return d / np.linalg.norm(d, axis=-1, keepdims=True), np.sign(np.stack([fx, fy, z], axis=-1))
+
+
+def test_cube2oct_sphere_depth_and_face_lookup():
+    """A cube map holding constant distance r and its own face index as colour: the octahedral depth must be
+    encode_oct_depth(r * dot(dir, front)) with front = normalize(sign(v)) (cube2oct/shader.comp:26-29), and the colour the
+    index of the face the direction's major axis selects."""
+    import vkr_probes
+    n, size, r = 32, 64, 3.0
+    cubes = vkr_probes.CubeMapSet(1, n, device="cpu")
+    for f in range(6):
+        col = np.zeros((n, n, 4), dtype=np.uint8)
+        col[..., 3] = 40 * (f + 1)                           # alpha is stored linearly: face id survives the sRGB decode
+        cubes.color.layer(f).upload(col)
+        cubes.distance.layer(f).upload(np.full((n, n), r, dtype=np.float16))
+    oc = vkr.ImageArray(size, size, vkr.R8G8B8A8_UNORM, 1, layers=1, device="cpu")
+    od = vkr.ImageArray(size, size, vkr.R16_UNORM, 7, layers=1, device="cpu")
+    orc.ok(orc.lib.orc_cube2oct(cubes.color.ptr, cubes.color.layer_stride, cubes.distance.ptr, cubes.distance.layer_stride, oc.layer(0).ptr, od.layer(0).ptr))
+    v, u = np.meshgrid(np.arange(size) / size, np.arange(size) / size, indexing="ij")
+    d, sg = _oct_decode_np(u, v)
+    front = sg / np.maximum(np.linalg.norm(sg, axis=-1, keepdims=True), 1e-30)
+    zlin = np.clip(r * (d * front).sum(-1), 0.05, 80.0)
+    f_, n_ = 80.0, 0.05
+    want = f_ / (f_ - n_) + f_ * n_ / (-zlin * (f_ - n_))
+    got = od.layer(0).download(0).astype(np.float64) / 65535.0
+    assert np.abs(got - want).max() < 1.5 / 65535 + 1e-6, np.abs(got - want).max()
+    a = np.abs(d)
+    face = np.where((a[..., 2] >= a[..., 0]) & (a[..., 2] >= a[..., 1]), np.where(d[..., 2] < 0, 5, 4),
+                    np.where(a[..., 1] >= a[..., 0], np.where(d[..., 1] < 0, 3, 2), np.where(d[..., 0] < 0, 1, 0)))
+    alpha = oc.layer(0).download()[..., 3]
+    margin = np.sort(a, axis=-1)
+    clear = (margin[..., 2] - margin[..., 1]) > 0.05          # away from face edges (where ties / rounding decide)
+    assert (alpha[clear] == 40 * (face[clear] + 1)).all()
+
+
+def test_probe_downsample_is_a_block_min():
+    rng = np.random.default_rng(3)
+    size = 64
+    od = vkr.ImageArray(size, size, vkr.R16_UNORM, 7, layers=1, device="cpu")
+    base = rng.integers(0, 65536, (size, size)).astype(np.uint16)
+    layer = od.layer(0)
+    layer.upload(base, 0)
+    orc.ok(orc.lib.orc_probe_downsample(layer.ptr))
+    for k in range(1, 7):
+        want = base.reshape(size >> k, 1 << k, size >> k, 1 << k).min(axis=(1, 3))
+        assert np.array_equal(layer.download(k), want), k
+
+
+def _probe_setup(w, h, device="cpu", grid_sz=2, size=128, cube=64, objects=0):
+    import vkr_probes
+    scene = vkr.synth_scene(0, objects)
+    grid = vkr_probes.OctahedralProbeGrid(grid_sz, size, device="cpu")
+    grid.min, grid.max = (-3.0, 1.0, -5.0), (3.0, 1.0, 5.0)
+    cubes = vkr_probes.CubeMapSet(grid_sz * grid_sz, cube, device="cpu").render_synthetic(scene, grid.positions())
+    gb = vkr.Gbuffer(w, h, device="cpu")
+    dp = vkr.synth_camera(0, 0, w, h, False)
+    vkr.synth_gbuffer(scene, dp, gb)
+    params = vkr_probes.ProbeTraceParams(vkr.mat_inverse(dp.camera), *list(dp.fovy_aspect_znear_zfar))
+    return scene, grid, cubes, gb, dp, params
+
+
+def test_trace_probe_floor_sees_the_wall():
+    """Ground + back wall + sky, 2x2 probes: wherever the mirror ray of a floor pixel analytically meets the wall's interior,
+    a reported hit must carry the wall's colour."""
+    import vkr_probes
+    w, h = 256, 144
+    scene, grid, cubes, gb, dp, params = _probe_setup(w, h)
+    for i in range(4):
+        orc.ok(orc.lib.orc_cube2oct(cubes.color.layer(6 * i).ptr, cubes.color.layer_stride, cubes.distance.layer(6 * i).ptr, cubes.distance.layer_stride,
+                                    grid.color_array.layer(i).ptr, grid.depth_array.layer(i).ptr))
+        orc.ok(orc.lib.orc_probe_downsample(grid.depth_array.layer(i).ptr))
+    out = vkr.Image(w, h, vkr.R8G8B8A8_UNORM, device="cpu")
+    k = vkr_probes.trace_constants(grid, params)
+    orc.ok(orc.lib.orc_trace_probe(C.byref(k), gb.depth.ptr, gb.normal.ptr, grid.color_array.ptr, grid.color_array.layer_stride, grid.depth_array.ptr,
+                                   grid.depth_array.layer_stride, out.ptr, 0, 0))
+    got = out.download()
+    # analytic mirror rays of floor pixels (uv = pixel / covered extent, camera = view 0 of the synthetic rig)
+    cw, ch = w // 8 * 8, h // 4 * 4
+    v, u = np.meshgrid((np.arange(ch) + 0.5) / h, (np.arange(cw) + 0.5) / w, indexing="ij")   # the G-buffer is ray-cast at pixel centres
+    d0 = gb.depth.download(0)[:ch, :cw].astype(np.float64) / 0xFFFFFF
+    Pv = reconstruct_np(u, v, d0, w / h)
+    inv = np.array(list(vkr.mat_inverse(dp.camera)), dtype=np.float64).reshape(4, 4).T
+    Pw = Pv @ inv[:3, :3].T + inv[:3, 3]
+    eye = inv[:3, 3]
+    V = Pw - eye
+    V /= np.linalg.norm(V, axis=-1, keepdims=True)
+    nrm = gb.normal.download()[:ch, :cw]
+    floor = (d0 < 1) & (nrm[..., 0] == 32768) & (nrm[..., 1] == 65535)          # oct(0, 1, 0)
+    assert np.abs(Pw[..., 1][floor]).max() < 1e-3
+    R = V * [1, -1, 1]                                          # reflect about n = +y
+    t = (scene.wall_z - Pw[..., 2]) / np.where(R[..., 2] > 1e-6, R[..., 2], np.nan)
+    hx, hy = Pw[..., 0] + t * R[..., 0], Pw[..., 1] + t * R[..., 1]
+    sees_wall = floor & (t > 0.5) & (np.abs(hx) < scene.wall_half_width - 1.0) & (hy > 0.5) & (hy < scene.wall_height - 0.5) & (t < 25)
+    assert sees_wall.sum() > 500
+    hit = got[:ch, :cw, 3] > 0
+    wall_srgb = np.array([scene.wall_albedo & 255, (scene.wall_albedo >> 8) & 255, (scene.wall_albedo >> 16) & 255], dtype=np.float64) / 255
+    wall_lin = np.where(wall_srgb <= 0.04045, wall_srgb / 12.92, ((wall_srgb + 0.055) / 1.055) ** 2.4)
+    sel = sees_wall & hit
+    assert sel.sum() > 0.3 * sees_wall.sum(), (sel.sum(), sees_wall.sum())
+    err = np.abs(got[:ch, :cw, :3][sel].astype(np.float64) / 255 - wall_lin).max(axis=-1)
+    # the probe march is an approximation (the hit is accepted in the first probe whose stored depth agrees within HIT_BIAS,
+    # seen from the probe, not from the ray origin): most, not all, of the reported hits are the wall
+    assert np.median(err) < 1.5 / 255 and (err < 2.5 / 255).mean() > 0.6, ((err < 2.5 / 255).mean(), np.quantile(err, [0.5, 0.9, 0.99]))
+    sky = d0 >= 1                                               # uv = pixel / extent is a texel corner: the bilinear depth mixes 4 texels
+    sky4 = sky.copy()
+    sky4[1:, :] &= sky[:-1, :]; sky4[:, 1:] &= sky[:, :-1]; sky4[1:, 1:] &= sky[:-1, :-1]
+    assert sky4.sum() > 100 and (got[:ch, :cw][sky4] == 0).all()

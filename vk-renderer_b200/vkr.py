@@ -82,6 +82,11 @@ class ScreenTraceParams(C.Structure):
                 ("znear", C.c_float), ("zfar", C.c_float)]
 
 
+class ProbeTraceParams(C.Structure):
+    _fields_ = [_mat("inverse_view"), ("probe_min", C.c_float * 4), ("probe_max", C.c_float * 4), ("grid_size", C.c_uint32), ("fovy", C.c_float),
+                ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float)]
+
+
 class SsrParams(C.Structure):
     _fields_ = [_mat("normal_mat"), ("fovy", C.c_float), ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float)]
 
@@ -402,6 +407,9 @@ _sig("vkr_gtao_main_graphics", PT(GtaoParams), IP, IP, IP, C.c_uint32, EP, VP)
 _sig("vkr_gtao_deinterleave", IP, C.c_uint32, IP, C.c_uint64, C.c_int, VP)
 _sig("vkr_gtao_main_deinterleaved", PT(GtaoParams), IP, C.c_uint64, IP, IP, C.c_int, C.c_uint32, EP, VP)
 _sig("vkr_gtao_reproject", PT(C.c_float), IP, IP, C.c_uint32, IP, IP, IP, EP, VP)
+_sig("vkr_cube2oct", IP, C.c_uint64, IP, C.c_uint64, IP, C.c_uint64, IP, C.c_uint64, C.c_uint32, C.c_uint32, VP)
+_sig("vkr_probe_downsample", IP, C.c_uint64, C.c_uint32, C.c_uint32, VP)
+_sig("vkr_trace_probe", PT(ProbeTraceParams), IP, IP, IP, C.c_uint64, IP, C.c_uint64, IP, EP, VP)
 _sig("vkr_ssao", PT(SsaoParams), IP, IP, VP)
 _sig("vkr_ssao_ex", PT(SsaoParams), IP, IP, EP, VP)
 _sig("vkr_ssr_legacy", PT(SsrParams), IP, IP, IP, IP, IP, VP)
@@ -551,6 +559,22 @@ def gtao_main_deinterleaved(p, depth_array, normal, raw, pattern_n=2, layer=0, e
 def gtao_reproject(fovy_aspect_znear_zfar, depth, prev_depth, gtao, prev_gtao, out, depth_lod=1, ext=None, stream=None):
     f4 = (C.c_float * 4)(*fovy_aspect_znear_zfar)
     check(lib.vkr_gtao_reproject(f4, depth.ptr, prev_depth.ptr, depth_lod, gtao.ptr, prev_gtao.ptr, out.ptr, _e(ext), stream_ptr(stream)))
+
+
+# ---- probe_renderer compute path (include/vkr_probe.h) -------------------------------------------------------------
+def cube2oct(cube_color, cube_distance, oct_color, oct_depth, first_layer=0, probe_count=1, stream=None):
+    """cube_*: ImageArray with 6 * probe_count faces; oct_*: ImageArray of probe layers."""
+    check(lib.vkr_cube2oct(cube_color.ptr, cube_color.layer_stride, cube_distance.ptr, cube_distance.layer_stride, oct_color.ptr, oct_color.layer_stride,
+                           oct_depth.ptr, oct_depth.layer_stride, first_layer, probe_count, stream_ptr(stream)))
+
+
+def probe_downsample(probe_depth, first_layer=0, layer_count=1, stream=None):
+    check(lib.vkr_probe_downsample(probe_depth.ptr, probe_depth.layer_stride, first_layer, layer_count, stream_ptr(stream)))
+
+
+def trace_probe(p, depth, normal, probe_color, probe_depth, out, ext=None, stream=None):
+    check(lib.vkr_trace_probe(C.byref(p), depth.ptr, normal.ptr, probe_color.ptr, probe_color.layer_stride, probe_depth.ptr, probe_depth.layer_stride,
+                              out.ptr, _e(ext), stream_ptr(stream)))
 
 
 def sphere_samples(seed=0, count=16):
