@@ -38,6 +38,10 @@ def parse():
                          "probes: 512 independent 256x256 views, Hi-Z+GTAO+SSR, sharded over the ranks (configs[3]); "
                          "tiles: ONE 7680x4320 frame sequence split into row tiles, halo rows over NVLink peer memory (configs[4])")
     ap.add_argument("--views", type=int, default=512)
+    ap.add_argument("--tiles-gather", default="none", choices=["none", "rank0"],
+                    help="tiles workload: leave each rank's finished TAA rows resident where they were computed (none), or send them to rank 0 every "
+                         "frame (rank0: 265 MB per 8K frame into one GPU)")
+    ap.add_argument("--no-tiles-balance", dest="tiles_balance", action="store_false", help="tiles workload: keep the even row split")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -388,8 +392,11 @@ def run_probes(args, rank, world):
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        t_host0 = time.perf_counter()
         for i in range(W, W + K):
             step(i)
+        host_ms = (time.perf_counter() - t_host0) * 1e3 / K      # CPU time to ENQUEUE one frame (not a GPU time)
+        tf.finish()                                          # the last frame's TAA halo (waited for inside the next frame otherwise)
         stream.wait_stream(side)
         e1.record(stream)
         stream.synchronize()
@@ -420,8 +427,9 @@ def run_probes(args, rank, world):
 
 def run_tiles(args, rank, world):
     """BASELINE configs[4]: one 7680x4320 sequence, full chain, rows split over the ranks (vkr_tiles.RowTiledFrame): inputs and
-    Hi-Z replicated, six halo exchanges per frame as direct peer stores + stream-side flags, the finished TAA rows sent to rank 0
-    (NCCL send/recv on a side stream: the final gather).  Strong scaling."""
+    Hi-Z replicated, six halo exchanges per frame as direct peer stores + stream-side flags.  The finished TAA rows stay on the rank
+    that computed them (--tiles-gather none, the default) or are sent to rank 0 every frame (rank0: NCCL send/recv on a side
+    stream; 265 MB per frame into one GPU, which then bounds the frame rate).  Strong scaling."""
     import torch
     import torch.distributed as dist
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -442,8 +450,8 @@ def run_tiles(args, rank, world):
         return out
 
     nres = 3
+    jit = [float(((f * 2654435761) % 1000) / 1000.0 - 0.5) for f in range(nres)]
     with torch.cuda.stream(stream):
-        tf = vkr_tiles.RowTiledFrame(w, h, rank, world, allgather_bytes, device=f"cuda:{local}", motion_rows=16, stream=stream)
         scene = vkr.synth_scene(0, 64)
         dps = [vkr.synth_camera(0, f, w, h, True) for f in range(nres)]
         G = []
@@ -452,9 +460,32 @@ def run_tiles(args, rank, world):
             vkr.synth_gbuffer(scene, dps[f], gb, stream=stream)
             G.append(gb)
         D = [g.depth for g in G]
+        # Cost-balanced tiles: march length and blur radius vary down the frame, so equal rows are not equal work.  Before the
+        # timed region every rank times its own tile WITHOUT exchanges, the times are all-gathered and the strip boundaries moved
+        # (vkr_tiles.balance_bounds); three rounds.  This is set-up, like choosing a launch configuration: not timed.
+        bounds = vkr_tiles.even_bounds(h // 2, world)
+        history, cal_ms = [list(bounds)], []
+        for _ in range(3 if world > 1 and args.tiles_balance else 0):
+            cal = vkr_tiles.RowTiledFrame(w, h, rank, world, allgather_bytes, device=f"cuda:{local}", motion_rows=16, stream=stream, bounds=bounds)
+            cal.exchange_enabled = False
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            for i in range(2 + 4):
+                if i == 2:
+                    ev[0].record(stream)
+                cal.gb = G[i % nres]
+                cal.gb.prev_depth = D[(i - 1) % nres]
+                cal.render_frame(dps[i % nres], jit[i % nres], swap_depth=False)
+            ev[1].record(stream)
+            stream.synchronize()
+            t = [None] * world
+            dist.all_gather_object(t, ev[0].elapsed_time(ev[1]) / 4)
+            cal_ms.append([round(x, 3) for x in t])
+            cal.close(dist.barrier)
+            bounds = vkr_tiles.balance_bounds(bounds, t)
+            history.append(list(bounds))
+        tf = vkr_tiles.RowTiledFrame(w, h, rank, world, allgather_bytes, device=f"cuda:{local}", motion_rows=16, stream=stream, bounds=bounds)
         cleared = tf.gb.prev_depth
     stream.synchronize()
-    jit = [float(((f * 2654435761) % 1000) / 1000.0 - 0.5) for f in range(nres)]
     y0, y1 = tf.own_rows(True)
     spans = [None] * world
     if world > 1:
@@ -471,7 +502,7 @@ def run_tiles(args, rank, world):
         gb.prev_depth = D[(f - 1) % nres] if i > 0 else cleared
         tf.gb = gb
         out = tf.render_frame(dps[f], jit[f], swap_depth=False)
-        if world > 1:                                        # final gather: finished rows to rank 0, off the compute stream
+        if world > 1 and args.tiles_gather == "rank0":       # final gather: finished rows to rank 0, off the compute stream
             done.record(stream)
             side.wait_event(done)
             with torch.cuda.stream(side):
@@ -494,8 +525,11 @@ def run_tiles(args, rank, world):
         sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
+        t_host0 = time.perf_counter()
         for i in range(W, W + K):
             step(i)
+        host_ms = (time.perf_counter() - t_host0) * 1e3 / K      # CPU time to ENQUEUE one frame (not a GPU time)
+        tf.finish()                                          # the last frame's TAA halo (waited for inside the next frame otherwise)
         stream.wait_stream(side)
         e1.record(stream)
         stream.synchronize()
@@ -508,7 +542,7 @@ def run_tiles(args, rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms, fails = float(t[0].item()), int(t[1].item())
     sampler.join(timeout=1.0)
-    tf.close()
+    tf.close(dist.barrier if world > 1 else None)
     if rank != 0:
         return
     peak, peak_src = peaks()
@@ -519,8 +553,12 @@ def run_tiles(args, rank, world):
             "config": {"workload": f"full chain on ONE {w}x{h} sequence, row tiles over {world} rank(s) (BASELINE configs[4])", "frames_resident": nres,
                        "l2": "inputs larger than L2 (one 8K frame touches > 4 GB)",
                        "parallelism": "rows split in 16-row strips; inputs + Hi-Z replicated; 6 halo exchanges per frame as peer stores over NVLink with "
-                                      "stream-side flags; finished TAA rows sent to rank 0 (NCCL send/recv, side stream)",
-                       "halo_rows": tf.halo, "wait_timeouts": fails},
+                                      "stream-side flags, pushed on a transfer stream and waited for one independent pass later; " + ("finished TAA rows sent to rank 0 every frame (NCCL send/recv, side stream)"
+                                                               if args.tiles_gather == "rank0" else
+                                                               "finished TAA rows stay resident on the rank that computed them (SURVEY 8e: shard-resident output)"),
+                       "halo_rows": tf.halo, "wait_timeouts": fails, "host_enqueue_ms_per_frame_rank0": round(host_ms, 3),
+                       "strip_bounds": {"final": bounds, "even": history[0], "tile_ms_without_exchange_per_round": cal_ms, "balanced": bool(world > 1 and args.tiles_balance),
+                                        "note": "16-row half-res strips; boundaries moved by 3 untimed calibration rounds so every rank's tile costs the same"}},
             "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
             "gpu_launches": vkr_tiles.RowTiledFrame.KERNELS_PER_FRAME * K, "clocks": sampler.result()}

@@ -45,9 +45,9 @@ for f in range(frames):
         g, r = got.download()[r0:r1], want.download()[r0:r1]
         if not np.array_equal(g.view(np.uint8), r.view(np.uint8)):
             bad.append((f, name, int((g.view(np.uint8) != r.view(np.uint8)).sum())))
+tf.finish()
 fails = tf.wait_failures()
-dist.barrier()
-tf.close()
+tf.close(dist.barrier)
 dist.destroy_process_group()
 assert not bad and fails == 0, (rank, bad, fails)
 print("rank", rank, "rows", tf.own_rows(True), "ok")

@@ -77,10 +77,14 @@ class PeerSlab:
     def peer_address(self, rank, local_address):
         return self.peers[rank] + (local_address - self.ptr)
 
-    def close(self):
+    def close(self, barrier=None):
+        """Unmap the neighbours' slabs, then free our own.  `barrier` (a callable that synchronises all ranks) is called between
+        the two steps so that no slab is freed while another process still has it mapped."""
         for p in self.peers.values():
             _P.vkr_peer_close(C.c_void_p(p))
         self.peers = {}
+        if barrier is not None:
+            barrier()
         self.tensor = None
         _P.vkr_peer_free(C.c_void_p(self.ptr))
 
@@ -90,6 +94,35 @@ def tile_rows(h2, world, rank):
     strips = (h2 + vkr.ROW_ALIGN - 1) // vkr.ROW_ALIGN
     s0, s1 = vkr_views.shard_range(strips, world, rank)
     return min(s0 * vkr.ROW_ALIGN, h2), min(s1 * vkr.ROW_ALIGN, h2)
+
+
+def balance_bounds(bounds, times_ms, min_strips=3):
+    """New strip boundaries that equalise the per-rank time, taking the measured time of each current tile as uniformly spread
+    over its strips (SSR march length and blur radius vary down the frame, so equal rows are not equal work)."""
+    world = len(times_ms)
+    total = bounds[-1]
+    dens = []
+    for r in range(world):
+        n = max(bounds[r + 1] - bounds[r], 1)
+        dens += [times_ms[r] / n] * (bounds[r + 1] - bounds[r])
+    cum = [0.0]
+    for d in dens:
+        cum.append(cum[-1] + d)
+    out = [0]
+    for r in range(1, world):
+        target = cum[-1] * r / world
+        s = min(range(total + 1), key=lambda i: abs(cum[i] - target))
+        s = max(s, out[-1] + min_strips)
+        out.append(s)
+    out.append(total)
+    for r in range(world - 1, 0, -1):                       # keep min_strips at the tail as well
+        out[r] = min(out[r], out[r + 1] - min_strips)
+    return out
+
+
+def even_bounds(h2, world):
+    strips = (h2 + vkr.ROW_ALIGN - 1) // vkr.ROW_ALIGN
+    return [vkr_views.shard_range(strips, world, r)[0] for r in range(world)] + [strips]
 
 
 def halo_ranges(a, b, halo, height):
@@ -107,12 +140,16 @@ class RowTiledFrame:
     """
     EXCHANGES = ("rays", "reflections", "blurred", "raw", "accumulated_ao", "taa")
 
-    def __init__(self, w, h, rank, world, allgather_bytes, device="cuda", motion_rows=8, lut_size=1024, stream=None, wait_timeout_ms=4000):
+    def __init__(self, w, h, rank, world, allgather_bytes, device="cuda", motion_rows=8, lut_size=1024, stream=None, wait_timeout_ms=4000, bounds=None):
         self.w, self.h, self.rank, self.world, self.stream = w, h, rank, world, stream
         self.device = torch.device(device)
         self.timeout = wait_timeout_ms
         w2, h2 = w // 2, h // 2
-        self.a, self.b = tile_rows(h2, world, rank)              # own half-res rows
+        if bounds is None:
+            self.a, self.b = tile_rows(h2, world, rank)          # own half-res rows: an even split of the 16-row strips
+        else:                                                    # caller-chosen strip boundaries (cost-balanced tiles, see balance_bounds)
+            assert len(bounds) == world + 1 and bounds[0] == 0 and all(x <= y for x, y in zip(bounds, bounds[1:]))
+            self.a, self.b = min(bounds[rank] * vkr.ROW_ALIGN, h2), min(bounds[rank + 1] * vkr.ROW_ALIGN, h2)
         if self.a >= self.b:
             raise vkr.VkrError(f"rank {rank} of {world} owns no rows of a {w}x{h} frame: use fewer ranks")
         self.halo = dict(rays=1, reflections=11, blurred=2, raw=2, accumulated_ao=motion_rows, taa=2 * motion_rows + 2)
@@ -139,15 +176,27 @@ class RowTiledFrame:
             if r is not None:
                 self.slab.open_peer(r, handles[r])
         self.epoch, self.counter, self.frame = 0, 0, 0
+        self.xfer = torch.cuda.Stream(device=self.device)        # halo pushes + flag stores run here, beside the compute stream
 
     # ---- peer plumbing -------------------------------------------------------------------------------------
     def _flag(self, base, exchange, from_upper):
         """Address of the flag (in the slab at `base`) that the upper / lower neighbour raises for `exchange`."""
         return base + 4 * (2 * self.EXCHANGES.index(exchange) + (0 if from_upper else 1))
 
-    def exchange(self, name, img, full_res=False):
-        """Push this rank's boundary rows of `img` into both neighbours' copies, raise their flags, wait for ours."""
-        st = vkr.stream_ptr(self.stream)
+    def _compute_stream(self):
+        return self.stream if self.stream is not None else torch.cuda.current_stream(self.device)
+
+    exchange_enabled = True      # False: render own rows without touching the neighbours (timing a tile on its own)
+
+    def push(self, name, img, full_res=False):
+        """After everything queued on the compute stream so far: copy this rank's boundary rows of `img` into both neighbours'
+        copies and raise their flags — on the transfer stream, so the compute stream goes on with work that does not need them."""
+        if (self.up is None and self.down is None) or not self.exchange_enabled:
+            return
+        ev = torch.cuda.Event()
+        ev.record(self._compute_stream())
+        self.xfer.wait_event(ev)
+        st = C.c_void_p(self.xfer.cuda_stream)
         k = 2 if full_res else 1
         a, b, hgt = self.a * k, self.b * k, img.height
         up, down = halo_ranges(a, b, self.halo[name], hgt)
@@ -157,35 +206,60 @@ class RowTiledFrame:
             peer_img = self.slab.peer_address(nb, img.desc.base)
             vkr.check(_P.vkr_peer_push_rows(img.ptr, 0, rows[0], rows[1], C.c_void_p(peer_img), st))
             vkr.check(_P.vkr_peer_signal(C.c_void_p(self._flag(self.slab.peers[nb], name, from_upper=i_am_upper)), self.epoch, st))
+
+    def wait(self, name, epoch=None):
+        """Hold the compute stream until both neighbours' rows of exchange `name` (of this frame, or of `epoch`) have landed."""
+        if not self.exchange_enabled:
+            return
+        st = vkr.stream_ptr(self.stream)
         for nb, from_upper in ((self.up, True), (self.down, False)):
             if nb is not None:
-                vkr.check(_P.vkr_peer_wait(C.c_void_p(self._flag(self.slab.ptr, name, from_upper)), self.epoch, self.timeout, st))
+                vkr.check(_P.vkr_peer_wait(C.c_void_p(self._flag(self.slab.ptr, name, from_upper)), self.epoch if epoch is None else epoch, self.timeout, st))
+
+    def exchange(self, name, img, full_res=False):
+        """push + wait back to back (no overlap)."""
+        self.push(name, img, full_res)
+        self.wait(name)
 
     # ---- one frame -------------------------------------------------------------------------------------------
     def render_frame(self, dp, gtao_angle_jitter=0.0, swap_depth=True):
-        """src/main.cpp:345-391 + the remaps :416-420 on the CURRENT contents of self.gb (inputs), own rows only."""
+        """src/main.cpp:345-391 + the remaps :416-420 on the CURRENT contents of self.gb (inputs), own rows only.
+
+        The passes are issued in an order that puts one independent pass between every halo push and the pass that reads it
+        (GTAO main behind the ray exchange, the SSR filter behind the raw-AO exchange, ...), and the TAA halo of frame f is only
+        waited for behind frame f+1's Hi-Z: five of the six exchanges are hidden behind compute.  Every pass still sees exactly
+        the inputs of the reference order — passes that are swapped do not depend on each other (main.cpp:375-388: ssr.run only
+        feeds gtao through `raw`, which stays in order)."""
         self.epoch += 1
         P = vkr_views.view_params(dp, self.frame, self.counter, gtao_angle_jitter)
         gb, st = self.gb, self.stream
         half = vkr.make_ext([], rows=(self.a, self.b))
         full = vkr.make_ext([], rows=self.own_rows(full_res=True))
+        self._compute_stream().wait_stream(self.xfer)            # last frame's pushes read images this frame overwrites
         vkr.hiz_build(gb.depth, gb.normal, gb.velocity_vectors, gb.downsampled_normals, gb.downsampled_velocity_vectors, stream=st)
+        if self.frame > 0:
+            self.wait("taa", self.epoch - 1)                     # neighbours are done with frame f-1: their halos may be overwritten
         vkr.sssr_trace_ex(P["trace"], gb.depth, gb.downsampled_normals, gb.material, self.halton, self.pdf, self.rays, self.raw, half, st)
-        self.exchange("rays", self.rays)
-        vkr.sssr_filter_ex(P["trace"], self.rays, gb.depth, gb.albedo, gb.normal, gb.material, self.reflections, half, st)
-        self.exchange("reflections", self.reflections)
-        vkr.sssr_blur_ex(P["blur"], gb.depth, gb.normal, self.reflections, gb.material, self.blurred_history, gb.downsampled_velocity_vectors,
-                         gb.prev_depth, self.blurred, half, st)
-        self.exchange("blurred", self.blurred)
+        self.push("rays", self.rays)
         vkr.gtao_main_ex(P["gtao"], gb.depth, gb.normal, gb.material, self.pdf, self.raw, half, 1, st)
-        self.exchange("raw", self.raw)
+        self.push("raw", self.raw)
+        self.wait("rays")
+        vkr.sssr_filter_ex(P["trace"], self.rays, gb.depth, gb.albedo, gb.normal, gb.material, self.reflections, half, st)
+        self.push("reflections", self.reflections)
+        self.wait("raw")
         vkr.gtao_filter_ex(P["gtao"], gb.depth, self.raw, self.filtered, half, 1, st)
         vkr.gtao_accumulate_ex(P["accum"], gb.depth, gb.prev_depth, self.filtered, self.accumulated_ao, gb.downsampled_velocity_vectors,
                                self.accumulated_history, half, 1, st)
-        self.exchange("accumulated_ao", self.accumulated_ao)
+        self.push("accumulated_ao", self.accumulated_ao)
+        self.wait("reflections")
+        vkr.sssr_blur_ex(P["blur"], gb.depth, gb.normal, self.reflections, gb.material, self.blurred_history, gb.downsampled_velocity_vectors,
+                         gb.prev_depth, self.blurred, half, st)
+        self.push("blurred", self.blurred)
+        self.wait("accumulated_ao")
+        self.wait("blurred")
         vkr.deferred_shading_ex(P["shade"], gb.albedo, gb.normal, gb.material, gb.depth, self.accumulated_ao, self.brdf, self.blurred, self.color_out, full, st)
         vkr.taa_resolve_ex(P["taa"], self.taa_history, gb.prev_depth, gb.depth, gb.velocity_vectors, self.color_out, self.taa_target, full, st)
-        self.exchange("taa", self.taa_target, full_res=True)
+        self.push("taa", self.taa_target, full_res=True)
         out = self.taa_target
         if swap_depth:
             gb.depth, gb.prev_depth = gb.prev_depth, gb.depth
@@ -205,8 +279,15 @@ class RowTiledFrame:
     def wait_failures(self):
         return int(_P.vkr_peer_wait_failed())
 
-    def close(self):
+    def finish(self):
+        """Wait (on the compute stream) for the neighbours' last TAA halo: after this every exchanged row of the last frame is in place."""
+        if self.frame > 0:
+            self.wait("taa", self.epoch)
+
+    def close(self, barrier=None):
         torch.cuda.synchronize()
-        self.slab.close()
+        if barrier is not None:
+            barrier()                                            # nobody is still pushing into our slab
+        self.slab.close(barrier)
 
     KERNELS_PER_FRAME = 10   # hiz tile + tail, trace, filter, blur, gtao main/filter/accumulate, shading, taa (+ signal/wait kernels)
