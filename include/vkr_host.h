@@ -68,6 +68,13 @@ const char* vkr_app_last_tasks(VkrApp* app);
 /* The parameter blocks the optional "SSAO" / "SSR" tasks of the last frame were given (options alt.ssao / alt.ssr; the
  * passes of reference src/ssao.cpp and src/ssr.cpp, which the reference's frame loop does not schedule). */
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out);
+/* ProbeRenderer::render_probe_grid (reference src/probe_renderer.cpp:253-283) on the app's 4x4 grid of 256^2 octahedral probes:
+ * per probe the tasks CubemapProbe (synthetic faces, vkr_synth_cubemap), Cubemap2Octahedral, DownsampleProbe; submitted at once.
+ * With option alt.trace_probe every later frame ends with ProbeTracePass::run into image "probe_reflection". */
+int vkr_app_render_probe_grid(VkrApp* app, const VkrSynthScene* scene, const float* min3, const float* max3);
+/* Descriptor of layer 0 of a named (array) image, the byte distance between its layers and their number:
+ * probe_color probe_depth (16 layers) probe_cube_color probe_cube_distance (6 faces) and every name of vkr_app_get_image. */
+int vkr_app_get_image_array(VkrApp* app, const char* name, VkrImage* out, uint64_t* layer_stride, uint32_t* layers);
 /* Host-side state of the last frame by name: "gtao.angle_offset", "gv.angle_offset" (the angle push constants of the live GTAO
  * and of the variant object behind option alt.gtao_variants). */
 int vkr_app_get_value(VkrApp* app, const char* name, float* out);

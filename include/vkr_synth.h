@@ -72,6 +72,12 @@ int vkr_synth_gbuffer_host(const VkrSynthScene* scene, const VkrDrawTAAParams* p
                            const VkrImage* normal, const VkrImage* material, const VkrImage* velocity,
                            const VkrImage* depth, int threads);
 
+/* Device: the six cube faces of a probe at `position3` (stand-in for ProbeRenderer::render_cubemap, reference
+ * src/probe_renderer.cpp:78-168, shaders/cubemap_probe/shader.frag): cube_color R8G8B8A8_SRGB = albedo, cube_distance
+ * R16_SFLOAT = radial distance, faces in Vulkan order +x -x +y -y +z -z at base + f * face_stride. */
+int vkr_synth_cubemap(const VkrSynthScene* scene, const float* position3, const VkrImage* cube_color, uint64_t color_face_stride,
+                      const VkrImage* cube_distance, uint64_t distance_face_stride, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

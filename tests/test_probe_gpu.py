@@ -96,3 +96,54 @@ def test_probe_validation(cuda):
     d, nrm, out = vkr.Image(64, 32, vkr.D24_UNORM_S8_UINT), vkr.Image(64, 32, vkr.R16G16_UNORM), vkr.Image(64, 32, vkr.R8G8B8A8_UNORM)
     with pytest.raises(vkr.VkrError):
         vkr.trace_probe(k, d, nrm, grid.color_array, grid.depth_array, out)                     # grid_size < 2 ("Ooops", probe_renderer.cpp:266)
+
+
+def test_host_app_probe_grid_and_trace(cuda):
+    """The C++ ProbeRenderer / ProbeTracePass classes behind the host app: the cube faces of the device producer equal the
+    Python producer's, the octahedral probes and their pyramids equal the oracle's on those faces, and the traced reflection
+    equals the oracle's on the app's own probe bytes."""
+    import chain
+    import vkr_host
+    w, h = 320, 180
+    scene = vkr.synth_scene(0, 32)
+    app = vkr_host.App(w, h, device=0)
+    pmin, pmax = (-3.0, 1.0, -5.0), (3.0, 1.0, 5.0)
+    app.render_probe_grid(scene, pmin, pmax)
+    tasks = app.last_tasks()
+    assert tasks == ["CubemapProbe", "Cubemap2Octahedral", "DownsampleProbe"] * 16
+    color, depth = app.readback_array("probe_color"), app.readback_array("probe_depth")
+    cube_c, cube_d = app.readback_array("probe_cube_color"), app.readback_array("probe_cube_distance")
+    grid = vkr_probes.OctahedralProbeGrid(4, 256, device="cpu")
+    grid.min, grid.max = pmin, pmax
+    # the cube map in the app holds the LAST probe of the grid
+    last = vkr_probes.CubeMapSet(1, 128, device="cpu").render_synthetic(scene, [grid.positions()[15]])
+    assert np.array_equal(cube_c.buf.numpy(), last.color.buf.numpy())
+    dd = np.abs(cube_d.buf.numpy().view(np.int16).astype(np.int32) - last.distance.buf.numpy().view(np.int16).astype(np.int32))
+    assert dd.max() <= 1                                                       # fp16 codes: at most one ulp between the two producers
+    ref_c, ref_d = vkr.Image(256, 256, vkr.R8G8B8A8_UNORM, device="cpu"), vkr.Image(256, 256, vkr.R16_UNORM, depth.mips, device="cpu")
+    orc.ok(orc.lib.orc_cube2oct(cube_c.ptr, cube_c.layer_stride, cube_d.ptr, cube_d.layer_stride, ref_c.ptr, ref_d.ptr))
+    orc.ok(orc.lib.orc_probe_downsample(ref_d.ptr))
+    assert (color.layer(15).download() != ref_c.download()).any(axis=-1).mean() <= 1e-4
+    for lod in range(depth.mips):
+        assert (depth.layer(15).download(lod) != ref_d.download(lod)).mean() <= 1e-4, lod
+    assert all((depth.layer(i).download(3) > 0).any() for i in range(16))
+
+    app.set_option("alt.trace_probe", 1)
+    oc = chain.Chain(w, h, chain.OracleBackend(), lut_size=1024)
+    dp = vkr.synth_camera(0, 0, w, h, True)
+    P = oc.begin_frame(scene)
+    app.upload_gbuffer(oc.gb)
+    app.render_frame(dp, chain.angle_jitter(0))
+    assert app.last_tasks()[-1] == "TraceProbe"
+    grid.color_array.buf.copy_(color.buf)
+    grid.depth_array.buf.copy_(depth.buf)
+    params = vkr_probes.ProbeTraceParams(vkr.mat_inverse(dp.camera), *list(dp.fovy_aspect_znear_zfar))
+    k = vkr_probes.trace_constants(grid, params)
+    ref = vkr.Image(w, h, vkr.R8G8B8A8_UNORM, device="cpu")
+    orc.ok(orc.lib.orc_trace_probe(C.byref(k), oc.gb.depth.ptr, oc.gb.normal.ptr, grid.color_array.ptr, grid.color_array.layer_stride, grid.depth_array.ptr,
+                                   grid.depth_array.layer_stride, ref.ptr, 0, 0))
+    g, r = app.readback("probe_reflection").download().astype(np.int32), ref.download().astype(np.int32)
+    assert (r[..., 3] > 0).mean() > 0.02
+    d = np.abs(g - r).max(axis=-1)
+    assert (d > 1).mean() <= 1e-3, ((d > 1).sum(), d.max())
+    app.close()

@@ -158,6 +158,32 @@ __global__ void __launch_bounds__(256) synth_kernel(const VkrSynthScene* __restr
   *((uint32_t*)(depth.p + (size_t)py * depth.pitch) + px) = o.depth;
 }
 
+// Cube faces of a probe (stand-in for ProbeRenderer::render_cubemap, reference src/probe_renderer.cpp:78-168): face f sees
+// direction s' X + t' Y - Z (Vulkan face order +x -x +y -y +z -z) through a 90-degree square camera; colour = the albedo code,
+// distance = |view position| reconstructed from the D24 depth code the G-buffer producer would have written.
+__global__ void __launch_bounds__(256) synth_cube_kernel(const VkrSynthScene* __restrict__ scene_g, float px, float py, float pz, int n, Mip color, Mip dist) {
+  __shared__ VkrSynthScene sc;
+  for (int i = threadIdx.x; i < (int)(sizeof(VkrSynthScene) / 4); i += blockDim.x) ((uint32_t*)&sc)[i] = ((const uint32_t*)scene_g)[i];
+  __syncthreads();
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5), face = blockIdx.z;
+  if (x >= n || y >= n) return;
+  const float AX[6][9] = {{0, 0, -1, 0, -1, 0, -1, 0, 0}, {0, 0, 1, 0, -1, 0, 1, 0, 0}, {1, 0, 0, 0, 0, 1, 0, -1, 0},
+                          {1, 0, 0, 0, 0, -1, 0, 1, 0},   {1, 0, 0, 0, -1, 0, 0, 0, -1}, {-1, 0, 0, 0, -1, 0, 0, 0, 1}};
+  SynthFrameK f;
+  for (int i = 0; i < 16; i++) { f.inv_view[i] = 0.f; f.view[i] = 0.f; f.mvp[i] = (i % 5 == 0) ? 1.f : 0.f; f.prev_mvp[i] = f.mvp[i]; }
+  for (int c = 0; c < 3; c++) for (int r = 0; r < 3; r++) f.inv_view[4 * c + r] = AX[face][3 * c + r];
+  f.inv_view[12] = px; f.inv_view[13] = py; f.inv_view[14] = pz; f.inv_view[15] = 1.f;
+  f.aspect = 1.f; f.tg = 1.f; f.zn = 0.05f; f.zf = 80.f; f.jx = f.jy = 0.f; f.W = n; f.H = n;
+  const SynthOut o = synth_pixel(sc, f, x, y);
+  const double d = (double)o.depth / 16777215.0, zn = 0.05, zf = 80.0;
+  const double z = zn * zf / (d * (zf - zn) - zf);
+  const float cx = 2.0f * ((float)x + 0.5f) / (float)n - 1.0f, cy = 2.0f * ((float)y + 0.5f) / (float)n - 1.0f;
+  const float ray_len = sqrtf((1.0f + cx * cx) + cy * cy);
+  const float distance = (float)(-z) * ray_len;
+  *((uint32_t*)(color.p + (size_t)face * color.ls + (size_t)y * color.pitch) + x) = o.albedo;
+  *((__half*)(dist.p + (size_t)face * dist.ls + (size_t)y * dist.pitch) + x) = __float2half_rn(distance);
+}
+
 static int synth_check(const VkrSynthScene* scene, const VkrDrawTAAParams* p, const VkrImage* albedo, const VkrImage* normal,
                        const VkrImage* material, const VkrImage* velocity, const VkrImage* depth) {
   if (!scene || !p || scene->object_count > VKR_SYNTH_MAX_OBJECTS || !image_ok(albedo, VKR_FORMAT_R8G8B8A8_SRGB) ||
@@ -230,4 +256,29 @@ extern "C" int vkr_synth_gbuffer_host(const VkrSynthScene* scene, const VkrDrawT
   work(0);
   for (auto& th : pool) th.join();
   return VKR_OK;
+}
+
+extern "C" int vkr_synth_cubemap(const VkrSynthScene* scene, const float* position3, const VkrImage* cube_color, uint64_t color_face_stride,
+                                 const VkrImage* cube_distance, uint64_t distance_face_stride, void* stream) {
+  if (!scene || !position3 || scene->object_count > VKR_SYNTH_MAX_OBJECTS || !image_ok(cube_color, VKR_FORMAT_R8G8B8A8_SRGB) ||
+      !image_ok(cube_distance, VKR_FORMAT_R16_SFLOAT) || !color_face_stride || !distance_face_stride) {
+    set_error("synth_cubemap: null argument, unexpected format or missing face stride");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  const uint32_t n = cube_color->width;
+  if (cube_color->height != n || cube_distance->width != n || cube_distance->height != n) {
+    set_error("synth_cubemap: faces must be square and of one size");
+    return VKR_ERR_SIZE_MISMATCH;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  VkrSynthScene* dscene = nullptr;
+  if (cudaMallocAsync(&dscene, sizeof(VkrSynthScene), st) != cudaSuccess) return check_launch("synth scene alloc");
+  cudaMemcpyAsync(dscene, scene, sizeof(VkrSynthScene), cudaMemcpyHostToDevice, st);
+  Mip c = make_mip(cube_color, 0), d = make_mip(cube_distance, 0);
+  c.ls = color_face_stride; d.ls = distance_face_stride;
+  dim3 grid((n + 31) / 32, (n + 7) / 8, 6);
+  synth_cube_kernel<<<grid, 256, 0, st>>>(dscene, position3[0], position3[1], position3[2], (int)n, c, d);
+  int rc = check_launch("synth_cube_kernel");
+  cudaFreeAsync(dscene, st);
+  return rc;
 }

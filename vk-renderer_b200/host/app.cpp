@@ -45,6 +45,11 @@ struct VkrApp {
   ImageResourceId ssao_tex, ssr_tex;
   SSAOPass ssao_pass;
   ScreenSpaceTrace screen_trace;
+  ProbeRenderer probe_renderer;                      // src/probe_renderer.hpp: not instantiated by the reference's main(), off by default
+  OctahedralProbeGrid probe_grid;
+  ProbeTracePass probe_trace;
+  ImageResourceId probe_reflection;
+  bool alt_trace_probe = false, probes_rendered = false;
   GTAO gtao_alt;     // a second GTAO object so the variants do not disturb the live chain's images
   bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false, alt_gtao_variants = false;
   VkrSsrParams last_ssr{};
@@ -56,7 +61,9 @@ struct VkrApp {
         gtao{render_graph, w, h, /*USE_RAY_QUERY*/ false, /*half_res*/ true},                   // main.cpp:265
         ssr{render_graph, w, h}, taa_pass{render_graph, w, h}, shading_pass{render_graph},
         ssao_tex{create_ssao_texture(render_graph, w, h)}, ssr_tex{create_ssr_tex(render_graph, w, h)}, ssao_pass{render_graph, ssao_tex, 0},
-        screen_trace{render_graph, w, h}, gtao_alt{render_graph, w, h, false, true, 2} {
+        screen_trace{render_graph, w, h}, probe_renderer{render_graph, CUBE_SIZE}, probe_grid{render_graph, 4, PROBE_SIZE},
+        gtao_alt{render_graph, w, h, false, true, 2} {
+    { gpu::ImageInfo pr; pr.format = VKR_FORMAT_R8G8B8A8_UNORM; pr.width = w; pr.height = h; probe_reflection = render_graph.create_image(pr); }
     ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
     ssr.preintegrate_brdf(render_graph);
     gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
@@ -111,6 +118,11 @@ struct VkrApp {
       screen_trace.add_filter_pass(render_graph, tp, gbuffer.depth);
       screen_trace.add_accumulate_pass(render_graph, tp, gbuffer.depth, gbuffer.prev_depth);
     }
+    if (alt_trace_probe) {
+      if (!probes_rendered) throw std::runtime_error{"alt.trace_probe: call vkr_app_render_probe_grid first"};
+      ProbeTraceParams pp{glm::inverse(draw_params.camera), fovy, aspect, znear, zfar};
+      probe_trace.run(render_graph, probe_grid, gbuffer.depth, gbuffer.normal, probe_reflection, pp);
+    }
     if (alt_gtao_variants) {
       gtao_alt.angle_jitter = angle_jitter;
       gtao_alt.add_main_pass_graphics(render_graph, gtao_params, gbuffer.depth, gbuffer.normal);
@@ -157,6 +169,11 @@ struct VkrApp {
     else if (name == "brdf") id = ssr.get_preintegrated_brdf();
     else if (name == "ssao") id = ssao_tex;
     else if (name == "ssr_legacy") id = ssr_tex;
+    else if (name == "probe_color") id = probe_grid.color_array;
+    else if (name == "probe_depth") id = probe_grid.depth_array;
+    else if (name == "probe_cube_color") id = probe_renderer.get_cubemap_color();
+    else if (name == "probe_cube_distance") id = probe_renderer.get_cubemap_distance();
+    else if (name == "probe_reflection") id = probe_reflection;
     else if (name == "gv_raw") id = gtao_alt.raw;
     else if (name == "gv_filtered") id = gtao_alt.filtered;
     else if (name == "gv_output") id = r ? gtao_alt.prev_frame : gtao_alt.output;
@@ -281,6 +298,27 @@ int vkr_app_sync(VkrApp* app) {
   VKR_TRY(app->render_graph.wait_idle())
 }
 
+int vkr_app_render_probe_grid(VkrApp* app, const VkrSynthScene* scene, const float* min3, const float* max3) {
+  if (!app || !scene || !min3 || !max3) { host_error("render_probe_grid: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    app->probe_renderer.render_probe_grid(app->render_graph, *scene, vec3{min3[0], min3[1], min3[2]}, vec3{max3[0], max3[1], max3[2]}, app->probe_grid);
+    app->render_graph.submit();
+    app->task_names.clear();
+    for (auto& n : app->render_graph.last_task_names()) { app->task_names += n; app->task_names += '\n'; }
+    app->probes_rendered = true;
+  })
+}
+
+int vkr_app_get_image_array(VkrApp* app, const char* name, VkrImage* out, uint64_t* layer_stride, uint32_t* layers) {
+  if (!app || !name || !out || !layer_stride || !layers) { host_error("get_image_array: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  ImageResourceId id;
+  if (!app->lookup(name, id)) { host_error("get_image_array: unknown image '%s'", name); return VKR_ERR_INVALID_ARGUMENT; }
+  *out = app->render_graph.image(id);
+  *layer_stride = app->render_graph.layer_stride(id);
+  *layers = app->render_graph.get_descriptor(id).array_layers;
+  return VKR_OK;
+}
+
 int vkr_app_get_value(VkrApp* app, const char* name, float* out) {
   if (!app || !name || !out) { host_error("get_value: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
   std::string n = name;
@@ -325,6 +363,7 @@ int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   else if (n == "alt.ssr") app->alt_ssr = v != 0.f;
   else if (n == "alt.screen_trace") app->alt_screen_trace = v != 0.f;
   else if (n == "alt.gtao_variants") app->alt_gtao_variants = v != 0.f;
+  else if (n == "alt.trace_probe") app->alt_trace_probe = v != 0.f;
   else if (n == "alt.ssao_reference_packing") app->ssao_pass.reference_packing = v != 0.f;
   else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
   else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;

@@ -16,6 +16,7 @@
 #include <cstring>
 #include <vector>
 
+#include "../../include/vkr_synth.h"
 #include "rendergraph.hpp"
 
 namespace glmlite {  // the two glm types the pass interface exposes
@@ -268,4 +269,56 @@ struct ScreenSpaceTrace {
 
  private:
   uint32_t frame_count = 0;
+};
+
+// ---- probe_renderer (reference src/probe_renderer.hpp:6-81) ---------------------------------------------------------
+const uint32_t PROBE_SIZE = 256;
+const uint32_t CUBE_SIZE = 128;
+
+struct OctahedralProbe {
+  OctahedralProbe(rendergraph::RenderGraph& graph, uint32_t size = PROBE_SIZE);
+  vec3 pos{0.f, 0.f, 0.f};
+  rendergraph::ImageResourceId color;
+  rendergraph::ImageResourceId depth;
+};
+
+struct OctahedralProbeGrid {
+  OctahedralProbeGrid(rendergraph::RenderGraph& graph, uint32_t grid_sz = 4, uint32_t size = PROBE_SIZE);
+  vec3 min{0.f, 0.f, 0.f};
+  vec3 max{0.f, 0.f, 0.f};
+  uint32_t grid_size{0};
+  rendergraph::ImageResourceId color_array;
+  rendergraph::ImageResourceId depth_array;
+};
+
+// The reference rasterises the cube faces from its SceneRenderer (render_cubemap / render_side, :78-168); here the faces come
+// from the synthetic scene's ray-caster (vkr_synth_cubemap), so `SceneRenderer&` becomes `const VkrSynthScene&`.
+struct ProbeRenderer {
+  ProbeRenderer(rendergraph::RenderGraph& graph, uint32_t cubemap_res = CUBE_SIZE);
+  void render_cubemap(rendergraph::RenderGraph& graph, const VkrSynthScene& scene, const vec3 pos);
+  void render_probe(rendergraph::RenderGraph& graph, const VkrSynthScene& scene, const vec3 pos, OctahedralProbe& probe);
+  void render_probe_grid(rendergraph::RenderGraph& graph, const VkrSynthScene& scene, vec3 min, vec3 max, OctahedralProbeGrid& probe_grid);
+  rendergraph::ImageResourceId get_cubemap_color() const { return cubemap_color; }        // not in the reference: for readback
+  rendergraph::ImageResourceId get_cubemap_distance() const { return cubemap_distance; }
+
+ private:
+  rendergraph::ImageResourceId cubemap_color;
+  rendergraph::ImageResourceId cubemap_distance;
+  void render_octahedral(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId probe_color, rendergraph::ImageResourceId probe_depth,
+                         uint32_t array_layer = 0);
+  void probe_downsample(rendergraph::RenderGraph& graph, rendergraph::ImageResourceId probe_depth, uint32_t array_layer = 0);
+};
+
+struct ProbeTraceParams {
+  glm::mat4 inv_view;  // camera -> world
+  float fovy;
+  float aspect;
+  float znear;
+  float zfar;
+};
+
+struct ProbeTracePass {
+  ProbeTracePass() {}
+  void run(rendergraph::RenderGraph& graph, OctahedralProbeGrid& probe, rendergraph::ImageResourceId gbuffer_depth, rendergraph::ImageResourceId gbuffer_norm,
+           rendergraph::ImageResourceId out_image, const ProbeTraceParams& params);
 };

@@ -44,6 +44,10 @@ lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 lib.vkr_app_bind_gbuffer.restype = C.c_int
 lib.vkr_app_bind_gbuffer.argtypes = [C.c_void_p] + [C.POINTER(vkr.VkrImage)] * 5
 lib.vkr_app_task_timing.restype = C.c_int
+lib.vkr_app_render_probe_grid.restype = C.c_int
+lib.vkr_app_render_probe_grid.argtypes = [C.c_void_p, C.POINTER(vkr.SynthScene), C.POINTER(C.c_float), C.POINTER(C.c_float)]
+lib.vkr_app_get_image_array.restype = C.c_int
+lib.vkr_app_get_image_array.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(vkr.VkrImage), C.POINTER(C.c_uint64), C.POINTER(C.c_uint32)]
 lib.vkr_app_get_value.restype = C.c_int
 lib.vkr_app_get_value.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_float)]
 lib.vkr_app_screen_trace_params.restype = C.c_int
@@ -124,6 +128,24 @@ class App:
         a, r = vkr.SsaoParams(), vkr.SsrParams()
         _check(lib.vkr_app_alt_params(self.h, C.byref(a), C.byref(r)))
         return a, r
+
+    def render_probe_grid(self, scene, pmin, pmax):
+        _check(lib.vkr_app_render_probe_grid(self.h, C.byref(scene), (C.c_float * 3)(*pmin), (C.c_float * 3)(*pmax)))
+
+    def readback_array(self, name):
+        """A named array image (all layers, all mips) as a CPU vkr.ImageArray."""
+        import torch
+        d, stride, layers = vkr.VkrImage(), C.c_uint64(), C.c_uint32()
+        _check(lib.vkr_app_get_image_array(self.h, name.encode(), C.byref(d), C.byref(stride), C.byref(layers)))
+        self.sync()
+        out = vkr.ImageArray(d.width, d.height, d.format, d.mip_count, layers=layers.value, device="cpu")
+        assert out.layer_stride == stride.value
+        nbytes = stride.value * layers.value
+
+        class _Mem:
+            __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (d.base, False), "version": 2}
+        out.buf.copy_(torch.as_tensor(_Mem(), device=f"cuda:{self.device}").cpu())
+        return out
 
     def get_value(self, name):
         v = C.c_float()
