@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvkr_b200.so")
+LIB_PATH = os.environ.get("VKR_B200_LIB") or os.path.join(_HERE, "libvkr_b200.so")   # override: kernel-variant experiments (tools/variant.sh)
 if not os.path.exists(LIB_PATH):
     raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                       "(there is no CPU fallback for the vkr passes)")
