@@ -290,6 +290,7 @@ __device__ __forceinline__ bool tap_is_texel(const Tap& t, int& x, int& y) {
 // single-MUFU reciprocal / square root / division (2 ulp): the IEEE forms cost 8-12 instructions plus a slow-path call
 __device__ __forceinline__ float rcp_fast(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float sqrt_fast(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float rsqrt_fast(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ float div_fast(float a, float b) { return a * rcp_fast(b); }
 __device__ __forceinline__ float dot3f(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
 __device__ __forceinline__ f3 norm3f(f3 a) { float s = rsqrtf(dot3f(a, a)); return mk3(a.x * s, a.y * s, a.z * s); }

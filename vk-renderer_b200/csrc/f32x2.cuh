@@ -20,11 +20,18 @@ __device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 r; asm("mul.rn.f32x2 %0, %1,
 __device__ __forceinline__ f2 add2(f2 a, f2 b) { f2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
 
 
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) { f2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r.v) : "l"(a.v), "l"(b.v)); return r; }
+
 // UNFUSED a * b + c.  ptxas contracts mul.rn.f32x2 followed by add.rn.f32x2 into FFMA2 — unlike the scalar .rn forms,
 // and with -fmad=false too (checked with cuobjdump on CUDA 12.9) — which would change the bits of the paths that must
-// round like the oracle's unfused fp32.  The sum is therefore written as fma(p, one, c) with `one` = 1.0f that ptxas
-// cannot see (it arrives in the kernel's parameter block): p * 1 is exact, so the result is RN(RN(a * b) + c), and the
+// round like the oracle's unfused fp32.  The sum is therefore written as fma(p, one, c) with a 1.0f the compiler cannot
+// fold (it is read from constant memory at run time): p * 1 is exact, so the result is RN(RN(a * b) + c), and the
 // instruction count is the same as mul + add.
+static __constant__ float vkr_opaque_one = 1.0f;
+__device__ __forceinline__ f2 one2() { return dup(vkr_opaque_one); }
+__device__ __forceinline__ f2 add2_unfused(f2 p, f2 c, f2 one) { return fma2(p, one, c); }                       // p is a product
 __device__ __forceinline__ f2 mul_add2_unfused(f2 a, f2 b, f2 c, f2 one) { return fma2(mul2(a, b), one, c); }
+// GLSL mix(a, b, t) = a * (1 - t) + b * t on two value pairs at once, every operation rounded like common.cuh gmix()
+__device__ __forceinline__ f2 gmix2(f2 a, f2 b, float one_minus_t, float t, f2 one) { return fma2(mul2(b, dup(t)), one, mul2(a, dup(one_minus_t))); }
 
 }  // namespace vkr

@@ -4,6 +4,7 @@
 // (reference src/gtao.cpp:84-148,:198-239,:286-347; shaders/gtao/{main,filter,accum}.comp).
 #include <vector>
 #include "brdf.cuh"
+#include "f32x2.cuh"
 
 namespace vkr {
 
@@ -21,19 +22,50 @@ struct GtaoK {
 // Precision: the thickness break compares view-space z of consecutive samples, and z is ill-conditioned in d, so the
 // depth footprint stays the exact unfused bilinear and z the correctly rounded quotient; the horizon cosine itself is a
 // running max of a continuous quantity (value-only: rsqrt normalisation, FMA dot products).
-__device__ __forceinline__ float find_horizon(const Mip& depth, float su, float sv, f3 camera_start, float dirx, float diry,
+// TILE: the CTA has staged the decoded depth texels its taps can reach (clamp-to-edge applied while staging) in shared
+// memory, so a tap is 4 LDS instead of 4 clamped address computations + 4 LDG + 4 D24 decodes.  The bilinear footprint
+// runs on packed fp32 (x with y, top row with bottom row); every operation rounds like the scalar unfused form.
+struct DepthTile { const float* s; int ox, oy; };
+#define GT_SW 72
+#define GT_SH 48
+template <bool TILE>
+__device__ __forceinline__ float find_horizon(const Mip& depth, const DepthTile& tile, float su, float sv, f3 camera_start, float dirx, float diry,
                                               f3 v, const CamF& cam) {
   float h_cos = -1.0f;
   float previous_z = camera_start.z;
+  const f2 one = one2(), suv = pk(su, sv), dir = pk(dirx, diry), wh = pk((float)depth.w, (float)depth.h);
+  const f2 tg2 = pk(cam.aspect_tg, cam.tg), ncs = pk(-camera_start.x, -camera_start.y);
 #pragma unroll 1
   for (int i = 1; i <= 16; i++) {
     const float s = (float)i * 0.0625f;                                      // float(i) / 16, exact
-    const float tu = FA(su, FM(s, dirx)), tv = FA(sv, FM(s, diry));
-    const float z = linearize_rn(sample_d24(depth, tu, tv), cam);
+    const f2 tuv = mul_add2_unfused(dup(s), dir, suv, one);                  // FA(su, FM(s, dirx)), FA(sv, FM(s, diry))
+    float d;
+    if (TILE) {
+      // make_tap + bilerp of common.cuh on the staged window
+      const f2 xy = mul_add2_unfused(tuv, wh, dup(-0.5f), one);
+      float x, y, wx, wy, omx, omy, top, bot;
+      unpk(xy, x, y);
+      const float fx = floorf(x), fy = floorf(y);
+      const f2 w2 = sub2(xy, pk(fx, fy));
+      unpk(w2, wx, wy);
+      unpk(sub2(dup(1.0f), w2), omx, omy);
+      int idx = ((int)fy - tile.oy) * GT_SW + ((int)fx - tile.ox);
+      idx = min(max(idx, 0), GT_SW * (GT_SH - 1) - 2);                       // memory safety only: in range by construction of the window
+      const float* q = tile.s + idx;
+      unpk(gmix2(pk(q[0], q[GT_SW]), pk(q[1], q[GT_SW + 1]), omx, wx, one), top, bot);
+      d = FA(FM(top, omy), FM(bot, wy));
+    } else {
+      float tu, tv;
+      unpk(tuv, tu, tv);
+      d = sample_d24(depth, tu, tv);
+    }
+    const float z = linearize_rn(d, cam);
     if (z > FA(previous_z, MAX_THIKNESS)) break;
     previous_z = z;
-    const f3 off = mk3(fmaf(1.0f - 2.f * tu, z * cam.aspect_tg, -camera_start.x), fmaf(1.0f - 2.f * tv, z * cam.tg, -camera_start.y), z - camera_start.z);
-    const float sample_cos = dot3f(v, off) * rsqrtf(dot3f(off, off));
+    float ox, oy;
+    unpk(fma2(fma2(dup(-2.f), tuv, dup(1.0f)), mul2(dup(z), tg2), ncs), ox, oy);
+    const f3 off = mk3(ox, oy, z - camera_start.z);
+    const float sample_cos = dot3f(v, off) * rsqrt_fast(dot3f(off, off));   // no denormal fix-up: |off|^2 < 1e-38 is a zero offset
     h_cos = fmaxf(h_cos, sample_cos);                                        // a NaN (zero offset) is ignored by both max forms
   }
   return h_cos;
@@ -47,7 +79,8 @@ __device__ __forceinline__ float gtao_direction(int x, int y) { return (1.0f / 1
 // surfaces: whether the argument rounds to 1 or 1 + 2^-23 decides between a finite angle and NaN, and a NaN texel
 // spreads through the 4x4 filter and the temporal history.  Everything feeding it therefore keeps the oracle's
 // unfused IEEE evaluation (once per pixel); the 16-tap horizon search and the closing integral are value-only.
-__device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& k, const CamF& cam, float su, float sv, float frag_depth, f3 camera_pos,
+template <bool TILE>
+__device__ __forceinline__ float slice_occlusion(const Mip& depth, const DepthTile& tile, const GtaoK& k, const CamF& cam, float su, float sv, float frag_depth, f3 camera_pos,
                                                  f3 w0, f3 camera_normal, float rx, float ry, float angle, f3* Lout, bool mis) {
   const float sdx = FM(rx, cosf(angle)), sdy = FM(ry, sinf(angle));
   const f3 sample_end_pos = reconstruct_view_vec(FA(su, sdx), FA(sv, sdy), frag_depth, k.cam);
@@ -56,7 +89,7 @@ __device__ __forceinline__ float slice_occlusion(const Mip& depth, const GtaoK& 
   const f3 normal_projected = camera_normal - dot3(camera_normal, slice_normal) * slice_normal;
   const f3 X = -norm3(cross3(slice_normal, w0));
   const float n = FS(VKR_PI / 2.0f, acosf(dot3(norm3(normal_projected), X)));
-  const float h_cos = find_horizon(depth, su, sv, camera_pos, sdx, sdy, w0, cam);
+  const float h_cos = find_horizon<TILE>(depth, tile, su, sv, camera_pos, sdx, sdy, w0, cam);
   float h = acosf(h_cos);
   h = gmin(FA(n, gmin(FS(h, n), VKR_PI / 2.0f)), h);                        // GLSL min: a NaN n propagates
   const float len = len3(normal_projected);
@@ -74,14 +107,51 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k0, const GtaoK* _
     depth = layer_of(depth, z); normal = layer_of(normal, z); material = layer_of(material, z); pdf = layer_of(pdf, z); raw = layer_of(raw, z);
   }
   const GtaoK& k = LAYERED ? kl : k0;
+  __shared__ float s_tile[GT_SW * GT_SH];
+  __shared__ int s_box[4];
   const int px = blockIdx.x * 32 + (threadIdx.x & 31), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 5);
-  if (px >= k.tw || py >= k.th) return;
+  const bool active = px < k.tw && py < k.th;
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
+  const CamF cam = make_camf(k.cam);
+  const float frag_depth = active ? sample_d24(depth, su, sv) : 1.f;
+
+  // The texels this CTA's horizon taps can reach: each pixel's own texel +- its radius (<= 16 texels) plus the
+  // bilinear footprint.  When the box fits the staging buffer (it does unless the depth level is much finer than the
+  // AO image) the taps read decoded texels from shared memory.
+  {
+    int lox = 0x7fffffff, loy = 0x7fffffff, hix = -0x7fffffff, hiy = -0x7fffffff;
+    if (active && frag_depth < 1.f) {
+      const float rad = gmin(100.0f / len3(reconstruct_view_vec(su, sv, frag_depth, k.cam)), 16.0f);
+      const float xc = fmaf(su, (float)depth.w, -0.5f), yc = fmaf(sv, (float)depth.h, -0.5f);
+      if (rad >= 0.f && fabsf(xc) < 1e6f && fabsf(yc) < 1e6f) {
+        lox = (int)floorf(xc - rad) - 1; hix = (int)floorf(xc + rad) + 2;
+        loy = (int)floorf(yc - rad) - 1; hiy = (int)floorf(yc + rad) + 2;
+      } else {
+        lox = loy = -0x40000000; hix = hiy = 0x40000000;                  // not a sane camera: no staging
+      }
+    }
+    if (threadIdx.x == 0) { s_box[0] = s_box[1] = 0x7fffffff; s_box[2] = s_box[3] = -0x7fffffff; }
+    __syncthreads();
+    lox = __reduce_min_sync(0xFFFFFFFFu, lox); loy = __reduce_min_sync(0xFFFFFFFFu, loy);
+    hix = __reduce_max_sync(0xFFFFFFFFu, hix); hiy = __reduce_max_sync(0xFFFFFFFFu, hiy);
+    if ((threadIdx.x & 31) == 0) { atomicMin(&s_box[0], lox); atomicMin(&s_box[1], loy); atomicMax(&s_box[2], hix); atomicMax(&s_box[3], hiy); }
+    __syncthreads();
+  }
+  DepthTile tile;
+  tile.s = s_tile; tile.ox = s_box[0]; tile.oy = s_box[1];
+  const int bw = s_box[2] - tile.ox + 1, bh = s_box[3] - tile.oy + 1;
+  const bool use_tile = s_box[2] >= tile.ox && bw <= GT_SW && bh <= GT_SH && s_box[3] >= tile.oy;
+  if (use_tile) {
+    for (int t = threadIdx.x; t < bw * bh; t += 256) {
+      const int ly = t / bw, lx = t - ly * bw;
+      const int qx = min(max(tile.ox + lx, 0), depth.w - 1), qy = min(max(tile.oy + ly, 0), depth.h - 1);   // clamp-to-edge per index
+      s_tile[ly * GT_SW + lx] = d24_to_float(ld32(depth, qx, qy));
+    }
+    __syncthreads();
+  }
+  if (!active) return;
   uint2* out = (uint2*)(raw.p + (size_t)py * raw.pitch) + px;
   float ox = 0.f, oy = 1.0f / (2 * VKR_PI);
-  const CamF cam = make_camf(k.cam);
-
-  const float frag_depth = sample_d24(depth, su, sv);
   if (k.use_mis > 0) {                                                     // mis_gtao, main.comp:219-274
     if (frag_depth >= 1.f) { *out = make_uint2(pack_half2(0.f, 1.0f), 0u); return; }
     f3 camera_pos = reconstruct_view_vec(su, sv, frag_depth, k.cam);
@@ -92,7 +162,8 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k0, const GtaoK* _
     float base_angle = FA(gtao_direction(px, py), k.angle_offset);
     float angle = FM(2 * VKR_PI, base_angle);
     f3 L;
-    float occlusion = slice_occlusion(depth, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true);
+    float occlusion = use_tile ? slice_occlusion<true>(depth, tile, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true)
+                               : slice_occlusion<false>(depth, tile, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, &L, true);
 
     float roughness;
     {
@@ -129,7 +200,8 @@ __global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k0, const GtaoK* _
       float sum = 0.f;
       for (int d = 0; d < dirs; d++) {
         float angle = 2 * VKR_PI * (base_angle + (float)d / (float)dirs);
-        sum += slice_occlusion(depth, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false);
+        sum += use_tile ? slice_occlusion<true>(depth, tile, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false)
+                        : slice_occlusion<false>(depth, tile, k, cam, su, sv, frag_depth, camera_pos, w0, camera_normal, rx, ry, angle, nullptr, false);
       }
       ox = 2 * sum / (float)dirs;
     }
