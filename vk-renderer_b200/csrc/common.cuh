@@ -9,6 +9,7 @@
 // (__fmul_rn/__fsub_rn) so the discrete choice is identical to an unfused evaluation.
 #pragma once
 #include <cuda_runtime.h>
+#include "f32x2.cuh"
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include "../../include/vkr_passes.h"
@@ -206,10 +207,29 @@ __device__ __forceinline__ float bilerp(float t00, float t10, float t01, float t
   return gmix(gmix(t00, t10, wx), gmix(t01, t11, wx), wy);
 }
 
+// Two D24 texels decoded at once: div_by_const on a packed pair (same three roundings per lane).
+__device__ __forceinline__ f2 d24x2_to_float(uint32_t ka, uint32_t kb) {
+  const f2 k = pk((float)(ka & 0xFFFFFFu), (float)(kb & 0xFFFFFFu)), r = dup(1.0f / 16777215.0f);
+  const f2 q = mul2(k, r);
+  return fma2(fma2(q, dup(-16777215.0f), k), r, q);
+}
+// textureLod of a D24 level, exact: make_tap + bilerp above, evaluated on packed fp32 (x with y, the left texel column
+// with the right one).  Every lane rounds like the scalar unfused operation it replaces, so the result is bit-identical
+// to bilerp(d24_to_float(..) x 4, wx, wy); it just takes ~13 fewer issue slots.
 __device__ __forceinline__ float sample_d24(const Mip& m, float u, float v, int ox = 0, int oy = 0) {
-  Tap t = make_tap(u, v, m.w, m.h, ox, oy);
-  return bilerp(d24_to_float(ld32(m, t.x0, t.y0)), d24_to_float(ld32(m, t.x1, t.y0)),
-                d24_to_float(ld32(m, t.x0, t.y1)), d24_to_float(ld32(m, t.x1, t.y1)), t.wx, t.wy);
+  const f2 one = one2();
+  const f2 xy = mul_add2_unfused(pk(u, v), pk((float)m.w, (float)m.h), dup(-0.5f), one);
+  float x, y, wx, wy, omx, omy, top, bot;
+  unpk(xy, x, y);
+  const float fx = floorf(x), fy = floorf(y);
+  const f2 w2 = sub2(xy, pk(fx, fy));
+  unpk(w2, wx, wy);
+  unpk(sub2(dup(1.0f), w2), omx, omy);
+  const int x0 = (int)fx + ox, y0 = (int)fy + oy;
+  const int xa = min(max(x0, 0), m.w - 1), xb = min(max(x0 + 1, 0), m.w - 1), ya = min(max(y0, 0), m.h - 1), yb = min(max(y0 + 1, 0), m.h - 1);
+  const f2 left = d24x2_to_float(ld32(m, xa, ya), ld32(m, xa, yb)), right = d24x2_to_float(ld32(m, xb, ya), ld32(m, xb, yb));
+  unpk(gmix2(left, right, omx, wx, one), top, bot);
+  return FA(FM(top, omy), FM(bot, wy));
 }
 
 __device__ __forceinline__ float2 unpack_rg16unorm(uint32_t k) { return make_float2(unorm16_to_float(k & 0xFFFFu), unorm16_to_float(k >> 16)); }

@@ -98,7 +98,7 @@ __device__ __forceinline__ float slice_occlusion(const Mip& depth, const DepthTi
 }
 
 template <bool LAYERED>
-__global__ void __launch_bounds__(256) gtao_main_kernel(GtaoK k0, const GtaoK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf,
+__global__ void __launch_bounds__(256, 5) gtao_main_kernel(GtaoK k0, const GtaoK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf,
                                                         Mip raw, const float* __restrict__ srgb) {
   GtaoK kl;
   if (LAYERED) {

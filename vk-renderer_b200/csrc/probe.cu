@@ -15,8 +15,8 @@ namespace vkr {
 #define PR_ZNEAR 0.05f
 #define PR_ZFAR 80.f
 
-struct f2 { float x, y; };
-__device__ __forceinline__ f2 mk2(float x, float y) { f2 r; r.x = x; r.y = y; return r; }
+struct v2f { float x, y; };
+__device__ __forceinline__ v2f mk2(float x, float y) { v2f r; r.x = x; r.y = y; return r; }
 __device__ __forceinline__ float o_sign_nz(float k) { return (k >= 0.0f) ? 1.0f : -1.0f; }
 __device__ __forceinline__ float sign_g(float x) { return x > 0.0f ? 1.0f : (x < 0.0f ? -1.0f : 0.0f); }
 
@@ -31,7 +31,7 @@ __device__ __forceinline__ f3 oct_unfold(float u, float v) {                    
 }
 __device__ __forceinline__ f3 oct_decode(float u, float v) { return norm3(oct_unfold(u, v)); }
 __device__ __forceinline__ f3 oct_center(float u, float v) { f3 r = oct_unfold(u, v); return norm3(mk3(sign_g(r.x), sign_g(r.y), sign_g(r.z))); }
-__device__ __forceinline__ f2 oct_encode(f3 v) {                                                   // :59-66
+__device__ __forceinline__ v2f oct_encode(f3 v) {                                                   // :59-66
   float l1 = FA(FA(fabsf(v.x), fabsf(v.y)), fabsf(v.z));
   float inv = 1.0f / l1;
   float rx = FM(v.x, inv), ry = FM(v.y, inv);
@@ -183,12 +183,12 @@ __device__ __forceinline__ f3 probe_raymarch(const PyramidView& P, unsigned long
 }
 
 // :277-331
-__device__ __forceinline__ int trace_segment_hi(const ProbeArrays& A, f3 ray_origin, f3 ray_dir, float t0, float t1, float& tmin, int probe_index, f2& stop_tc) {
+__device__ __forceinline__ int trace_segment_hi(const ProbeArrays& A, f3 ray_origin, f3 ray_dir, float t0, float t1, float& tmin, int probe_index, v2f& stop_tc) {
   const float RAY_EPS = 0.001f;
   f3 probe_start = ray_origin + ray_dir * FA(t0, RAY_EPS);
   const f3 probe_end = ray_origin + ray_dir * FS(t1, RAY_EPS);
   { const f3 d = probe_start - probe_end; if (dot3(d, d) < 0.001f) probe_start = ray_dir; }
-  const f2 start_oct = oct_encode(norm3(probe_start)), end_oct = oct_encode(norm3(probe_end));
+  const v2f start_oct = oct_encode(norm3(probe_start)), end_oct = oct_encode(norm3(probe_end));
   const f3 front = oct_center(FM(0.5f, FA(start_oct.x, end_oct.x)), FM(0.5f, FA(start_oct.y, end_oct.y)));
   const float start_depth = FS(encode_oct_depth(dot3(probe_start, front), PR_ZNEAR, PR_ZFAR), 0.0005f);
   const float end_depth = encode_oct_depth(dot3(probe_end, front), PR_ZNEAR, PR_ZFAR);
@@ -210,7 +210,7 @@ __device__ __forceinline__ int trace_segment_hi(const ProbeArrays& A, f3 ray_ori
 }
 
 // :386-412
-__device__ __forceinline__ int trace_probe_one(const ProbeK& k, const ProbeArrays& A, f3 ray_origin, f3 ray_dir, int probe_index, float& tmin, float tmax, f2& hitexc) {
+__device__ __forceinline__ int trace_probe_one(const ProbeK& k, const ProbeArrays& A, f3 ray_origin, f3 ray_dir, int probe_index, float& tmin, float tmax, v2f& hitexc) {
   const float denom = (float)(k.grid_size - 1u);
   const f3 probe_step = mk3(FS(k.probe_max.x, k.probe_min.x) / denom, FS(k.probe_max.y, k.probe_min.y) / denom, FS(k.probe_max.z, k.probe_min.z) / denom);
   const float gy = (float)((uint32_t)probe_index / k.grid_size), gx = (float)((uint32_t)probe_index % k.grid_size);
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(128) trace_probe_kernel(ProbeK k, LaunchX lx, 
   int i = 0, probes_left = 4, hit_probe = -1, result = TRACE_RESULT_UNKNOWN;
   float tmin = 0.f;
   const float tmax = 30.f;
-  f2 hit = mk2(0.f, 0.f);
+  v2f hit = mk2(0.f, 0.f);
   while (probes_left > 0) {
     const int bx = base_probe % (int)k.grid_size, by = base_probe / (int)k.grid_size;              // next_probe :348-354
     const int probe_id = (by + ((i >> 1) & 1)) * (int)k.grid_size + bx + (i & 1);

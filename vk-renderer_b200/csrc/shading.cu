@@ -128,10 +128,17 @@ __global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const 
 #pragma unroll
         for (int i = 0; i < 3; i++) d[j][i] = d24_to_float(ld32(depth1, cx[i], cy[j]));
     }
-    float dl0 = fabsf(FS(bilerp(d[0][0], d[0][1], d[1][0], d[1][1], t1.wx, t1.wy), depth));
-    float dl1 = fabsf(FS(bilerp(d[0][1], d[0][2], d[1][1], d[1][2], t1.wx, t1.wy), depth));
-    float dl2 = fabsf(FS(bilerp(d[1][0], d[1][1], d[2][0], d[2][1], t1.wx, t1.wy), depth));
-    float dl3 = fabsf(FS(bilerp(d[1][1], d[1][2], d[2][1], d[2][2], t1.wx, t1.wy), depth));
+    // the four bilerp(...) of the reference on packed fp32: row j gives the horizontal mixes of its two texel pairs at
+    // once, then rows (0,1) and (1,2) are mixed vertically — each lane rounds like the scalar gmix chain
+    const f2 one = one2();
+    const float omx = FS(1.0f, t1.wx), omy = FS(1.0f, t1.wy);
+    const f2 h0 = gmix2(pk(d[0][0], d[0][1]), pk(d[0][1], d[0][2]), omx, t1.wx, one);
+    const f2 h1 = gmix2(pk(d[1][0], d[1][1]), pk(d[1][1], d[1][2]), omx, t1.wx, one);
+    const f2 h2 = gmix2(pk(d[2][0], d[2][1]), pk(d[2][1], d[2][2]), omx, t1.wx, one);
+    float dl0, dl1, dl2, dl3;
+    unpk(sub2(gmix2(h0, h1, omy, t1.wy, one), dup(depth)), dl0, dl1);
+    unpk(sub2(gmix2(h1, h2, omy, t1.wy, one), dup(depth)), dl2, dl3);
+    dl0 = fabsf(dl0); dl1 = fabsf(dl1); dl2 = fabsf(dl2); dl3 = fabsf(dl3);
     float min_delta = gmin(gmin(dl0, dl1), gmin(dl2, dl3));
     if (min_delta == dl0) { ox = 0; oy = 0; }
     else if (min_delta == dl1) { ox = 1; oy = 0; }

@@ -84,17 +84,30 @@ __global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k0, const TaaK* _
     const unsigned char* rows[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) rows[j] = history.p + (size_t)clampi(iy - 1 + j, H - 1) * history.pitch;
-    f3 t[4][4];
+    // texels as {r, g} pairs + b: the five footprints' red and green run on packed fp32 (same roundings per lane as wsum)
+    f2 trg[4][4];
+    float tb[4][4];
 #pragma unroll
     for (int j = 0; j < 4; j++)
 #pragma unroll
       for (int i = 0; i < 4; i++)
-        if (!((i == 0 || i == 3) && (j == 0 || j == 3))) t[j][i] = unpack_rgb16f(__ldg((const uint2*)rows[j] + xs[i]));
-    f3 hist = wsum3(t[1][1], t[1][2], t[2][1], t[2][2], w);
-    f3 c0 = wsum3(t[1][2], t[1][3], t[2][2], t[2][3], w);   // offset (+1, 0)
-    f3 c1 = wsum3(t[2][1], t[2][2], t[3][1], t[3][2], w);   // offset (0, +1)
-    f3 c2 = wsum3(t[1][0], t[1][1], t[2][0], t[2][1], w);   // offset (-1, 0)
-    f3 c3 = wsum3(t[0][1], t[0][2], t[1][1], t[1][2], w);   // offset (0, -1)
+        if (!((i == 0 || i == 3) && (j == 0 || j == 3))) {
+          const uint2 q = __ldg((const uint2*)rows[j] + xs[i]);
+          const float2 rg = unpack_rg16f(q.x);
+          trg[j][i] = pk(rg.x, rg.y);
+          tb[j][i] = unpack_rg16f(q.y).x;
+        }
+    const f2 w00 = dup(w.w00), w10 = dup(w.w10), w01 = dup(w.w01), w11 = dup(w.w11);
+#define TAA_FOOT(OUT, J, I)                                                                                                           \
+  f3 OUT;                                                                                                                             \
+  unpk(fma2(trg[J + 1][I + 1], w11, fma2(trg[J + 1][I], w01, fma2(trg[J][I + 1], w10, mul2(trg[J][I], w00)))), OUT.x, OUT.y);         \
+  OUT.z = wsum(tb[J][I], tb[J][I + 1], tb[J + 1][I], tb[J + 1][I + 1], w);
+    TAA_FOOT(hist, 1, 1)
+    TAA_FOOT(c0, 1, 2)   // offset (+1, 0)
+    TAA_FOOT(c1, 2, 1)   // offset (0, +1)
+    TAA_FOOT(c2, 1, 0)   // offset (-1, 0)
+    TAA_FOOT(c3, 0, 1)   // offset (0, -1)
+#undef TAA_FOOT
     // min/max/clamp as single FMNMX (differs from the GLSL select form only when a history texel is NaN)
     f3 cmin = mk3(fminf(fminf(c0.x, c1.x), fminf(c2.x, c3.x)), fminf(fminf(c0.y, c1.y), fminf(c2.y, c3.y)), fminf(fminf(c0.z, c1.z), fminf(c2.z, c3.z)));
     f3 cmax = mk3(fmaxf(fmaxf(c0.x, c1.x), fmaxf(c2.x, c3.x)), fmaxf(fmaxf(c0.y, c1.y), fmaxf(c2.y, c3.y)), fmaxf(fmaxf(c0.z, c1.z), fmaxf(c2.z, c3.z)));
