@@ -6,6 +6,9 @@
 #include "brdf.cuh"
 #include "f32x2.cuh"
 
+#ifndef GTAO_MIN_CTAS
+#define GTAO_MIN_CTAS 5   // resident CTAs per SM the register allocation must allow (tools/variant.sh sweeps it)
+#endif
 namespace vkr {
 
 struct GtaoK {
@@ -98,7 +101,7 @@ __device__ __forceinline__ float slice_occlusion(const Mip& depth, const DepthTi
 }
 
 template <bool LAYERED>
-__global__ void __launch_bounds__(256, 5) gtao_main_kernel(GtaoK k0, const GtaoK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf,
+__global__ void __launch_bounds__(256, GTAO_MIN_CTAS) gtao_main_kernel(GtaoK k0, const GtaoK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip normal, Mip material, Mip pdf,
                                                         Mip raw, const float* __restrict__ srgb) {
   GtaoK kl;
   if (LAYERED) {

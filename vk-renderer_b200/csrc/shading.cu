@@ -5,6 +5,9 @@
 #include <vector>
 #include "brdf.cuh"
 
+#ifndef SHADE_MIN_CTAS
+#define SHADE_MIN_CTAS 8   // resident CTAs per SM the register allocation must allow (tools/variant.sh sweeps it)
+#endif
 namespace vkr {
 
 struct ShadeK {
@@ -41,7 +44,7 @@ __device__ __forceinline__ float srgb_encode_fast(float l) {       // linear -> 
 #define SH_HW 19
 #define SH_HH 7
 template <bool SAME, bool LAYERED, bool HALF>
-__global__ void __launch_bounds__(256) deferred_shading_kernel(ShadeK k0, const ShadeK* __restrict__ kv, LaunchX lx, Dim dim, Mip albedo_tex, Mip normal_tex,
+__global__ void __launch_bounds__(256, SHADE_MIN_CTAS) deferred_shading_kernel(ShadeK k0, const ShadeK* __restrict__ kv, LaunchX lx, Dim dim, Mip albedo_tex, Mip normal_tex,
                                                                Mip material_tex, Mip depth0, Mip depth1, Mip occlusion_tex, Mip brdf_tex, Mip reflections_tex,
                                                                Mip out, const float* __restrict__ srgb) {
   ShadeK kl;

@@ -5,6 +5,9 @@
 #include <vector>
 #include "brdf.cuh"
 
+#ifndef FILTER_MIN_CTAS
+#define FILTER_MIN_CTAS 6   // resident CTAs per SM the register allocation must allow (tools/variant.sh sweeps it)
+#endif
 namespace vkr {
 
 struct FilterK {
@@ -30,7 +33,7 @@ struct TapRec {
 // Nothing here selects between discrete alternatives (ray validity is an exact unorm16 compare), so the whole pass runs on
 // the value-only helpers of common.cuh; depth linearisation keeps its exact denominator.
 template <bool LAYERED>
-__global__ void __launch_bounds__(256) sssr_filter_kernel(FilterK k0, const FilterK* __restrict__ kv, LaunchX lx, Dim dim, Mip rays, Mip depth1, Mip albedo_tex,
+__global__ void __launch_bounds__(256, FILTER_MIN_CTAS) sssr_filter_kernel(FilterK k0, const FilterK* __restrict__ kv, LaunchX lx, Dim dim, Mip rays, Mip depth1, Mip albedo_tex,
                                                           Mip normal_tex, Mip material_tex, Mip out, const float* __restrict__ srgb) {
   __shared__ float4 s_a[(FT_W + 2) * (FT_H + 2)];
   __shared__ float4 s_b[(FT_W + 2) * (FT_H + 2)];

@@ -4,6 +4,9 @@
 #include <vector>
 #include "common.cuh"
 
+#ifndef TAA_MIN_CTAS
+#define TAA_MIN_CTAS 6   // resident CTAs per SM the register allocation must allow (tools/variant.sh sweeps it)
+#endif
 namespace vkr {
 
 struct TaaK {
@@ -41,7 +44,7 @@ __device__ __forceinline__ f3 wsum3(f3 a, f3 b, f3 c, f3 d, const TapW& w) {
 // SAME: colour and velocity have the output's extent, so their bilinear footprint at the pixel's own centre is the
 // texel itself (common.cuh tap_is_texel); otherwise the general footprint is evaluated.
 template <bool SAME, bool LAYERED>
-__global__ void __launch_bounds__(256) taa_resolve_kernel(TaaK k0, const TaaK* __restrict__ kv, LaunchX lx, Dim dim, Mip history, Mip prev_depth, Mip depth,
+__global__ void __launch_bounds__(256, TAA_MIN_CTAS) taa_resolve_kernel(TaaK k0, const TaaK* __restrict__ kv, LaunchX lx, Dim dim, Mip history, Mip prev_depth, Mip depth,
                                                           Mip velocity, Mip color, Mip out, const float* __restrict__ srgb) {
   TaaK kl;
   if (LAYERED) {
