@@ -95,29 +95,38 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
   }
   float h = 0.f;
   int i = 0;
+  // horizon sample (:258-262): a running max of a continuous quantity -> value-only arithmetic.
+  // len(v) < 0.3 <=> |v|^2 < 0.09; a zero-length v gives NaN, which both max forms ignore.
+#define TRACE_HORIZON(SURFACE_Z)                                                                                                   \
+  {                                                                                                                                \
+    const f3 v = sub3f(reconstruct_fast(position.x, position.y, SURFACE_Z, camf), view_vec);                                       \
+    const float d2 = dot3f(v, v);                                                                                                  \
+    if (d2 < 0.09f) { /* most samples of a long ray are farther than 0.3: skip the normalisation */                               \
+      float r;                                                                                                                     \
+      asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d2));                                                                     \
+      h = fmaxf(h, dot3f(pixel_normal, v) * r);                                                                                    \
+    }                                                                                                                              \
+  }
+  // The first 15 steps never leave mip 0 (:250), for every ray: a uniform loop with the level's extent, pointer and cell
+  // size as compile-time-indexed constants, no level bookkeeping and an unconditional horizon sample.
+#pragma unroll 1
+  for (; i < 15; ++i) {
+    float mpx = FM(ssx, position.x), mpy = FM(ssy, position.y);
+    float surface_z = fetch_pyramid(P, poff, (int)mpx, (int)mpy, 0);
+    advance_ray(origin, direction, inv_direction, mpx, mpy, rinvx, rinvy, fox, foy, uox, uoy, surface_z, position, current_t);
+    TRACE_HORIZON(surface_z)
+  }
   while (i < 80 && current_mip >= 0) {
     float mpx = FM(resx, position.x), mpy = FM(resy, position.y);
     float surface_z = fetch_pyramid(P, poff, (int)mpx, (int)mpy, current_mip);
     bool skipped = advance_ray(origin, direction, inv_direction, mpx, mpy, rinvx, rinvy, fox, foy, uox, uoy, surface_z, position, current_t);
-    bool mip0sample = i < 15;
-    if (!mip0sample) {
-      current_mip += skipped ? 1 : -1;
-      float f = skipped ? 0.5f : 2.0f, g = skipped ? 2.0f : 0.5f;
-      resx *= f; resy *= f; rinvx *= g; rinvy *= g;
-    }
+    current_mip += skipped ? 1 : -1;
+    float f = skipped ? 0.5f : 2.0f, g = skipped ? 2.0f : 0.5f;
+    resx *= f; resy *= f; rinvx *= g; rinvy *= g;
     ++i;
-    if (current_mip <= 1) {
-      // horizon sample (:258-262): a running max of a continuous quantity -> value-only arithmetic.
-      // len(v) < 0.3 <=> |v|^2 < 0.09; a zero-length v gives NaN, which both max forms ignore.
-      const f3 v = sub3f(reconstruct_fast(position.x, position.y, surface_z, camf), view_vec);
-      const float d2 = dot3f(v, v);
-      if (d2 < 0.09f) {                                   // most samples of a long ray are farther than 0.3: skip the normalisation
-        float r;
-        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d2));
-        h = fmaxf(h, dot3f(pixel_normal, v) * r);
-      }
-    }
+    if (current_mip <= 1) TRACE_HORIZON(surface_z)
   }
+#undef TRACE_HORIZON
   bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
   const f3 out_ray = position;
 
