@@ -7,6 +7,7 @@ Two regimes:
     errors may compound, tolerances are the same and must not drift with the frame index.
 Tolerances: tests/parity.py.
 """
+import ctypes as C
 import json
 import os
 
@@ -71,7 +72,8 @@ def test_lut_kernels(cuda, oracle_luts):
     assert parity.TOLERANCES["brdf"](m), m
 
 
-@pytest.mark.parametrize("w,h,frames,view", [(1280, 720, 3, 0), (640, 360, 4, 3), (256, 256, 3, 5)])
+# 328x200: the half-res images are 164x100, so the 32-wide and 16-high tiles of trace / blur / GTAO end ragged
+@pytest.mark.parametrize("w,h,frames,view", [(1280, 720, 3, 0), (640, 360, 4, 3), (256, 256, 3, 5), (328, 200, 3, 2)])
 def test_pass_level_parity(cuda, oracle_luts, w, h, frames, view):
     import torch
     scene = vkr.synth_scene(view, 64)
@@ -141,3 +143,60 @@ def test_free_running_chain(cuda, w, h, frames):
         if series[-1] < floor or series[-1] < min(series[:-1]) - 3.0:
             failures.append(dict(drift=o, series=series))
     assert not failures, failures
+
+
+@pytest.mark.parametrize("depth_lod,use_mis,two_dirs", [(0, 0, 1), (1, 0, 1), (1, 0, 0), (0, 1, 0)])
+def test_gtao_main_depth_sources(cuda, oracle_luts, depth_lod, use_mis, two_dirs):
+    """GTAO main stages the depth texels its horizon taps can reach in shared memory when their box fits (depth level of
+    the AO image's size: lod 1) and reads global memory otherwise (lod 0: twice as fine, box too large).  Both against the
+    oracle, with and without the second slice direction and the MIS blend (reference gtao/main.comp:185-274)."""
+    import torch
+    w, h = 320, 192
+    scene = vkr.synth_scene(4, 64)
+    pdf_ref, _ = oracle_luts
+    oc = chain.Chain(w, h, chain.OracleBackend(), luts=(pdf_ref, oracle_luts[1]))
+    cc = chain.Chain(w, h, chain.CudaBackend(), luts=(pdf_ref.clone_to("cuda"), oracle_luts[1].clone_to("cuda")))
+    P = oc.begin_frame(scene, view_seed=4)
+    cc.begin_frame(scene, view_seed=4, gbuffer_from=oc.gb)
+    for c in (oc, cc):                                   # Hi-Z and the SSR trace first: raw holds the (occlusion, pdf) the MIS path reads
+        st = c.steps(P)
+        st[0][1]()
+        st[1][1]()
+    torch.cuda.synchronize()
+    sync_images(cc, oc)
+    g = P["gtao"]
+    g.use_mis, g.two_directions = use_mis, two_dirs
+    oc.b.o.ok(oc.b.o.lib.orc_gtao_main(C.byref(g), oc.gb.depth.ptr, oc.gb.normal.ptr, oc.gb.material.ptr, oc.pdf.ptr, oc.raw.ptr, depth_lod, 0, oc.raw.height))
+    vkr.gtao_main(g, cc.gb.depth, cc.gb.normal, cc.gb.material, cc.pdf, cc.raw, depth_lod=depth_lod)
+    torch.cuda.synchronize()
+    m = parity.compare_image("raw", cc.raw, oc.raw, task="GTAO_main")
+    print(depth_lod, use_mis, two_dirs, m)
+    assert parity.TOLERANCES["raw"](m), m
+
+
+@pytest.mark.parametrize("max_roughness,accumulate,disable_blur", [(1.0, 0, 0), (0.25, 1, 0), (1.0, 1, 1), (0.0, 0, 0)])
+def test_blur_radius_classes(cuda, oracle_luts, max_roughness, accumulate, disable_blur):
+    """The blur's window follows the material: radius 11 at full roughness, 1 with the blur disabled or max_roughness 0
+    (reference advanced_ssr/blur.comp:39-53).  The CUDA kernel walks row PAIRS, so the small and the odd/even aligned
+    windows, the mixed-radius warps at material edges and the ragged tiles (164x100 half-res) are all exercised here."""
+    import torch
+    w, h = 328, 200
+    scene = vkr.synth_scene(6, 64)
+    oc = chain.Chain(w, h, chain.OracleBackend(), luts=oracle_luts)
+    cc = chain.Chain(w, h, chain.CudaBackend(), luts=(oracle_luts[0].clone_to("cuda"), oracle_luts[1].clone_to("cuda")))
+    for f in range(2):                                   # second frame: a real history for the temporal blend
+        P = oc.begin_frame(scene, view_seed=6)
+        cc.begin_frame(scene, view_seed=6, gbuffer_from=oc.gb)
+        for t in range(3):                               # Hi-Z, trace, filter on the oracle side only; the blur is judged on its inputs
+            oc.steps(P)[t][1]()
+        b = P["blur"]
+        b.max_roughness, b.accumulate, b.disable_blur = max_roughness, accumulate, disable_blur
+        sync_images(cc, oc)
+        oc.steps(P)[3][1]()
+        cc.steps(P)[3][1]()
+        torch.cuda.synchronize()
+        m = parity.compare_image("blurred", cc.images()["blurred"], oc.images()["blurred"], task="SSSR_blur")
+        print(f, max_roughness, accumulate, disable_blur, m)
+        assert parity.TOLERANCES["blurred"](m), m
+        oc.end_frame()
+        cc.end_frame()

@@ -352,14 +352,17 @@ extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, c
   const bool same = same_extent(dvelocity, out_blurred) && out_blurred->width <= 8192 && out_blurred->height <= 8192;
   auto kern = same ? (kv ? sssr_blur_kernel<true, true> : sssr_blur_kernel<true, false>) : (kv ? sssr_blur_kernel<false, true> : sssr_blur_kernel<false, false>);
   {
-    static bool once[4] = {false, false, false, false};      // opt in to > 48 KB of dynamic shared memory, once per instantiation
+    // opt in to > 48 KB of dynamic shared memory: a per-device, per-instantiation attribute (set once each)
+    static unsigned char done[64][4];
+    int dev = 0;
+    cudaGetDevice(&dev);
     const int id = (same ? 2 : 0) + (kv ? 1 : 0);
-    if (!once[id]) {
+    if (dev < 0 || dev >= 64 || !done[dev][id]) {
       if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BLUR_SMEM_BYTES) != cudaSuccess) {
         set_error("sssr_blur: cannot reserve shared memory");
         return VKR_ERR_CUDA;
       }
-      once[id] = true;
+      if (dev >= 0 && dev < 64) done[dev][id] = 1;
     }
   }
   kern<<<grid, 256, BLUR_SMEM_BYTES, st>>>(k, kv, LaunchX{x.yb0}, make_dim(out_blurred->width, out_blurred->height), make_mip(depth, 1, x, 0), make_mip(normal, 0, x, 1),

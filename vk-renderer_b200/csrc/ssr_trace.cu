@@ -7,6 +7,9 @@
 #include "brdf.cuh"
 #include "march.cuh"
 
+#ifndef TRACE_UNROLL_A
+#define TRACE_UNROLL_A 1
+#endif
 namespace vkr {
 
 struct TraceK {
@@ -109,7 +112,8 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
   }
   // The first 15 steps never leave mip 0 (:250), for every ray: a uniform loop with the level's extent, pointer and cell
   // size as compile-time-indexed constants, no level bookkeeping and an unconditional horizon sample.
-#pragma unroll 1
+  constexpr int unroll_a = TRACE_UNROLL_A;
+#pragma unroll unroll_a
   for (; i < 15; ++i) {
     float mpx = FM(ssx, position.x), mpy = FM(ssy, position.y);
     float surface_z = fetch_pyramid(P, poff, (int)mpx, (int)mpy, 0);
