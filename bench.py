@@ -276,6 +276,18 @@ def run_ours(args, rank, world):
     if os.path.exists(tpath):
         traffic = json.load(open(tpath)).get(f"{w}x{h}", {}).get(dname)
     chain_alg = 128.0 * npix
+    # why the HBM fraction is low: the chain's executed warp instructions (same ncu capture) against the issue slots the
+    # frame time offers (SMs x 4 schedulers x the SM clock sampled during the timed region)
+    issue = None
+    clocks = sampler.result()
+    if os.path.exists(tpath) and clocks.get("sm_mhz"):
+        winst = json.load(open(tpath)).get(f"{w}x{h}:warp_inst")
+        if winst:
+            import torch
+            sms = torch.cuda.get_device_properties(0).multi_processor_count
+            total = float(sum(winst.values()))
+            issue = {"warp_inst_per_frame": total, "slots_per_frame": ms_step * 1e-3 * sms * 4 * clocks["sm_mhz"] * 1e6,
+                     "frac": total / (ms_step * 1e-3 * sms * 4 * clocks["sm_mhz"] * 1e6), "source": "profiles/traffic.json (smsp__inst_executed.sum)"}
     line = {"metric": "chain_throughput", "value": value, "unit": "Gpix/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {w}x{h} TAA sequence with synthetic velocity (BASELINE configs[2])",
@@ -284,9 +296,9 @@ def run_ours(args, rank, world):
             "roofline": {"bound": "hbm", "kernel": dname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": avg_ms,
                          "chain": {"alg_bytes_per_frame": chain_alg, "achieved": chain_alg / (ms_step * 1e-3) / 1e9,
-                                   "frac": chain_alg / (ms_step * 1e-3) / 1e9 / peak},
+                                   "frac": chain_alg / (ms_step * 1e-3) / 1e9 / peak, "issue_slots": issue},
                          "per_task_ms": {k: v[0] / max(v[1], 1) for k, v in tasks.items()}},
-            "gpu_launches": KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+            "gpu_launches": KERNELS_PER_FRAME * K, "clocks": clocks}
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:

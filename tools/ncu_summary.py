@@ -35,7 +35,7 @@ def unit_scale(key, want):
 TASK = {"hiz_tile": "DownsampleGbuffer+DownsampleDepth", "sssr_trace": "SSSR_trace", "sssr_filter": "SSSR_filter", "sssr_blur": "SSSR_blur",
         "gtao_main": "GTAO_main", "gtao_filter": "GTAO_filter", "gtao_accumulate": "GTAO_accumulate", "deferred_shading": "DeferedShading",
         "taa_resolve": "TAA"}
-seen, kernels, traffic = set(), [], {}
+seen, kernels, traffic, winst = set(), [], {}, {}
 for r in rows[2:]:
     d = dict(zip(hdr, r))
     name = d["Kernel Name"].split("(")[0].replace("vkr::", "").strip()
@@ -60,10 +60,12 @@ for r in rows[2:]:
     for key, task in TASK.items():
         if key in name and rd is not None and wr is not None:
             traffic[task] = traffic.get(task, 0.0) + (rd + wr) * 1e6       # hiz: tile kernel only (the tail kernel adds ~12 KB)
+            winst[task] = winst.get(task, 0.0) + (kernels[-1]["warp_inst"] or 0.0)
 json.dump({"cmd": cmd, "size": size, "note": note, "kernels": kernels}, open(out, "w"), indent=1)
 tpath = os.path.join(os.path.dirname(out), "traffic.json")
 tj = json.load(open(tpath)) if os.path.exists(tpath) else {}
 tj[size] = traffic
+tj[size + ":warp_inst"] = winst                 # executed warp instructions per launch (smsp__inst_executed.sum)
 tj["source"] = f"{out} (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
 json.dump(tj, open(tpath, "w"), indent=1)
 for kk in kernels:
