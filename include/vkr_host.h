@@ -65,6 +65,10 @@ int vkr_app_sync(VkrApp* app);
 void* vkr_app_stream(VkrApp* app);
 /* Names of the tasks replayed by the last submit, '\n'-separated (for tests). */
 const char* vkr_app_last_tasks(VkrApp* app);
+/* One character per task of the last submit, in the same order: '0' = issued on the app's stream, '1' = on the rendergraph's
+ * second stream (independent branches of a frame run side by side; option "graph.concurrent_branches", default 1; always '0'
+ * while task timing is on). */
+const char* vkr_app_last_lanes(VkrApp* app);
 /* The parameter blocks the optional "SSAO" / "SSR" tasks of the last frame were given (options alt.ssao / alt.ssr; the
  * passes of reference src/ssao.cpp and src/ssr.cpp, which the reference's frame loop does not schedule). */
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out);
@@ -81,7 +85,7 @@ int vkr_app_get_value(VkrApp* app, const char* name, float* out);
 /* Likewise for the "ScreenTrace" task (option alt.screen_trace; reference src/screen_trace.cpp). */
 int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out);
 /* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the
- * whole DownsamplePass instead of the per-task calls. */
+ * whole DownsamplePass instead of the per-task calls.  graph.concurrent_branches: see vkr_app_last_lanes. */
 int vkr_app_set_option(VkrApp* app, const char* name, float value);
 
 #ifdef __cplusplus

@@ -73,3 +73,40 @@ def test_device_producer_equals_host_twin(cuda):
                 ga, gb_ = ga.view(np.uint16), gb_.view(np.uint16)
             mism = float((ga != gb_).mean())
             assert mism <= 1e-5, (name, mism)      # a handful of silhouette pixels may flip on libm-free but FMA-free code paths
+
+
+def test_rendergraph_branches_overlap_and_change_nothing(cuda):
+    """The rendergraph issues the frame's independent branches on two streams from the tasks' declared image uses
+    (SSR filter + blur next to the three GTAO tasks).  The lanes are the expected ones, task timing forces one stream,
+    and six frames with and without the second stream end in bit-identical images (every hazard is carried by an event)."""
+    import vkr_host
+    w, h, frames = 640, 360, 6
+    scene = vkr.synth_scene(3, 64)
+    outs = {}
+    cams = [vkr.synth_camera(1, f, w, h, True) for f in range(frames)]
+    host_gbs = []
+    for f in range(frames):                              # host twin of the producer: identical input bytes for every mode
+        g = vkr.Gbuffer(w, h, device="cpu")
+        vkr.synth_gbuffer(scene, cams[f], g)
+        host_gbs.append(g)
+    for mode in ("two_lanes", "one_lane", "timed"):
+        app = vkr_host.App(w, h)
+        app.set_option("graph.concurrent_branches", 0.0 if mode == "one_lane" else 1.0)
+        if mode == "timed":
+            app.task_timing(True)
+        for f in range(frames):
+            app.upload_gbuffer(host_gbs[f])
+            app.render_frame(cams[f], chain.angle_jitter(f))
+        tasks, lanes = app.last_tasks(), app.last_lanes()
+        assert len(tasks) == len(lanes) == 9
+        if mode == "two_lanes":
+            assert dict(zip(tasks, lanes)) == {"DownsampleGbuffer+DownsampleDepth": 0, "SSSR_trace": 0, "SSSR_filter": 0, "SSSR_blur": 0, "GTAO_main": 1,
+                                               "GTAO_filter": 1, "GTAO_accumulate": 1, "DeferedShading": 0, "TAA": 0}
+        else:
+            assert lanes == [0] * 9
+        outs[mode] = {n: app.readback(n).download() for n in ("rays", "raw", "filtered", "accumulated_ao", "reflections", "blurred", "color", "taa")}
+        app.close()
+    for mode in ("one_lane", "timed"):
+        for n, a in outs["two_lanes"].items():
+            b = outs[mode][n]
+            assert a.tobytes() == b.tobytes(), (mode, n)

@@ -53,7 +53,7 @@ struct VkrApp {
   GTAO gtao_alt;     // a second GTAO object so the variants do not disturb the live chain's images
   bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false, alt_gtao_variants = false;
   VkrSsrParams last_ssr{};
-  std::string task_names;
+  std::string task_names, task_lanes;
   uint64_t frames = 0;
 
   VkrApp(int device, uint32_t w, uint32_t h, void* stream)
@@ -135,6 +135,8 @@ struct VkrApp {
     render_graph.submit();                                                                        // :402
     task_names.clear();
     for (auto& n : render_graph.last_task_names()) { task_names += n; task_names += '\n'; }
+    task_lanes.clear();
+    for (int l : render_graph.last_task_lanes()) task_lanes += (char)('0' + l);
 
     render_graph.remap(gbuffer.depth, gbuffer.prev_depth);                                        // main.cpp:416-420
     render_graph.remap(gtao.output, gtao.prev_frame);
@@ -305,6 +307,8 @@ int vkr_app_render_probe_grid(VkrApp* app, const VkrSynthScene* scene, const flo
     app->render_graph.submit();
     app->task_names.clear();
     for (auto& n : app->render_graph.last_task_names()) { app->task_names += n; app->task_names += '\n'; }
+    app->task_lanes.clear();
+    for (int l : app->render_graph.last_task_lanes()) app->task_lanes += (char)('0' + l);
     app->probes_rendered = true;
   })
 }
@@ -343,11 +347,13 @@ int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_o
 
 void* vkr_app_stream(VkrApp* app) { return app ? app->render_graph.stream() : nullptr; }
 const char* vkr_app_last_tasks(VkrApp* app) { return app ? app->task_names.c_str() : ""; }
+const char* vkr_app_last_lanes(VkrApp* app) { return app ? app->task_lanes.c_str() : ""; }
 
 int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   if (!app || !name) return VKR_ERR_INVALID_ARGUMENT;
   std::string n = name;
   if (n == "fused_hiz") app->downsample_pass.fused = v != 0.f;
+  else if (n == "graph.concurrent_branches") app->render_graph.enable_concurrent_branches(v != 0.f);
   else if (n == "gtao.mis") app->gtao.mis_gtao = v != 0.f;
   else if (n == "gtao.two_directions") app->gtao.two_directions = v != 0.f;
   else if (n == "gtao.only_reflections") app->gtao.only_reflections = v != 0.f;

@@ -36,6 +36,8 @@ RenderGraph::~RenderGraph() {
   for (void* p : allocations) cudaFree(p);
   for (auto& p : pending_) { cudaEventDestroy((cudaEvent_t)p.start); cudaEventDestroy((cudaEvent_t)p.stop); }
   for (void* e : event_pool_) cudaEventDestroy((cudaEvent_t)e);
+  for (void* e : sync_events_) cudaEventDestroy((cudaEvent_t)e);
+  if (aux_stream_) cudaStreamDestroy((cudaStream_t)aux_stream_);
 }
 
 void* RenderGraph::get_event() {
@@ -111,41 +113,101 @@ void RenderGraph::remap(ImageResourceId src, ImageResourceId dst) {
 void RenderGraph::submit() {
   cuda_check(cudaSetDevice(device_), "cudaSetDevice");
   RenderResources resources{*this};
-  gpu::CmdContext cmd{stream_};
   last_names.clear();
+  last_lanes.clear();
   std::vector<std::unique_ptr<BaseTask>> run;
   run.swap(tasks);  // a task may not enqueue tasks for this submit
-  for (auto& t : run) {
-    last_names.push_back(t->name);
-    if (timing_) {
-      Pending p{t->name, get_event(), get_event()};
-      cuda_check(cudaEventRecord((cudaEvent_t)p.start, (cudaStream_t)stream_), "cudaEventRecord");
-      t->write_commands(resources, cmd);
-      cuda_check(cudaEventRecord((cudaEvent_t)p.stop, (cudaStream_t)stream_), "cudaEventRecord");
-      pending_.push_back(p);
-    } else {
-      t->write_commands(resources, cmd);
+  if (timing_ || !concurrent_ || run.size() < 3) {
+    gpu::CmdContext cmd{stream_};
+    for (auto& t : run) {
+      last_names.push_back(t->name);
+      last_lanes.push_back(0);
+      if (timing_) {
+        Pending p{t->name, get_event(), get_event()};
+        cuda_check(cudaEventRecord((cudaEvent_t)p.start, (cudaStream_t)stream_), "cudaEventRecord");
+        t->write_commands(resources, cmd);
+        cuda_check(cudaEventRecord((cudaEvent_t)p.stop, (cudaStream_t)stream_), "cudaEventRecord");
+        pending_.push_back(p);
+      } else {
+        t->write_commands(resources, cmd);
+      }
     }
+    return;
   }
+
+  // Two lanes.  Dependencies at whole-image granularity from the declared uses: a read depends on the image's last
+  // writer; a write on its last writer and on every reader since.
+  if (!aux_stream_) {
+    cudaStream_t s;
+    cuda_check(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking), "cudaStreamCreate");
+    aux_stream_ = s;
+  }
+  while (sync_events_.size() < run.size() + 1) {
+    cudaEvent_t e;
+    cuda_check(cudaEventCreateWithFlags(&e, cudaEventDisableTiming), "cudaEventCreate");
+    sync_events_.push_back(e);
+  }
+  const int n = (int)run.size();
+  std::vector<int> last_writer(slots.size(), -1), lane(n, 0);
+  std::vector<std::vector<int>> readers(slots.size());
+  void* lane_stream[2] = {stream_, aux_stream_};
+  int lane_last[2] = {-1, -1};
+  bool aux_used = false;
+  // the aux lane starts after everything already queued on the graph's stream
+  cuda_check(cudaEventRecord((cudaEvent_t)sync_events_[n], (cudaStream_t)stream_), "cudaEventRecord");
+  cuda_check(cudaStreamWaitEvent((cudaStream_t)aux_stream_, (cudaEvent_t)sync_events_[n], 0), "cudaStreamWaitEvent");
+  for (int i = 0; i < n; i++) {
+    BaseTask& t = *run[i];
+    std::vector<int> deps;
+    auto add = [&](int d) { if (d >= 0 && std::find(deps.begin(), deps.end(), d) == deps.end()) deps.push_back(d); };
+    for (const ImageUse& u : t.uses) {
+      add(last_writer[u.slot]);
+      if (u.write) for (int r : readers[u.slot]) add(r);
+    }
+    auto is_dep = [&](int d) { return d >= 0 && std::find(deps.begin(), deps.end(), d) != deps.end(); };
+    int l = 0;
+    if (!t.uses.empty() && i > 0) {          // a task that declares nothing is ordered after everything: lane 0, all deps
+      if (is_dep(lane_last[0]) || lane_last[0] < 0) l = 0;
+      else if (is_dep(lane_last[1]) || lane_last[1] < 0) l = 1;
+      else l = 1 - lane[i - 1];
+    }
+    if (t.uses.empty()) for (int d = 0; d < i; d++) add(d);
+    lane[i] = l;
+    for (int d : deps)
+      if (lane[d] != l) cuda_check(cudaStreamWaitEvent((cudaStream_t)lane_stream[l], (cudaEvent_t)sync_events_[d], 0), "cudaStreamWaitEvent");
+    gpu::CmdContext cmd{lane_stream[l]};
+    t.write_commands(resources, cmd);
+    cuda_check(cudaEventRecord((cudaEvent_t)sync_events_[i], (cudaStream_t)lane_stream[l]), "cudaEventRecord");
+    lane_last[l] = i;
+    aux_used |= l == 1;
+    for (const ImageUse& u : t.uses) {
+      if (u.write) { last_writer[u.slot] = i; readers[u.slot].clear(); }
+      else readers[u.slot].push_back(i);
+    }
+    last_names.push_back(t.name);
+    last_lanes.push_back(l);
+  }
+  if (aux_used) cuda_check(cudaStreamWaitEvent((cudaStream_t)stream_, (cudaEvent_t)sync_events_[lane_last[1]], 0), "cudaStreamWaitEvent");
 }
 
 void RenderGraph::wait_idle() { cuda_check(cudaStreamSynchronize((cudaStream_t)stream_), "cudaStreamSynchronize"); }
 
-ImageViewId RenderGraphBuilder::make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count) {
+ImageViewId RenderGraphBuilder::make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, bool write) {
   const VkrImage& d = graph.image(id);
+  if (uses_) uses_->push_back(ImageUse{(uint32_t)id.get_index(), write});
   if (base_mip + mip_count > d.mip_count || mip_count == 0) throw std::runtime_error("Image subresource out of range");  // rendergraph.cpp:390-392
   gpu::ImageViewRange r;
   r.base_mip = base_mip; r.mips_count = mip_count;
   return ImageViewId{id, r};
 }
 
-ImageViewId RenderGraphBuilder::use_color_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
-ImageViewId RenderGraphBuilder::use_depth_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
-ImageViewId RenderGraphBuilder::use_storage_image(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1); }
+ImageViewId RenderGraphBuilder::use_color_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1, true); }
+ImageViewId RenderGraphBuilder::use_depth_attachment(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1, true); }
+ImageViewId RenderGraphBuilder::use_storage_image(ImageResourceId id, uint32_t mip, uint32_t) { return make_view(id, mip, 1, true); }
 ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t, uint32_t) {
-  return make_view(id, base_mip, mip_count);
+  return make_view(id, base_mip, mip_count, false);
 }
-ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id) { return make_view(id, 0, graph.image(id).mip_count); }
+ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id) { return make_view(id, 0, graph.image(id).mip_count, false); }
 gpu::ImageInfo RenderGraphBuilder::get_image_info(ImageResourceId id) { return graph.get_descriptor(id); }
 
 const VkrImage* RenderResources::get_image(const ImageViewId& ref) const { return &graph.image(ref.get_id()); }

@@ -72,11 +72,15 @@ struct ImageViewId {
 
 struct RenderGraph;
 
-// reference rendergraph.hpp:17-55.  Usage declarations keep their names; they only validate the
-// subresource range (reference rendergraph.cpp:390-392 "Image subresource out of range") because
-// hazards are resolved by stream order.
+// One declared use of an image by a task: whole-image granularity (slot index at record time), read or write.
+struct ImageUse { uint32_t slot; bool write; };
+
+// reference rendergraph.hpp:17-55.  Usage declarations keep their names; they validate the subresource range
+// (reference rendergraph.cpp:390-392 "Image subresource out of range") and record the image as read or written by the
+// task.  Where the reference derives layout transitions and barriers from these declarations, submit() derives which
+// tasks of a frame may run side by side on two CUDA streams (see RenderGraph::submit).
 struct RenderGraphBuilder {
-  explicit RenderGraphBuilder(RenderGraph& g) : graph{g} {}
+  explicit RenderGraphBuilder(RenderGraph& g, std::vector<ImageUse>* uses = nullptr) : graph{g}, uses_{uses} {}
   ImageViewId use_color_attachment(ImageResourceId id, uint32_t mip, uint32_t layer);
   ImageViewId use_depth_attachment(ImageResourceId id, uint32_t mip, uint32_t layer);
   ImageViewId use_storage_image(ImageResourceId id, uint32_t mip, uint32_t layer);
@@ -86,7 +90,8 @@ struct RenderGraphBuilder {
 
  private:
   RenderGraph& graph;
-  ImageViewId make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count);
+  std::vector<ImageUse>* uses_;
+  ImageViewId make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, bool write);
 };
 
 // reference rendergraph.hpp:57-83: resolves ids to memory at replay time (after any remap).
@@ -105,6 +110,7 @@ struct BaseTask {
   virtual void write_commands(RenderResources&, gpu::CmdContext&) = 0;
   virtual ~BaseTask() {}
   std::string name;
+  std::vector<ImageUse> uses;   // filled by the builder while the task is declared
 };
 
 template <typename TaskData>
@@ -129,16 +135,25 @@ struct RenderGraph {
 
   template <typename TaskData>
   void add_task(const std::string& name, TaskCreateCB<TaskData> create_cb, TaskRunCB<TaskData> run_cb) {  // reference :116-128
-    RenderGraphBuilder builder{*this};
     std::unique_ptr<Task<TaskData>> ptr{new Task<TaskData>{name}};
+    RenderGraphBuilder builder{*this, &ptr->uses};
     create_cb(ptr->data, builder);
     ptr->callback = run_cb;
     tasks.push_back(std::move(ptr));
   }
 
-  // Replays the recorded tasks in order on the graph's stream and clears the list (reference
-  // rendergraph.cpp:271-337 minus barriers / present).  Asynchronous; wait_idle() joins.
+  // Replays the recorded tasks and clears the list (reference rendergraph.cpp:271-337 minus layout transitions /
+  // present).  Asynchronous; wait_idle() joins.  Tasks are issued in recording order.  With concurrent branches enabled
+  // (default) a task none of whose declared images was written by — or, for the images it writes, read by — the task
+  // issued just before it goes to a second stream, so independent branches of the frame (here the SSR filter + blur
+  // against the three GTAO tasks) share the GPU and fill each other's tails and latency-bound phases; every true
+  // dependency across the two streams is carried by an event, and the second stream is joined back into the graph's
+  // stream before submit() returns.  Per-task timing needs tasks that do not overlap: while it is on, or with
+  // concurrent branches off, everything runs on the one stream.
   void submit();
+  void enable_concurrent_branches(bool on) { concurrent_ = on; }
+  // lane (0 = the graph's stream, 1 = the second one) each task of the last submit ran on
+  const std::vector<int>& last_task_lanes() const { return last_lanes; }
   void wait_idle();
 
   ImageResourceId create_image(const gpu::ImageInfo& info);  // zero-initialised device memory
@@ -175,6 +190,10 @@ struct RenderGraph {
   void* get_event();
   std::vector<std::unique_ptr<BaseTask>> tasks;
   std::vector<std::string> last_names;
+  std::vector<int> last_lanes;
+  bool concurrent_ = true;
+  void* aux_stream_ = nullptr;          // created on first use
+  std::vector<void*> sync_events_;      // cudaEventDisableTiming, one per task of a submit, reused
   void* stream_ = nullptr;
   bool owns_stream_ = true;
   int device_ = 0;

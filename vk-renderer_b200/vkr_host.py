@@ -37,6 +37,8 @@ lib.vkr_app_stream.restype = C.c_void_p
 lib.vkr_app_stream.argtypes = [C.c_void_p]
 lib.vkr_app_last_tasks.restype = C.c_char_p
 lib.vkr_app_last_tasks.argtypes = [C.c_void_p]
+lib.vkr_app_last_lanes.restype = C.c_char_p
+lib.vkr_app_last_lanes.argtypes = [C.c_void_p]
 lib.vkr_app_set_option.restype = C.c_int
 lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 
@@ -159,6 +161,10 @@ class App:
 
     def last_tasks(self):
         return lib.vkr_app_last_tasks(self.h).decode().split()
+
+    def last_lanes(self):
+        """Stream lane (0 or 1) of each task of the last frame, in the order of last_tasks()."""
+        return [int(c) for c in lib.vkr_app_last_lanes(self.h).decode()]
 
     def image_desc(self, name):
         d = vkr.VkrImage()
