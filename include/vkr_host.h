@@ -57,10 +57,14 @@ int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao
 /* Descriptor of a named image AS OF THE LAST RENDERED FRAME (the ping-pong remaps are undone in the
  * lookup): albedo normal material velocity depth prev_depth dn dv rays raw filtered accumulated_ao
  * reflections blurred color taa pdf brdf ssao ssr_legacy
- * st_raw st_filtered st_accumulated gv_raw gv_filtered gv_output gv_deinterleaved (layer 0). */
+ * st_raw st_filtered st_accumulated gv_raw gv_filtered gv_output gv_deinterleaved (layer 0) tile_planes. */
 int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out);
 /* Asynchronous device->host copy of the whole allocation of a named image (all mips). */
 int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes);
+/* Asynchronous device->host copy of a named rendergraph buffer of the SSSR tile path (option alt.ssr_tiles; reference
+ * src/advanced_ssr.cpp:77-83): reflective_indirect glossy_indirect (3 x uint32) reflective_tiles glossy_tiles (int32 each).
+ * size_out (may be NULL) receives the buffer size; host_dst NULL only queries it. */
+int vkr_app_readback_buffer(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes, uint64_t* size_out);
 int vkr_app_sync(VkrApp* app);
 void* vkr_app_stream(VkrApp* app);
 /* Names of the tasks replayed by the last submit, '\n'-separated (for tests). */
@@ -84,6 +88,8 @@ int vkr_app_get_image_array(VkrApp* app, const char* name, VkrImage* out, uint64
 int vkr_app_get_value(VkrApp* app, const char* name, float* out);
 /* Likewise for the "ScreenTrace" task (option alt.screen_trace; reference src/screen_trace.cpp). */
 int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out);
+/* alt.ssr_tiles: AdvancedSSR::run also issues SSSR_Clear, SSSR_Classification, SSSR_Tile_Regression and the indirect SSSR_trace
+ * (reference src/advanced_ssr.cpp:547-550, commented out there); ssr.glossy_roughness_value = the classification threshold. */
 /* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the
  * whole DownsamplePass instead of the per-task calls.  graph.concurrent_branches: see vkr_app_last_lanes. */
 int vkr_app_set_option(VkrApp* app, const char* name, float value);

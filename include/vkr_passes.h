@@ -235,6 +235,35 @@ int vkr_sssr_blur(const VkrBlurParams* p, const VkrImage* depth, const VkrImage*
                   const VkrImage* material, const VkrImage* history, const VkrImage* dvelocity,
                   const VkrImage* prev_depth, const VkrImage* out_blurred, void* stream);
 
+/* ---- SSSR tile path (reference src/advanced_ssr.cpp:216-302,:440-538; left out of AdvancedSSR::run at :547-550) -------------
+ * Buffers are plain device pointers the callee borrows: *_indirect = one VkDispatchIndirectCommand {x, y, z} (12 bytes) whose .x
+ * counts the tiles of its list; *_tiles = int32 tile indices (tile = 8x8 block of the half-res `rays` image, index =
+ * tile_y * ceil(w/8) + tile_x), capacity >= the number of tiles.  The list ORDER comes out of atomicAdd, as in the reference. */
+typedef struct VkrClassifyParams {   /* push constants of SSSR_Classification (src/advanced_ssr.cpp:464-471) */
+  int32_t width, height;             /* extent of `rays` (half-res) */
+  float max_roughness;
+  float glossy_value;
+} VkrClassifyParams;
+typedef struct VkrRegressionParams { /* push constants of SSSR_Tile_Regression (src/advanced_ssr.cpp:508-518) */
+  float camera_to_world[16];         /* the reference passes transpose(normal_mat) */
+  float fovy, aspect, znear, zfar;
+} VkrRegressionParams;
+/* Task "SSSR_Clear" (:440-452): both commands <- {0, 1, 1}. */
+int vkr_sssr_clear_indirect(void* reflective_indirect, void* glossy_indirect, void* stream);
+/* Task "SSSR_Classification" (:454-495, classification.comp): mean roughness of each tile < glossy_value -> reflective list,
+ * else glossy list.  material = the full-res image, sampled at pixel / extent. */
+int vkr_sssr_classification(const VkrClassifyParams* p, const VkrImage* material, int32_t* reflective_tiles, int32_t* glossy_tiles,
+                            void* reflective_indirect, void* glossy_indirect, void* stream);
+/* One of the two vkCmdDispatchIndirect of task "SSSR_trace" (:216-302, trace_indirect.comp): reflection_type 0 = mirror list
+ * (50 cells from view level 0 + thickness test), 1 = glossy list (25 cells from view level 1).  The tile count is read on the
+ * device from indirect->x (clamped to max_tiles, the list capacity): no host synchronisation.  p->render_flags is not read. */
+int vkr_sssr_trace_indirect(const VkrTraceParams* p, uint32_t reflection_type, const VkrImage* depth, const VkrImage* dnormal,
+                            const VkrImage* material, const float* halton_vec4x128, const int32_t* tiles, const void* indirect,
+                            uint32_t max_tiles, const VkrImage* out_rays, void* stream);
+/* Task "SSSR_Tile_Regression" (:497-538, regression.comp): per half-res 8x8 tile the plane n with n . x = 1 through the tile's
+ * camera-relative world positions (.xyz) and the mean squared residual (.w) -> out_planes R32G32B32A32_SFLOAT. */
+int vkr_sssr_tile_regression(const VkrRegressionParams* p, const VkrImage* depth, const VkrImage* out_planes, void* stream);
+
 /* ---- GTAO (reference src/gtao.cpp) ------------------------------------------------ */
 /* Task "GTAO_main" (:84-148, gtao/main.comp); raw is read-modify-write. depth_lod = GTAO::depth_lod (:23). */
 int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,

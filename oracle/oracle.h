@@ -182,6 +182,16 @@ int orc_probe_downsample(const OrcImage* probe_depth_layer);
 int orc_trace_probe(const OrcProbeTraceParams* p, const OrcImage* depth, const OrcImage* normal, const OrcImage* probe_color,
                     uint64_t color_layer_stride, const OrcImage* probe_depth, uint64_t depth_layer_stride, const OrcImage* out, int y0, int y1);
 
+/* SSSR tile path (dead in AdvancedSSR::run): reference shaders/advanced_ssr/{classification,trace_indirect,regression}.comp.
+ * indirect = VkDispatchIndirectCommand {x, y, z}; classification appends to the lists in ascending tile index. */
+int orc_sssr_classification(int tex_w, int tex_h, float g_max_roughness, float g_glossy_value, const OrcImage* material,
+                            int32_t* reflective_tiles, int32_t* glossy_tiles, uint32_t* reflective_indirect, uint32_t* glossy_indirect);
+int orc_sssr_trace_indirect(const OrcTraceParams* p, uint32_t reflection_type, const OrcImage* depth, const OrcImage* dnormal,
+                            const OrcImage* material, const float* halton_vec4x128, const int32_t* tiles, uint32_t tile_count,
+                            const OrcImage* out_rays);
+int orc_sssr_tile_regression(const float* camera_to_world16, const float* fovy_aspect_znear_zfar, const OrcImage* depth,
+                             const OrcImage* out_planes);
+
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);
 void orc_probe_decode_normal(const float* uv2, float* out3);

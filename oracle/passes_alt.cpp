@@ -53,35 +53,6 @@ static float depth_nearest(const View& v, vec2 uv) {
   return texelFetch(v, ivec2(x, y), 0).x;
 }
 
-// screen_trace.glsl:51-100
-static vec3 hierarchical_raymarch(const View& depth_tex, vec3 origin, vec3 direction, int most_detailed_mip, uint32_t max_traversal_intersections, bool& valid_hit) {
-  const vec3 inv_direction = vec3(direction.x != 0 ? 1.0f / direction.x : MAX_T_FLOAT, direction.y != 0 ? 1.0f / direction.y : MAX_T_FLOAT,
-                                  direction.z != 0 ? 1.0f / direction.z : MAX_T_FLOAT);
-  int current_mip = most_detailed_mip;
-  vec2 screen_size = to_vec2(textureSize(depth_tex, 0));
-  vec2 current_mip_resolution = get_mip_resolution(screen_size, current_mip);
-  vec2 current_mip_resolution_inv = 1.0f / current_mip_resolution;
-  vec2 uv_offset = 0.005f * std::exp2((float)most_detailed_mip) / screen_size;
-  uv_offset.x = direction.x < 0 ? -uv_offset.x : uv_offset.x;
-  uv_offset.y = direction.y < 0 ? -uv_offset.y : uv_offset.y;
-  vec2 floor_offset = vec2(direction.x < 0 ? 0 : 1, direction.y < 0 ? 0 : 1);
-  float current_t;
-  vec3 position;
-  initial_advance_ray(origin, direction, inv_direction, current_mip_resolution, current_mip_resolution_inv, floor_offset, uv_offset, position, current_t);
-  uint32_t i = 0;
-  while (i < max_traversal_intersections && current_mip >= most_detailed_mip) {
-    vec2 current_mip_position = current_mip_resolution * position.xy();
-    float surface_z = texelFetch(depth_tex, to_ivec2(current_mip_position), current_mip).x;
-    bool skipped_tile = advance_ray(origin, direction, inv_direction, current_mip_position, current_mip_resolution_inv, floor_offset, uv_offset, surface_z, position, current_t);
-    current_mip += skipped_tile ? 1 : -1;
-    current_mip_resolution *= skipped_tile ? 0.5f : 2.0f;
-    current_mip_resolution_inv *= skipped_tile ? 2.0f : 0.5f;
-    ++i;
-  }
-  valid_hit = (i <= max_traversal_intersections);
-  return position;
-}
-
 static float smoothstep1(float e0, float e1, float x) {
   float t = clamp((x - e0) / (e1 - e0), 0.0f, 1.0f);
   return t * t * (3.0f - 2.0f * t);

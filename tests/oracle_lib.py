@@ -67,6 +67,9 @@ _sig("orc_gtao_reproject", FP, IP, IP, U, IP, IP, IP, I, I)
 _sig("orc_cube2oct", IP, C.c_uint64, IP, C.c_uint64, IP, IP)
 _sig("orc_probe_downsample", IP)
 _sig("orc_trace_probe", C.POINTER(vkr.ProbeTraceParams), IP, IP, IP, C.c_uint64, IP, C.c_uint64, IP, I, I)
+_sig("orc_sssr_classification", I, I, C.c_float, C.c_float, IP, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p)
+_sig("orc_sssr_trace_indirect", C.POINTER(vkr.TraceParams), U, IP, IP, IP, FP, C.c_void_p, U, IP)
+_sig("orc_sssr_tile_regression", FP, FP, IP, IP)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

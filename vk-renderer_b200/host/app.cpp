@@ -183,6 +183,7 @@ struct VkrApp {
     else if (name == "st_raw") id = screen_trace.raw;
     else if (name == "st_filtered") id = screen_trace.filtered;
     else if (name == "st_accumulated") id = screen_trace.accumulated;
+    else if (name == "tile_planes") id = ssr.get_tile_planes();
     else return false;
     return true;
   }
@@ -295,6 +296,26 @@ int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t cap
   return VKR_OK;
 }
 
+int vkr_app_readback_buffer(VkrApp* app, const char* name, void* host_dst, uint64_t capacity, uint64_t* size_out) {
+  if (!app || !name) { host_error("readback_buffer: null argument"); return VKR_ERR_INVALID_ARGUMENT; }
+  const std::string n{name};
+  rendergraph::BufferResourceId id;
+  if (n == "reflective_indirect") id = app->ssr.get_reflective_indirect();
+  else if (n == "glossy_indirect") id = app->ssr.get_glossy_indirect();
+  else if (n == "reflective_tiles") id = app->ssr.get_reflective_tiles();
+  else if (n == "glossy_tiles") id = app->ssr.get_glossy_tiles();
+  else { host_error("readback_buffer: unknown buffer '%s'", name); return VKR_ERR_INVALID_ARGUMENT; }
+  const uint64_t total = app->render_graph.buffer_size(id);
+  if (size_out) *size_out = total;
+  if (!host_dst) return VKR_OK;
+  if (capacity < total) { host_error("readback_buffer: destination too small (%llu < %llu)", (unsigned long long)capacity, (unsigned long long)total); return VKR_ERR_INVALID_ARGUMENT; }
+  if (cudaMemcpyAsync(host_dst, app->render_graph.buffer(id), total, cudaMemcpyDeviceToHost, (cudaStream_t)app->render_graph.stream()) != cudaSuccess) {
+    host_error("readback_buffer: cudaMemcpyAsync failed");
+    return VKR_ERR_CUDA;
+  }
+  return VKR_OK;
+}
+
 int vkr_app_sync(VkrApp* app) {
   if (!app) return VKR_ERR_INVALID_ARGUMENT;
   VKR_TRY(app->render_graph.wait_idle())
@@ -370,6 +391,8 @@ int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   else if (n == "alt.screen_trace") app->alt_screen_trace = v != 0.f;
   else if (n == "alt.gtao_variants") app->alt_gtao_variants = v != 0.f;
   else if (n == "alt.trace_probe") app->alt_trace_probe = v != 0.f;
+  else if (n == "alt.ssr_tiles") app->ssr.settings.run_tile_path = v != 0.f;
+  else if (n == "ssr.glossy_roughness_value") app->ssr.settings.glossy_roughness_value = v;
   else if (n == "alt.ssao_reference_packing") app->ssao_pass.reference_packing = v != 0.f;
   else if (n == "shading.only_ao") app->shading_pass.only_ao = v != 0.f;
   else if (n == "shading.min_roughness") app->shading_pass.min_max_roughness.x = v;

@@ -160,9 +160,29 @@ struct AdvancedSSR {
     bool update_random = true;
     bool use_blur = true;
     int max_accumulated_rays = 16;
+    // not in the reference: run() issues the four tile tasks the reference has commented out at src/advanced_ssr.cpp:547-550
+    // (clear, classification, tile regression, indirect trace) ahead of the per-pixel trace, in that order
+    bool run_tile_path = false;
   } settings;
 
+  // The tile path (reference src/advanced_ssr.cpp:216-302,:440-538; private there and unreachable from run()).  Public here so
+  // a host can schedule the tasks itself.
+  void clear_indirect_params(rendergraph::RenderGraph& graph);
+  void run_classification_pass(rendergraph::RenderGraph& graph, const AdvancedSSRParams& params, const Gbuffer& gbuff);
+  void run_tile_regression_pass(rendergraph::RenderGraph& graph, const AdvancedSSRParams& params, const Gbuffer& gbuff);
+  void run_trace_indirect_pass(rendergraph::RenderGraph& graph, const AdvancedSSRParams& params, const Gbuffer& gbuff);
+  rendergraph::ImageResourceId get_tile_planes() const { return tile_planes; }
+  rendergraph::BufferResourceId get_reflective_indirect() const { return reflective_indirect; }
+  rendergraph::BufferResourceId get_glossy_indirect() const { return glossy_indirect; }
+  rendergraph::BufferResourceId get_reflective_tiles() const { return reflective_tiles; }
+  rendergraph::BufferResourceId get_glossy_tiles() const { return glossy_tiles; }
+
  private:
+  rendergraph::BufferResourceId reflective_indirect;
+  rendergraph::BufferResourceId glossy_indirect;
+  rendergraph::BufferResourceId reflective_tiles;
+  rendergraph::BufferResourceId glossy_tiles;
+  rendergraph::ImageResourceId tile_planes;
   float* halton_buffer = nullptr;  // device, 128 x vec4 (the Halton UBO)
   rendergraph::ImageResourceId rays;
   rendergraph::ImageResourceId reflections;

@@ -1,6 +1,8 @@
 // passes_ssr_taa.cpp — AdvancedSSR, DeferedShadingPass, TAA task bodies (see passes.hpp).
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include "passes.hpp"
 
 using namespace rendergraph;
@@ -31,6 +33,13 @@ AdvancedSSR::AdvancedSSR(RenderGraph& graph, uint32_t w, uint32_t h) {
   blurred_reflection_history = mk(VKR_FORMAT_R8G8B8A8_UNORM, w / 2, h / 2);
   preintegrated_pdf = mk(VKR_FORMAT_R32_SFLOAT, 1024, 1024);                                                     // :88-92
   preintegrated_brdf = mk(VKR_FORMAT_R16G16_SFLOAT, 1024, 1024);
+
+  reflective_indirect = graph.create_buffer(3 * sizeof(uint32_t));                                               // :77-79 VkDispatchIndirectCommand
+  glossy_indirect = graph.create_buffer(3 * sizeof(uint32_t));
+  const uint64_t tile_bytes = sizeof(int) * std::max<uint64_t>(1, (uint64_t)w * h / 64);                         // :81-83
+  reflective_tiles = graph.create_buffer(tile_bytes);
+  glossy_tiles = graph.create_buffer(tile_bytes);
+  tile_planes = mk(VKR_FORMAT_R32G32B32A32_SFLOAT, std::max(1u, w / 16), std::max(1u, h / 16));                  // :85-86
 }
 
 AdvancedSSR::~AdvancedSSR() { cudaFree(halton_buffer); }
@@ -139,7 +148,95 @@ void AdvancedSSR::run_blur_pass(RenderGraph& graph, const AdvancedSSRParams&, co
     });
 }
 
+// ---- the tile path --------------------------------------------------------------------------------
+void AdvancedSSR::clear_indirect_params(RenderGraph& graph) {                                                    // :440-452
+  struct Input {};
+  auto ri = reflective_indirect, gi = glossy_indirect;
+  graph.add_task<Input>("SSSR_Clear",
+    [&](Input&, RenderGraphBuilder& builder) {
+      builder.transfer_write(reflective_indirect);
+      builder.transfer_write(glossy_indirect);
+    },
+    [=](Input&, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_sssr_clear_indirect(resources.get_buffer(ri), resources.get_buffer(gi), cmd.stream), "SSSR_Clear");
+    });
+}
+
+void AdvancedSSR::run_classification_pass(RenderGraph& graph, const AdvancedSSRParams&, const Gbuffer& gbuff) { // :454-495
+  struct Input { ImageViewId material_tex; };
+  auto extent = graph.get_descriptor(rays).extent2D();
+  VkrClassifyParams pc{int(extent.width), int(extent.height), settings.max_rougness, settings.glossy_roughness_value};
+  auto ri = reflective_indirect, gi = glossy_indirect, rt = reflective_tiles, gt = glossy_tiles;
+  graph.add_task<Input>("SSSR_Classification",
+    [&](Input& input, RenderGraphBuilder& builder) {
+      input.material_tex = builder.sample_image(gbuff.material);
+      builder.use_storage_buffer(reflective_indirect, false);
+      builder.use_storage_buffer(glossy_indirect, false);
+      builder.use_storage_buffer(reflective_tiles, false);
+      builder.use_storage_buffer(glossy_tiles, false);
+    },
+    [=](Input& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_sssr_classification(&pc, resources.get_image(input.material_tex), (int32_t*)resources.get_buffer(rt), (int32_t*)resources.get_buffer(gt),
+                                        resources.get_buffer(ri), resources.get_buffer(gi), cmd.stream), "SSSR_Classification");
+    });
+}
+
+void AdvancedSSR::run_tile_regression_pass(RenderGraph& graph, const AdvancedSSRParams& params, const Gbuffer& gbuff) {  // :497-538
+  struct Input { ImageViewId depth_tex, planes_tex; };
+  VkrRegressionParams pc{};
+  copy_mat(pc.camera_to_world, glm::transpose(params.normal_mat));                                               // :518
+  pc.fovy = params.fovy; pc.aspect = params.aspect; pc.znear = params.znear; pc.zfar = params.zfar;
+  graph.add_task<Input>("SSSR_Tile_Regression",
+    [&](Input& input, RenderGraphBuilder& builder) {
+      input.depth_tex = builder.sample_image(gbuff.depth, 1, 1, 0, 1);                                           // :524
+      input.planes_tex = builder.use_storage_image(tile_planes, 0, 0);
+    },
+    [=](Input& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      vkr_check(vkr_sssr_tile_regression(&pc, resources.get_image(input.depth_tex), resources.get_image(input.planes_tex), cmd.stream), "SSSR_Tile_Regression");
+    });
+}
+
+void AdvancedSSR::run_trace_indirect_pass(RenderGraph& graph, const AdvancedSSRParams& params, const Gbuffer& gbuff) {   // :216-302
+  VkrTraceParams config = make_trace_params(params, counter);
+  config.max_roughness = settings.max_rougness;                                                                  // :238
+  if (settings.update_random) {                                                                                  // :240-243
+    counter++;
+    counter = counter % settings.max_accumulated_rays;
+  }
+  struct Input { ImageViewId depth, normal, material, out; };
+  auto mips_count = graph.get_descriptor(gbuff.depth).mip_levels;
+  const float* halton = halton_buffer;
+  auto ri = reflective_indirect, gi = glossy_indirect, rt = reflective_tiles, gt = glossy_tiles;
+  const uint32_t max_tiles = (uint32_t)(graph.buffer_size(reflective_tiles) / sizeof(int));
+  graph.add_task<Input>("SSSR_trace",
+    [&](Input& input, RenderGraphBuilder& builder) {
+      input.depth = builder.sample_image(gbuff.depth, 1, mips_count - 1, 0, 1);                                  // :254
+      input.normal = builder.sample_image(gbuff.downsampled_normals);
+      input.material = builder.sample_image(gbuff.material);
+      input.out = builder.use_storage_image(rays, 0, 0);
+      builder.use_indirect_buffer(reflective_indirect);
+      builder.use_indirect_buffer(glossy_indirect);
+      builder.use_storage_buffer(reflective_tiles);
+      builder.use_storage_buffer(glossy_tiles);
+    },
+    [=](Input& input, RenderResources& resources, gpu::CmdContext& cmd) {
+      // two dispatch_indirect of one pipeline (:291-299): mirror list, then glossy list
+      vkr_check(vkr_sssr_trace_indirect(&config, 0, resources.get_image(input.depth), resources.get_image(input.normal), resources.get_image(input.material),
+                                        halton, (const int32_t*)resources.get_buffer(rt), resources.get_buffer(ri), max_tiles, resources.get_image(input.out),
+                                        cmd.stream), "SSSR_trace(mirror tiles)");
+      vkr_check(vkr_sssr_trace_indirect(&config, 1, resources.get_image(input.depth), resources.get_image(input.normal), resources.get_image(input.material),
+                                        halton, (const int32_t*)resources.get_buffer(gt), resources.get_buffer(gi), max_tiles, resources.get_image(input.out),
+                                        cmd.stream), "SSSR_trace(glossy tiles)");
+    });
+}
+
 void AdvancedSSR::run(RenderGraph& graph, const AdvancedSSRParams& params, const DrawTAAParams& taa_params, const Gbuffer& gbuff, ImageResourceId ssr_occlusion) {
+  if (settings.run_tile_path) {                                                                                  // :547-550, commented out in the reference
+    clear_indirect_params(graph);
+    run_classification_pass(graph, params, gbuff);
+    run_tile_regression_pass(graph, params, gbuff);
+    run_trace_indirect_pass(graph, params, gbuff);
+  }
   run_trace_pass(graph, params, gbuff, ssr_occlusion);                                                           // :540-553
   run_filter_pass(graph, params, gbuff);
   run_blur_pass(graph, params, taa_params, gbuff);

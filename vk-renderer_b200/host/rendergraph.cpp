@@ -87,6 +87,29 @@ ImageResourceId RenderGraph::create_image(const gpu::ImageInfo& info) {
   return id;
 }
 
+BufferResourceId RenderGraph::create_buffer(uint64_t size) {
+  if (size == 0) throw std::runtime_error("create_buffer: empty buffer");
+  BufferSlot b{nullptr, size};
+  cuda_check(cudaSetDevice(device_), "cudaSetDevice");
+  cuda_check(cudaMalloc(&b.ptr, size), "cudaMalloc(buffer)");
+  cuda_check(cudaMemsetAsync(b.ptr, 0, size, (cudaStream_t)stream_), "cudaMemset(buffer)");
+  buffers.push_back(b);
+  allocations.push_back(b.ptr);
+  BufferResourceId id;
+  id.index = (uint32_t)buffers.size() - 1;
+  return id;
+}
+
+void* RenderGraph::buffer(BufferResourceId id) const {
+  if (id.get_index() >= buffers.size()) throw std::runtime_error("Invalid buffer resource id");
+  return buffers[id.get_index()].ptr;
+}
+
+uint64_t RenderGraph::buffer_size(BufferResourceId id) const {
+  buffer(id);
+  return buffers[id.get_index()].bytes;
+}
+
 const VkrImage& RenderGraph::image(ImageResourceId id) const {
   if (id.get_index() >= slots.size()) throw std::runtime_error("Invalid image resource id");
   return slots[id.get_index()].desc;
@@ -148,8 +171,10 @@ void RenderGraph::submit() {
     sync_events_.push_back(e);
   }
   const int n = (int)run.size();
-  std::vector<int> last_writer(slots.size(), -1), lane(n, 0);
-  std::vector<std::vector<int>> readers(slots.size());
+  const size_t n_res = slots.size() + buffers.size();
+  auto res_index = [&](uint32_t slot) -> size_t { return slot >= kBufferSlotBase ? slots.size() + (slot - kBufferSlotBase) : slot; };
+  std::vector<int> last_writer(n_res, -1), lane(n, 0);
+  std::vector<std::vector<int>> readers(n_res);
   void* lane_stream[2] = {stream_, aux_stream_};
   int lane_last[2] = {-1, -1};
   bool aux_used = false;
@@ -161,8 +186,8 @@ void RenderGraph::submit() {
     std::vector<int> deps;
     auto add = [&](int d) { if (d >= 0 && std::find(deps.begin(), deps.end(), d) == deps.end()) deps.push_back(d); };
     for (const ImageUse& u : t.uses) {
-      add(last_writer[u.slot]);
-      if (u.write) for (int r : readers[u.slot]) add(r);
+      add(last_writer[res_index(u.slot)]);
+      if (u.write) for (int r : readers[res_index(u.slot)]) add(r);
     }
     auto is_dep = [&](int d) { return d >= 0 && std::find(deps.begin(), deps.end(), d) != deps.end(); };
     int l = 0;
@@ -181,8 +206,8 @@ void RenderGraph::submit() {
     lane_last[l] = i;
     aux_used |= l == 1;
     for (const ImageUse& u : t.uses) {
-      if (u.write) { last_writer[u.slot] = i; readers[u.slot].clear(); }
-      else readers[u.slot].push_back(i);
+      if (u.write) { last_writer[res_index(u.slot)] = i; readers[res_index(u.slot)].clear(); }
+      else readers[res_index(u.slot)].push_back(i);
     }
     last_names.push_back(t.name);
     last_lanes.push_back(l);
@@ -210,6 +235,15 @@ ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id, uint32_t base_m
 ImageViewId RenderGraphBuilder::sample_image(ImageResourceId id) { return make_view(id, 0, graph.image(id).mip_count, false); }
 gpu::ImageInfo RenderGraphBuilder::get_image_info(ImageResourceId id) { return graph.get_descriptor(id); }
 
+void RenderGraphBuilder::use_buffer(BufferResourceId id, bool write) {
+  graph.buffer(id);
+  if (uses_) uses_->push_back(ImageUse{kBufferSlotBase + id.get_index(), write});
+}
+void RenderGraphBuilder::use_storage_buffer(BufferResourceId id, bool readonly) { use_buffer(id, !readonly); }
+void RenderGraphBuilder::use_indirect_buffer(BufferResourceId id) { use_buffer(id, false); }
+void RenderGraphBuilder::transfer_write(BufferResourceId id) { use_buffer(id, true); }
+
+void* RenderResources::get_buffer(BufferResourceId id) const { return graph.buffer(id); }
 const VkrImage* RenderResources::get_image(const ImageViewId& ref) const { return &graph.image(ref.get_id()); }
 const VkrImage* RenderResources::get_image(ImageResourceId id) const { return &graph.image(id); }
 

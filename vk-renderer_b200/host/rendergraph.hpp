@@ -70,10 +70,24 @@ struct ImageViewId {
   gpu::ImageViewRange range;
 };
 
+// reference src/rendergraph/resources.hpp: a slot index like ImageResourceId, for linear device buffers (SSBOs, indirect
+// dispatch commands).  Only the SSSR tile path uses buffers (reference src/advanced_ssr.cpp:77-83).
+struct BufferResourceId {
+  BufferResourceId() {}
+  uint32_t get_index() const { return index; }
+  bool operator==(const BufferResourceId& id) const { return index == id.index; }
+
+ private:
+  uint32_t index = ~0u;
+  friend struct RenderGraph;
+};
+
 struct RenderGraph;
 
 // One declared use of an image by a task: whole-image granularity (slot index at record time), read or write.
+// Buffers share the numbering: slot = kBufferSlotBase + buffer index.
 struct ImageUse { uint32_t slot; bool write; };
+constexpr uint32_t kBufferSlotBase = 0x40000000u;
 
 // reference rendergraph.hpp:17-55.  Usage declarations keep their names; they validate the subresource range
 // (reference rendergraph.cpp:390-392 "Image subresource out of range") and record the image as read or written by the
@@ -87,10 +101,15 @@ struct RenderGraphBuilder {
   ImageViewId sample_image(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t base_layer, uint32_t layer_count);
   ImageViewId sample_image(ImageResourceId id);  // whole image
   gpu::ImageInfo get_image_info(ImageResourceId id);
+  // reference rendergraph.hpp:40-55 (shader stage / usage flags dropped): declare a buffer as read or written by the task
+  void use_storage_buffer(BufferResourceId id, bool readonly = true);
+  void use_indirect_buffer(BufferResourceId id);
+  void transfer_write(BufferResourceId id);
 
  private:
   RenderGraph& graph;
   std::vector<ImageUse>* uses_;
+  void use_buffer(BufferResourceId id, bool write);
   ImageViewId make_view(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, bool write);
 };
 
@@ -100,6 +119,7 @@ struct RenderResources {
   // The image behind a view, as the C ABI wants it (whole image; the pass passes the mip window on).
   const VkrImage* get_image(const ImageViewId& ref) const;
   const VkrImage* get_image(ImageResourceId id) const;
+  void* get_buffer(BufferResourceId id) const;   // device pointer (reference: gpu::BufferPtr -> api_buffer())
 
  private:
   RenderGraph& graph;
@@ -158,6 +178,10 @@ struct RenderGraph {
 
   ImageResourceId create_image(const gpu::ImageInfo& info);  // zero-initialised device memory
   gpu::ImageInfo get_descriptor(ImageResourceId id) const;
+  // reference rendergraph.hpp create_buffer(VmaMemoryUsage, size, usage): zero-initialised device memory
+  BufferResourceId create_buffer(uint64_t size);
+  void* buffer(BufferResourceId id) const;
+  uint64_t buffer_size(BufferResourceId id) const;
   // Array images (gpu::ImageInfo::array_layers, reference src/gpu/resource_info.hpp:11-19): layer l of slot `id` lies
   // layer_stride(id) * l bytes after the descriptor's base.
   uint64_t layer_stride(ImageResourceId id) const;
@@ -181,6 +205,8 @@ struct RenderGraph {
  private:
   struct Slot { VkrImage desc; uint64_t bytes; uint32_t layers = 1; uint64_t layer_stride = 0; };
   std::vector<Slot> slots;
+  struct BufferSlot { void* ptr; uint64_t bytes; };
+  std::vector<BufferSlot> buffers;
   std::vector<void*> allocations;   // everything create_image() allocated (slots may be rebound / swapped)
   bool timing_ = false;
   struct Pending { std::string name; void* start; void* stop; };

@@ -46,6 +46,14 @@ class TraceParams(C.Structure):
                 ("znear", C.c_float), ("zfar", C.c_float), ("max_roughness", C.c_float), ("render_flags", C.c_uint32)]
 
 
+class ClassifyParams(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_roughness", C.c_float), ("glossy_value", C.c_float)]
+
+
+class RegressionParams(C.Structure):
+    _fields_ = [_mat("camera_to_world"), ("fovy", C.c_float), ("aspect", C.c_float), ("znear", C.c_float), ("zfar", C.c_float)]
+
+
 class BlurParams(C.Structure):
     _fields_ = [_mat("inverse_camera"), _mat("prev_inverse_camera"), ("fovy_aspect_znear_zfar", C.c_float * 4),
                 ("max_roughness", C.c_float), ("accumulate", C.c_uint32), ("disable_blur", C.c_uint32)]
@@ -336,6 +344,35 @@ _sig("vkr_gtao_filter", PT(GtaoParams), IP, IP, IP, C.c_uint32, VP)
 _sig("vkr_gtao_accumulate", PT(AccumParams), IP, IP, IP, IP, IP, IP, C.c_uint32, VP)
 _sig("vkr_deferred_shading", PT(ShadingParams), IP, IP, IP, IP, IP, IP, IP, IP, VP)
 _sig("vkr_taa_resolve", PT(TaaParams), IP, IP, IP, IP, IP, IP, VP)
+
+
+_sig("vkr_sssr_clear_indirect", VP, VP, VP)
+_sig("vkr_sssr_classification", PT(ClassifyParams), IP, VP, VP, VP, VP, VP)
+_sig("vkr_sssr_trace_indirect", PT(TraceParams), C.c_uint32, IP, IP, IP, FP, VP, VP, C.c_uint32, IP, VP)
+_sig("vkr_sssr_tile_regression", PT(RegressionParams), IP, IP, VP)
+
+
+def _dp(t):
+    return C.c_void_p(t.data_ptr())
+
+
+def sssr_clear_indirect(reflective_indirect, glossy_indirect, stream=None):
+    """SSSR_Clear: both int32[3] device tensors <- {0, 1, 1}."""
+    check(lib.vkr_sssr_clear_indirect(_dp(reflective_indirect), _dp(glossy_indirect), stream_ptr(stream)))
+
+
+def sssr_classification(p, material, reflective_tiles, glossy_tiles, reflective_indirect, glossy_indirect, stream=None):
+    check(lib.vkr_sssr_classification(C.byref(p), material.ptr, _dp(reflective_tiles), _dp(glossy_tiles), _dp(reflective_indirect),
+                                      _dp(glossy_indirect), stream_ptr(stream)))
+
+
+def sssr_trace_indirect(p, reflection_type, depth, dnormal, material, halton_dev, tiles, indirect, rays, stream=None):
+    check(lib.vkr_sssr_trace_indirect(C.byref(p), reflection_type, depth.ptr, dnormal.ptr, material.ptr, _dp(halton_dev), _dp(tiles), _dp(indirect),
+                                      tiles.numel(), rays.ptr, stream_ptr(stream)))
+
+
+def sssr_tile_regression(p, depth, out_planes, stream=None):
+    check(lib.vkr_sssr_tile_regression(C.byref(p), depth.ptr, out_planes.ptr, stream_ptr(stream)))
 
 
 def pdf_preintegrate(out, stream=None):

@@ -31,6 +31,8 @@ lib.vkr_app_get_image.restype = C.c_int
 lib.vkr_app_get_image.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(vkr.VkrImage)]
 lib.vkr_app_readback.restype = C.c_int
 lib.vkr_app_readback.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64]
+lib.vkr_app_readback_buffer.restype = C.c_int
+lib.vkr_app_readback_buffer.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
 lib.vkr_app_sync.restype = C.c_int
 lib.vkr_app_sync.argtypes = [C.c_void_p]
 lib.vkr_app_stream.restype = C.c_void_p
@@ -170,6 +172,16 @@ class App:
         d = vkr.VkrImage()
         _check(lib.vkr_app_get_image(self.h, name.encode(), C.byref(d)))
         return d
+
+    def readback_buffer(self, name, dtype="int32"):
+        """A named rendergraph buffer of the SSSR tile path as a numpy array."""
+        import numpy as np
+        size = C.c_uint64()
+        _check(lib.vkr_app_readback_buffer(self.h, name.encode(), None, 0, C.byref(size)))
+        out = np.empty(size.value // np.dtype(dtype).itemsize, dtype=dtype)
+        _check(lib.vkr_app_readback_buffer(self.h, name.encode(), out.ctypes.data_as(C.c_void_p), out.nbytes, None))
+        self.sync()
+        return out
 
     def readback(self, name, host_image=None, sync=True):
         """Copy a named image (all mips) into a CPU vkr.Image (allocated if not given)."""
