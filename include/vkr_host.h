@@ -57,7 +57,7 @@ int vkr_app_render_frame(VkrApp* app, const VkrDrawTAAParams* params, float gtao
 /* Descriptor of a named image AS OF THE LAST RENDERED FRAME (the ping-pong remaps are undone in the
  * lookup): albedo normal material velocity depth prev_depth dn dv rays raw filtered accumulated_ao
  * reflections blurred color taa pdf brdf ssao ssr_legacy
- * st_raw st_filtered st_accumulated gv_raw gv_filtered gv_output gv_deinterleaved (layer 0) tile_planes. */
+ * st_raw st_filtered st_accumulated gv_raw gv_filtered gv_output gv_deinterleaved (layer 0) tile_planes readback_image. */
 int vkr_app_get_image(VkrApp* app, const char* name, VkrImage* out);
 /* Asynchronous device->host copy of the whole allocation of a named image (all mips). */
 int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes);
@@ -65,6 +65,13 @@ int vkr_app_readback(VkrApp* app, const char* name, void* host_dst, uint64_t cap
  * src/advanced_ssr.cpp:77-83): reflective_indirect glossy_indirect (3 x uint32) reflective_tiles glossy_tiles (int32 each).
  * size_out (may be NULL) receives the buffer size; host_dst NULL only queries it. */
 int vkr_app_readback_buffer(VkrApp* app, const char* name, void* host_dst, uint64_t capacity_bytes, uint64_t* size_out);
+/* The capture buttons of the reference's frame loop (src/main.cpp:352-357,:393-412 + callbacks :118-176), synchronous:
+ * kind 0 = "Final frame": blit_image(TAA output -> sRGB8 read-back image), ReadBackSystem::read_image, PNG with alpha 255;
+ * kind 1 = depth mip 0 as a PNG of the 24-bit codes (R = low byte); kind 2 = the same codes as CSV ("y, 0,1,..", hex cells).
+ * Tasks issued: ["CopyImage",] "ImageRead" (vkr_app_last_tasks). */
+int vkr_app_capture(VkrApp* app, uint32_t kind, const char* path);
+/* Host-only: 8-bit RGBA PNG from tightly packed rows (stands in for stbi_write_png(path, w, h, 4, data, 0)). */
+int vkr_write_png_rgba8(const char* path, uint32_t width, uint32_t height, const void* rgba);
 int vkr_app_sync(VkrApp* app);
 void* vkr_app_stream(VkrApp* app);
 /* Names of the tasks replayed by the last submit, '\n'-separated (for tests). */

@@ -264,6 +264,19 @@ int vkr_sssr_trace_indirect(const VkrTraceParams* p, uint32_t reflection_type, c
  * camera-relative world positions (.xyz) and the mean squared residual (.w) -> out_planes R32G32B32A32_SFLOAT. */
 int vkr_sssr_tile_regression(const VkrRegressionParams* p, const VkrImage* depth, const VkrImage* out_planes, void* stream);
 
+/* ---- capture path (reference src/util_passes.cpp:152-180, src/image_readback.cpp:67-110, src/main.cpp:152-176) ------------ */
+/* Task "CopyImage" (blit_image): vkCmdBlitImage, VK_FILTER_LINEAR, all of src mip 0 onto all of dst mip 0 — destination texel p
+ * takes the bilinear, clamp-to-edge sample of src at (p + 0.5) / dst_extent, converted to dst's format.  src: R16G16B16A16_SFLOAT,
+ * R8G8B8A8_SRGB or R8G8B8A8_UNORM; dst: R8G8B8A8_SRGB or R8G8B8A8_UNORM (the reference blits the TAA target into its sRGB
+ * read-back image, src/main.cpp:220-223,:394). */
+int vkr_blit_image(const VkrImage* src, const VkrImage* dst, void* stream);
+/* Task "ImageRead" (ReadBackSystem::read_image): one mip level into a tightly packed DEVICE buffer of width * height * texel
+ * bytes (bufferRowLength = 0), ready for one contiguous device-to-host copy.  mode applies what the reference's callbacks do
+ * to the bytes on the host: DEPTH24 = 32-bit words & 0xFFFFFF (get_depth_cb / get_depth_png_cb), OPAQUE_ALPHA = byte 3 of every
+ * texel <- 255 (get_rgba_cb); both need 4-byte texels. */
+typedef enum VkrReadbackMode { VKR_READBACK_RAW = 0, VKR_READBACK_DEPTH24 = 1, VKR_READBACK_OPAQUE_ALPHA = 2 } VkrReadbackMode;
+int vkr_readback_pack(const VkrImage* image, uint32_t mip, uint32_t mode, void* out_tight, void* stream);
+
 /* ---- GTAO (reference src/gtao.cpp) ------------------------------------------------ */
 /* Task "GTAO_main" (:84-148, gtao/main.comp); raw is read-modify-write. depth_lod = GTAO::depth_lod (:23). */
 int vkr_gtao_main(const VkrGtaoParams* p, const VkrImage* depth, const VkrImage* normal, const VkrImage* material,

@@ -192,6 +192,10 @@ int orc_sssr_trace_indirect(const OrcTraceParams* p, uint32_t reflection_type, c
 int orc_sssr_tile_regression(const float* camera_to_world16, const float* fovy_aspect_znear_zfar, const OrcImage* depth,
                              const OrcImage* out_planes);
 
+/* Capture path: reference src/util_passes.cpp:152-180 blit_image, src/image_readback.cpp:67-110, src/main.cpp:152-176. */
+int orc_blit_image(const OrcImage* src, const OrcImage* dst);
+int orc_readback_pack(const OrcImage* image, uint32_t mip, uint32_t mode, void* out_tight);
+
 /* shared-math probes for the analytic anchors (tests only) */
 void orc_probe_encode_normal(const float* v3, float* out2);
 void orc_probe_decode_normal(const float* uv2, float* out3);

@@ -70,6 +70,8 @@ _sig("orc_trace_probe", C.POINTER(vkr.ProbeTraceParams), IP, IP, IP, C.c_uint64,
 _sig("orc_sssr_classification", I, I, C.c_float, C.c_float, IP, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p)
 _sig("orc_sssr_trace_indirect", C.POINTER(vkr.TraceParams), U, IP, IP, IP, FP, C.c_void_p, U, IP)
 _sig("orc_sssr_tile_regression", FP, FP, IP, IP)
+_sig("orc_blit_image", IP, IP)
+_sig("orc_readback_pack", IP, U, U, C.c_void_p)
 _sig("orc_probe_encode_normal", FP, FP, restype=None)
 _sig("orc_probe_decode_normal", FP, FP, restype=None)
 _sig("orc_probe_reconstruct", FP, C.c_float, FP, FP, restype=None)

@@ -9,6 +9,7 @@
 
 #include "../../include/vkr_host.h"
 #include "passes.hpp"
+#include "readback.hpp"
 
 using namespace rendergraph;
 
@@ -49,6 +50,9 @@ struct VkrApp {
   OctahedralProbeGrid probe_grid;
   ProbeTracePass probe_trace;
   ImageResourceId probe_reflection;
+  // capture path (main.cpp:220-223,:247,:352-357,:393-396): sRGB8 read-back image the TAA output is blitted into + ReadBackSystem
+  ImageResourceId readback_image;
+  ReadBackSystem readback_system;
   bool alt_trace_probe = false, probes_rendered = false;
   GTAO gtao_alt;     // a second GTAO object so the variants do not disturb the live chain's images
   bool alt_ssao = false, alt_ssr = false, alt_screen_trace = false, alt_gtao_variants = false;
@@ -64,6 +68,7 @@ struct VkrApp {
         screen_trace{render_graph, w, h}, probe_renderer{render_graph, CUBE_SIZE}, probe_grid{render_graph, 4, PROBE_SIZE},
         gtao_alt{render_graph, w, h, false, true, 2} {
     { gpu::ImageInfo pr; pr.format = VKR_FORMAT_R8G8B8A8_UNORM; pr.width = w; pr.height = h; probe_reflection = render_graph.create_image(pr); }
+    { gpu::ImageInfo ri; ri.format = VKR_FORMAT_R8G8B8A8_SRGB; ri.width = w; ri.height = h; readback_image = render_graph.create_image(ri); }   // main.cpp:220-223,:278
     ssr.preintegrate_pdf(render_graph);                                                           // main.cpp:269-270
     ssr.preintegrate_brdf(render_graph);
     gpu::ImageInfo sh; sh.format = VKR_FORMAT_D24_UNORM_S8_UINT; sh.width = 16; sh.height = 16;  // bound, never sampled (main.cpp:276-284)
@@ -184,6 +189,7 @@ struct VkrApp {
     else if (name == "st_filtered") id = screen_trace.filtered;
     else if (name == "st_accumulated") id = screen_trace.accumulated;
     else if (name == "tile_planes") id = ssr.get_tile_planes();
+    else if (name == "readback_image") id = readback_image;
     else return false;
     return true;
   }
@@ -313,6 +319,38 @@ int vkr_app_readback_buffer(VkrApp* app, const char* name, void* host_dst, uint6
     host_error("readback_buffer: cudaMemcpyAsync failed");
     return VKR_ERR_CUDA;
   }
+  return VKR_OK;
+}
+
+int vkr_app_capture(VkrApp* app, uint32_t kind, const char* path) {
+  if (!app || !path || kind > 2) { host_error("capture: null argument or unknown kind"); return VKR_ERR_INVALID_ARGUMENT; }
+  VKR_TRY({
+    ImageResourceId src;
+    ReadBackID id;
+    if (kind == 0) {                                                                              // "Final frame", main.cpp:393-396
+      app->lookup("taa", src);
+      blit_image(app->render_graph, src, app->readback_image);
+      id = app->readback_system.read_image(app->render_graph, app->readback_image, 0, 0, VKR_READBACK_OPAQUE_ALPHA);
+    } else {                                                                                      // depth, main.cpp:354
+      app->lookup("depth", src);
+      id = app->readback_system.read_image(app->render_graph, src, 0, 0, VKR_READBACK_DEPTH24);
+    }
+    app->render_graph.submit();
+    app->task_names.clear();
+    for (auto& n : app->render_graph.last_task_names()) { app->task_names += n; app->task_names += '\n'; }
+    uint32_t polls = 0;
+    while (!app->readback_system.is_data_available(id)) {                                         // main.cpp:404-412, once per frame there
+      app->readback_system.after_submit(app->render_graph);
+      if (++polls > 16) throw std::runtime_error{"capture: read-back never became available"};
+    }
+    auto data = app->readback_system.get_data(id);
+    const bool ok = kind == 0 ? get_rgba_cb(std::move(data), path) : kind == 1 ? get_depth_png_cb(std::move(data), path) : get_depth_cb(std::move(data), path);
+    if (!ok) throw std::runtime_error{std::string{"capture: cannot write "} + path};
+  })
+}
+
+int vkr_write_png_rgba8(const char* path, uint32_t width, uint32_t height, const void* rgba) {
+  if (!write_png_rgba8(path, width, height, (const uint8_t*)rgba)) { host_error("write_png_rgba8: cannot write '%s'", path ? path : "(null)"); return VKR_ERR_INVALID_ARGUMENT; }
   return VKR_OK;
 }
 

@@ -243,6 +243,9 @@ void RenderGraphBuilder::use_storage_buffer(BufferResourceId id, bool readonly) 
 void RenderGraphBuilder::use_indirect_buffer(BufferResourceId id) { use_buffer(id, false); }
 void RenderGraphBuilder::transfer_write(BufferResourceId id) { use_buffer(id, true); }
 
+void RenderGraphBuilder::transfer_read(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t, uint32_t) { make_view(id, base_mip, mip_count, false); }
+void RenderGraphBuilder::transfer_write(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t, uint32_t) { make_view(id, base_mip, mip_count, true); }
+
 void* RenderResources::get_buffer(BufferResourceId id) const { return graph.buffer(id); }
 const VkrImage* RenderResources::get_image(const ImageViewId& ref) const { return &graph.image(ref.get_id()); }
 const VkrImage* RenderResources::get_image(ImageResourceId id) const { return &graph.image(id); }

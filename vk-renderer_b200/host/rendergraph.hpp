@@ -105,6 +105,9 @@ struct RenderGraphBuilder {
   void use_storage_buffer(BufferResourceId id, bool readonly = true);
   void use_indirect_buffer(BufferResourceId id);
   void transfer_write(BufferResourceId id);
+  // image transfers (reference rendergraph.hpp: transfer_read / transfer_write with a subresource range)
+  void transfer_read(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t base_layer, uint32_t layer_count);
+  void transfer_write(ImageResourceId id, uint32_t base_mip, uint32_t mip_count, uint32_t base_layer, uint32_t layer_count);
 
  private:
   RenderGraph& graph;
@@ -200,6 +203,9 @@ struct RenderGraph {
 
   const VkrImage& image(ImageResourceId id) const;
   void* stream() const { return stream_; }
+  // reference RenderGraph::get_frames_count(): frames in flight (swapchain images there).  submit() here replays onto a stream
+  // immediately, so one frame is in flight; ReadBackSystem waits get_frames_count() + 1 submits like the reference.
+  uint32_t get_frames_count() const { return 1; }
   const std::vector<std::string>& last_task_names() const { return last_names; }
 
  private:

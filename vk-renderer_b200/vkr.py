@@ -375,6 +375,19 @@ def sssr_tile_regression(p, depth, out_planes, stream=None):
     check(lib.vkr_sssr_tile_regression(C.byref(p), depth.ptr, out_planes.ptr, stream_ptr(stream)))
 
 
+_sig("vkr_blit_image", IP, IP, VP)
+_sig("vkr_readback_pack", IP, C.c_uint32, C.c_uint32, VP, VP)
+READBACK_RAW, READBACK_DEPTH24, READBACK_OPAQUE_ALPHA = 0, 1, 2
+
+
+def blit_image(src, dst, stream=None):
+    check(lib.vkr_blit_image(src.ptr, dst.ptr, stream_ptr(stream)))
+
+
+def readback_pack(image, out_tensor, mip=0, mode=READBACK_RAW, stream=None):
+    check(lib.vkr_readback_pack(image.ptr, mip, mode, _dp(out_tensor), stream_ptr(stream)))
+
+
 def pdf_preintegrate(out, stream=None):
     check(lib.vkr_pdf_preintegrate(out.ptr, stream_ptr(stream)))
 

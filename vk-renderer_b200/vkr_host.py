@@ -33,6 +33,10 @@ lib.vkr_app_readback.restype = C.c_int
 lib.vkr_app_readback.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64]
 lib.vkr_app_readback_buffer.restype = C.c_int
 lib.vkr_app_readback_buffer.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+lib.vkr_app_capture.restype = C.c_int
+lib.vkr_app_capture.argtypes = [C.c_void_p, C.c_uint32, C.c_char_p]
+lib.vkr_write_png_rgba8.restype = C.c_int
+lib.vkr_write_png_rgba8.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p]
 lib.vkr_app_sync.restype = C.c_int
 lib.vkr_app_sync.argtypes = [C.c_void_p]
 lib.vkr_app_stream.restype = C.c_void_p
@@ -173,6 +177,12 @@ class App:
         _check(lib.vkr_app_get_image(self.h, name.encode(), C.byref(d)))
         return d
 
+    FINAL_FRAME, DEPTH_PNG, DEPTH_CSV = 0, 1, 2
+
+    def capture(self, kind, path):
+        """The reference's capture buttons (main.cpp:352-357,:393-412): blit + read-back + PNG / CSV file at `path`."""
+        _check(lib.vkr_app_capture(self.h, kind, str(path).encode()))
+
     def readback_buffer(self, name, dtype="int32"):
         """A named rendergraph buffer of the SSSR tile path as a numpy array."""
         import numpy as np
@@ -192,3 +202,35 @@ class App:
         if sync:
             self.sync()
         return host_image
+
+
+def write_png_rgba8(path, rgba):
+    """Host-only PNG writer of the capture path; rgba = uint8 array (h, w, 4)."""
+    import numpy as np
+    a = np.ascontiguousarray(rgba, dtype=np.uint8)
+    _check(lib.vkr_write_png_rgba8(str(path).encode(), a.shape[1], a.shape[0], a.ctypes.data_as(C.c_void_p)))
+
+
+def read_png_rgba8(path):
+    """Minimal decoder for the files write_png_rgba8 produces (8-bit RGBA, filter 0 scanlines); checks every chunk CRC."""
+    import struct
+    import zlib
+
+    import numpy as np
+    b = open(path, "rb").read()
+    assert b[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w, h = 8, b"", 0, 0
+    while pos < len(b):
+        n, typ = struct.unpack(">I4s", b[pos:pos + 8])
+        data = b[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", b[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(typ + data) == crc, typ
+        if typ == b"IHDR":
+            w, h, depth, ctype, comp, flt, inter = struct.unpack(">IIBBBBB", data)
+            assert (depth, ctype, comp, flt, inter) == (8, 6, 0, 0, 0)
+        elif typ == b"IDAT":
+            idat += data
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), dtype=np.uint8).reshape(h, w * 4 + 1)
+    assert (raw[:, 0] == 0).all()
+    return raw[:, 1:].reshape(h, w, 4).copy()
