@@ -42,6 +42,18 @@ def parse():
                     help="tiles workload: leave each rank's finished TAA rows resident where they were computed (none), or send them to rank 0 every "
                          "frame (rank0: 265 MB per 8K frame into one GPU)")
     ap.add_argument("--no-tiles-balance", dest="tiles_balance", action="store_false", help="tiles workload: keep the even row split")
+    ap.add_argument("--probes-lanes", type=int, default=2, choices=[1, 2],
+                    help="probes workload: 2 = SSR filter + blur on a second stream beside the GTAO passes inside the frame's CUDA graph")
+    ap.add_argument("--probes-groups", type=int, default=2,
+                    help="probes workload: split a rank's views into this many layer ranges, each running its chain on its own streams inside the "
+                         "frame's CUDA graph (independent views fill each other's launch gaps and tails)")
+    ap.add_argument("--probes-gather", default="allgather", choices=["allgather", "p2p", "none"],
+                    help="probes workload: how every rank gets all per-view results each frame — allgather: NCCL all_gather_into_tensor on a "
+                         "side stream; p2p: copy-engine pushes into every rank's cudaIpc slab with stream-side flags (vkr_gather.PeerGather: no "
+                         "SMs taken from the passes); none: skip it (diagnostic: what the gather costs the frame rate)")
+    ap.add_argument("--nccl-max-ctas", type=int, default=0,
+                    help="probes workload: cap the CTAs NCCL may use per collective (0 = NCCL's default).  The gather moves 64 MB per frame into "
+                         "every GPU while the passes want every SM; a small cap leaves the SMs to the passes")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -334,13 +346,20 @@ def run_probes(args, rank, world):
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        opts = None
+        if args.nccl_max_ctas > 0:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = args.nccl_max_ctas
+            opts.config.min_ctas = min(args.nccl_max_ctas, 1)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
     import vkr
     import vkr_views
     w = h = 256
     K, W = args.steps, args.warmup
     b, e = vkr_views.shard_range(args.views, world, rank)
     stream, side = torch.cuda.Stream(), torch.cuda.Stream()
+    lane2 = torch.cuda.Stream() if args.probes_lanes == 2 else None
+    gstreams = [(torch.cuda.Stream(), torch.cuda.Stream() if args.probes_lanes == 2 else None) for _ in range(max(0, args.probes_groups - 1))]
     assert e - b > 1, "the batched path needs at least 2 views per rank"
     nres = 4                                                # resident input frames (cycled); > L2 in total
     with torch.cuda.stream(stream):
@@ -378,8 +397,21 @@ def run_probes(args, rank, world):
         vb.blurred, vb.blurred_history = vb.blurred_history, vb.blurred
         vb.accumulated_ao, vb.accumulated_history = vb.accumulated_history, vb.accumulated_ao
 
+    pg = None
+    if world > 1 and args.probes_gather == "p2p":
+        import vkr_gather
+
+        def allgather_bytes(x):
+            out = [None] * world
+            dist.all_gather_object(out, x)
+            return out
+        pg = vkr_gather.PeerGather(args.views, [ao0.shape[1], refl0.shape[1]], rank, world, allgather_bytes, f"cuda:{local}")
+
     def gather(ao, refl):
-        if world > 1:                                        # final gather of the per-view results, off the compute stream
+        if pg is not None:
+            pg.push([ao, refl], stream)
+            return
+        if world > 1 and args.probes_gather == "allgather":  # final gather of the per-view results, off the compute stream
             done.record(stream)
             side.wait_event(done)
             with torch.cuda.stream(side):
@@ -390,6 +422,8 @@ def run_probes(args, rank, world):
         """Steps 0..nres-1 run eagerly, steps nres..2*nres-1 are captured into one CUDA graph each (the image bindings repeat
         with period nres, nres even), later steps replay: 9 kernel launches per frame with no host work between them."""
         f = i % nres
+        if pg is not None:
+            pg.sources_free(stream)                          # this frame overwrites the result images of two frames ago
         if i >= 2 * nres:
             graphs[f].replay()
             gather(*outs[f])
@@ -398,11 +432,11 @@ def run_probes(args, rank, world):
         if i >= nres:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=stream):
-                vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f)
+                vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f, aux_stream=lane2, group_streams=gstreams)
             graphs[f], outs[f] = g, vb.outputs()
             g.replay()
         else:
-            vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f)
+            vb.passes(params[f], flags=vkr.EXT_PARAMS_PREPARED, param_set=f, aux_stream=lane2, group_streams=gstreams)
         gather(*vb.outputs())
         swap()
 
@@ -424,7 +458,9 @@ def run_probes(args, rank, world):
         for i in range(W, W + K):
             step(i)
         host_ms = (time.perf_counter() - t_host0) * 1e3 / K      # CPU time to ENQUEUE one frame (not a GPU time)
-        tf.finish()                                          # the last frame's TAA halo (waited for inside the next frame otherwise)
+        if pg is not None:
+            pg.finish()                                      # the last epoch has landed here too
+            stream.wait_stream(pg.xfer)
         stream.wait_stream(side)
         e1.record(stream)
         stream.synchronize()
@@ -436,6 +472,10 @@ def run_probes(args, rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     sampler.join(timeout=1.0)
+    gather_timeouts = 0
+    if pg is not None:
+        gather_timeouts = pg.wait_failures()
+        pg.close(dist.barrier)
     if rank != 0:
         return
     peak, peak_src = peaks()
@@ -445,11 +485,11 @@ def run_probes(args, rank, world):
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.views} probe views 256x256, Hi-Z+GTAO+SSR, contiguous view blocks per rank (BASELINE configs[3])",
-                       "frames_resident": nres, "launch": "one CUDA graph of 9 kernels per frame, parameter blocks prepared once", "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
-                       "parallelism": f"views sharded over {world} rank(s); all_gather of AO + reflections per frame on a side stream"},
+                       "frames_resident": nres, "launch": f"one CUDA graph per frame: {args.probes_groups} view range(s) x 9 kernels" + (" (SSR filter+blur beside the GTAO passes)" if args.probes_lanes == 2 else "") + ", parameter blocks prepared once", "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
+                       "parallelism": f"views sharded over {world} rank(s); " + {"allgather": "all_gather of AO + reflections per frame on a side stream", "p2p": "AO + reflections pushed into every rank's cudaIpc slab per frame by the copy engines, stream-side flags (no collective, no SMs)", "none": "NO gather (diagnostic run)"}[args.probes_gather] + (f", NCCL capped at {args.nccl_max_ctas} CTAs" if args.nccl_max_ctas > 0 else "")},
             "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
-            "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+            "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * max(1, args.probes_groups) * K, "gather_wait_timeouts": gather_timeouts, "clocks": sampler.result()}
     print(json.dumps(line))
 
 

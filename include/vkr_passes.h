@@ -169,7 +169,7 @@ typedef struct VkrScreenTraceParams {
  *  - flags (layers > 1 only): VKR_EXT_PREPARE_ONLY converts and uploads the params blocks into params_scratch and
  *    returns without launching; VKR_EXT_PARAMS_PREPARED launches with the blocks an earlier call of the SAME entry
  *    left in params_scratch (no host conversion, no copy: the call is then pure kernel launches and can be captured
- *    into a CUDA graph). */
+ *    into a CUDA graph); first_param: see the struct. */
 #define VKR_ROW_ALIGN 16
 #define VKR_PARAMS_SCRATCH_STRIDE 256
 #define VKR_MAX_IMAGE_ARGS 10
@@ -181,6 +181,10 @@ typedef struct VkrLaunchExt {
   uint32_t flags;
   uint64_t layer_stride[VKR_MAX_IMAGE_ARGS];
   void* params_scratch;
+  uint32_t first_param;   /* with VKR_EXT_PARAMS_PREPARED: layer z of this launch uses block first_param + z of the prepared set, so a
+                           * batch prepared once can be launched as several layer ranges (each range's VkrImage arguments then
+                           * describe its first layer).  Independent ranges on separate streams fill each other's tails. */
+  uint32_t reserved;
 } VkrLaunchExt;
 
 /* ---- utilities ---------------------------------------------------------------- */

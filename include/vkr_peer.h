@@ -32,6 +32,12 @@ int vkr_peer_close(void* peer_ptr);
  * image's offset).  Rows are clamped to the mip's height; an empty range is a no-op.  Asynchronous on `stream`. */
 int vkr_peer_push_rows(const VkrImage* img, uint32_t lod, uint32_t row_begin, uint32_t row_end, void* peer_image_base, void* stream);
 
+/* Copies `rows` rows of `width_bytes` bytes from local device memory (row pitch src_pitch) to peer-mapped memory (row pitch
+ * dst_pitch) with the copy engines — no SM is involved, so a transfer queued beside running kernels costs them nothing.  Used for
+ * the final gather of the batched views (vkr_views.PeerGather): a rank's block of per-view results lands in every peer's
+ * gather buffer.  Asynchronous on `stream`. */
+int vkr_peer_push_2d(const void* src, uint64_t src_pitch, void* peer_dst, uint64_t dst_pitch, uint64_t width_bytes, uint64_t rows, void* stream);
+
 /* After everything queued on `stream` so far: system-scope release store of `value` to *flag (usually peer memory). */
 int vkr_peer_signal(uint32_t* flag, uint32_t value, void* stream);
 /* Holds `stream` until *flag >= value (system-scope acquire loads from a one-thread kernel).  After timeout_ms without

@@ -94,3 +94,46 @@ def test_row_window_validation(cuda):
     with pytest.raises(vkr.VkrError, match="row windows are not supported"):
         vkr.hiz_build_ex(cc.gb.depth, cc.gb.normal, cc.gb.velocity_vectors, cc.gb.downsampled_normals, cc.gb.downsampled_velocity_vectors,
                          vkr.make_ext([], rows=(0, 16)))
+
+
+def test_view_ranges_on_separate_streams_write_the_same_bytes(cuda):
+    """ViewBatch.passes with prepared parameter blocks split into layer ranges on their own stream pairs (what bench.py's probe
+    workload captures into its frame graph) writes exactly the bytes of the single-launch form, two frames in a row."""
+    import torch
+    w = h = 128
+    views = list(range(7))                               # odd count: ranges of 2, 2, 3 views
+    pdf = vkr.Image(64, 64, vkr.R32_SFLOAT)
+    vkr.pdf_preintegrate(pdf)
+    st = torch.cuda.Stream()
+    a = vkr_views.ViewBatch(w, h, views, luts=pdf, stream=st)
+    b = vkr_views.ViewBatch(w, h, views, luts=pdf, stream=st)
+    gs = [(torch.cuda.Stream(), torch.cuda.Stream()), (torch.cuda.Stream(), None)]
+    with torch.cuda.stream(st):
+        for f in range(2):
+            for vb in (a, b):
+                vb.synth_inputs()
+            P = a.params()
+            a.passes(P)
+            b.passes(P, flags=vkr.EXT_PREPARE_ONLY)
+            b.passes(P, flags=vkr.EXT_PARAMS_PREPARED, aux_stream=gs[1][0], group_streams=gs[:1] + [(gs[0][1], None)])
+            st.synchronize()
+            for name in ("depth", "dn", "dv", "rays", "raw", "reflections", "blurred", "filtered", "accumulated_ao"):
+                assert torch.equal(getattr(a, name).buf, getattr(b, name).buf), (f, name)
+            a.end_frame(); b.end_frame()
+
+
+@pytest.mark.parametrize("world,n_units,epochs", [(2, 16, 5), (3, 10, 4)])
+def test_peer_gather_equals_all_gather(cuda, world, n_units, epochs):
+    """vkr_gather.PeerGather (copy-engine pushes into every rank's cudaIpc slab + stream-side flags) against the blocks an
+    all_gather would deliver, several epochs in a row (buffer reuse), ragged shards, strided source rows.  One process per rank;
+    on a single-GPU box the ranks share cuda:0 (the IPC mapping, pushes and flags are exercised all the same)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    port = 29300 + (os.getpid() + world) % 500
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tests", "gather_worker.py"), root, str(n_units), str(epochs)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("ok") == world

@@ -47,6 +47,29 @@ pparams = vkr_probes.ProbeTraceParams(vkr.mat_inverse(P["shade"].camera), t.fovy
 probe_out = vkr.Image(w, h, vkr.R8G8B8A8_UNORM)
 pr.render_octahedral(cubes, grid.color_array, grid.depth_array, 0, 16)
 pr.probe_downsample(grid.depth_array, 0, 16)
+# SSSR tile path + capture path
+ntiles = ((w2 + 7) // 8) * ((h2 + 7) // 8)
+t_r, t_g = torch.zeros(ntiles, dtype=torch.int32, device="cuda"), torch.zeros(ntiles, dtype=torch.int32, device="cuda")
+i_r, i_g = torch.zeros(3, dtype=torch.int32, device="cuda"), torch.zeros(3, dtype=torch.int32, device="cuda")
+cls = vkr.ClassifyParams(w2, h2, 1.0, 0.5)
+hal_dev = torch.from_numpy(vkr.halton23_seq(128)).cuda()
+tile_rays = vkr.Image(w2, h2, vkr.R16G16B16A16_UNORM)
+planes = vkr.Image(max(1, w // 16), max(1, h // 16), vkr.R32G32B32A32_SFLOAT)
+rg = vkr.RegressionParams()
+C.memmove(rg.camera_to_world, vkr.mat_transpose(t.normal_mat), 64)
+rg.fovy, rg.aspect, rg.znear, rg.zfar = t.fovy, t.aspect, t.znear, t.zfar
+rb_img = vkr.Image(w, h, vkr.R8G8B8A8_SRGB)
+rb_tight = torch.zeros(w * h * 4, dtype=torch.uint8, device="cuda")
+
+
+def classify():
+    vkr.sssr_clear_indirect(i_r, i_g)
+    vkr.sssr_classification(cls, imgs["material"], t_r, t_g, i_r, i_g)
+
+
+classify()
+torch.cuda.synchronize()
+print("tiles: reflective", int(i_r[0]), "glossy", int(i_g[0]), "of", ntiles)
 NP = 16 * 256 * 256
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 calls = {"SSAO": (lambda: vkr.ssao(p, imgs["depth"], ao), 5.0),                       # D24 read + R8 write
@@ -58,6 +81,12 @@ calls = {"SSAO": (lambda: vkr.ssao(p, imgs["depth"], ao), 5.0),                 
          "GTAO_reproject(half-res)": (lambda: vkr.gtao_reproject(cam, imgs["depth"], imgs["prev_depth"], r16[0], r16[1], r16[2]), (8 + 6) / 4),
          "Cubemap2Octahedral x16": (lambda: pr.render_octahedral(cubes, grid.color_array, grid.depth_array, 0, 16), None),
          "DownsampleProbe x16": (lambda: pr.probe_downsample(grid.depth_array, 0, 16), None),
+         "SSSR_Clear+Classification": (classify, 1.0 + 2 * 4 / 256),          # material at half-res corners: every full-res texel once
+         "SSSR_trace(mirror tiles)": (lambda: vkr.sssr_trace_indirect(t, 0, imgs["depth"], imgs["dn"], imgs["material"], hal_dev, t_r, i_r, tile_rays), None),
+         "SSSR_trace(glossy tiles)": (lambda: vkr.sssr_trace_indirect(t, 1, imgs["depth"], imgs["dn"], imgs["material"], hal_dev, t_g, i_g, tile_rays), None),
+         "SSSR_Tile_Regression": (lambda: vkr.sssr_tile_regression(rg, imgs["depth"], planes), 1.0 + 16.0 / 256),
+         "CopyImage(TAA->sRGB8)": (lambda: vkr.blit_image(imgs["taa"], rb_img), 12.0),
+         "ImageRead(pack RGBA8)": (lambda: vkr.readback_pack(rb_img, rb_tight, 0, vkr.READBACK_OPAQUE_ALPHA), 8.0),
          "TraceProbe": (lambda: ptp.run(grid, imgs["depth"], imgs["normal"], probe_out, pparams), 12.0)}
 rows = []
 for name, (fn, alg) in calls.items():
@@ -71,7 +100,9 @@ for name, (fn, alg) in calls.items():
         torch.cuda.synchronize()
         tot += a.elapsed_time(b)
     ms = tot / iters
-    if alg is None:                    # probe conversion: 16 probes of 256^2, 6 B/texel out + cube reads / 1.33 * 2 B pyramid
+    if alg is None and name.startswith("SSSR_trace"):   # share of the per-pixel trace's 10.33 B/px that this list's tiles cover
+        alg_bytes = 10.33 * w * h * (int(i_r[0]) if "mirror" in name else int(i_g[0])) / ntiles
+    elif alg is None:                  # probe conversion: 16 probes of 256^2, 6 B/texel out + cube reads / 1.33 * 2 B pyramid
         alg_bytes = NP * (6 + 6) if "Cubemap" in name else NP * 2 * (1 + 1 / 3)
     else:
         alg_bytes = alg * w * h

@@ -16,7 +16,8 @@ for f in range(3):
     blk = it[:hh, :ww].reshape(hh // 2, 2, ww // 16, 16)
     wmax = blk.max(axis=(1, 3))
     b8 = it[:h2 // 8 * 8, :w2 // 4 * 4].reshape(h2 // 8, 8, w2 // 4, 4).max(axis=(1, 3))
-    print(f"frame {f}: mean iters {it.mean():.2f}  mean of warp(16x2) max {wmax.mean():.2f}  (4x8 tiles: {b8.mean():.2f})  utilisation {it.mean()/wmax.mean():.3f}  hist",
+    b84 = it[:h2 // 4 * 4, :w2 // 8 * 8].reshape(h2 // 4, 4, w2 // 8, 8).max(axis=(1, 3))
+    print(f"frame {f}: mean iters {it.mean():.2f}  mean of warp(16x2) max {wmax.mean():.2f}  (8x4: {b84.mean():.2f}, 4x8: {b8.mean():.2f})  utilisation {it.mean()/wmax.mean():.3f}  hist",
           np.histogram(it, bins=[0, 1, 5, 10, 16, 20, 30, 40, 60, 79, 81])[0] / it.size)
     for _, t, _ in st[2:]:
         t()

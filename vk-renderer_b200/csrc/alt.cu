@@ -190,7 +190,7 @@ extern "C" int vkr_ssao_ex(const VkrSsaoParams* p, const VkrImage* depth, const 
       for (int i = 0; i < x.layers; i++) ks[i] = make_ssao_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(SsaoK), x.layers, x.scratch(), st, "ssao"))) return rc;
     }
-    kv = (const SsaoK*)x.scratch();
+    kv = (const SsaoK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   SsaoSamples S;
@@ -234,7 +234,7 @@ extern "C" int vkr_ssr_legacy_ex(const VkrSsrParams* p, const VkrImage* depth, c
       for (int i = 0; i < x.layers; i++) ks[i] = make_ssr_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(SsrK), x.layers, x.scratch(), st, "ssr_legacy"))) return rc;
     }
-    kv = (const SsrK*)x.scratch();
+    kv = (const SsrK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   PyramidView P;                                   // every mip of the depth image (ssr.cpp:45 samples the whole chain)

@@ -44,6 +44,10 @@ int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, c
     set_error("%s: layers > 1 needs params_scratch (device memory, layers * VKR_PARAMS_SCRATCH_STRIDE bytes)", what);
     return VKR_ERR_INVALID_ARGUMENT;
   }
+  if (e && e->first_param && !(o->layers > 1 && (e->flags & VKR_EXT_PARAMS_PREPARED))) {
+    set_error("%s: first_param needs layers > 1 and VKR_EXT_PARAMS_PREPARED (it selects blocks of a set prepared earlier)", what);
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
   if (o->layers > 65535) { set_error("%s: at most 65535 layers per launch", what); return VKR_ERR_INVALID_ARGUMENT; }
   return VKR_OK;
 }

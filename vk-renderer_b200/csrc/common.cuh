@@ -55,6 +55,7 @@ struct ExtInfo {
   const VkrLaunchExt* e = nullptr;
   uint64_t stride(int i) const { return (e && e->layers > 1) ? e->layer_stride[i] : 0; }
   void* scratch() const { return e ? e->params_scratch : nullptr; }
+  unsigned first() const { return e ? e->first_param : 0u; }   // block of the prepared set the launch's layer 0 uses
   bool prepared() const { return e && (e->flags & VKR_EXT_PARAMS_PREPARED); }
   bool prepare_only() const { return e && (e->flags & VKR_EXT_PREPARE_ONLY); }
 };

@@ -346,7 +346,7 @@ extern "C" int vkr_gtao_main_ex(const VkrGtaoParams* p, const VkrImage* depth, c
       for (int i = 0; i < x.layers; i++) ks[i] = make_gtao_k(p + i, raw);
       if ((rc = upload_params(ks.data(), sizeof(GtaoK), x.layers, x.scratch(), st, "gtao_main"))) return rc;
     }
-    kv = (const GtaoK*)x.scratch();
+    kv = (const GtaoK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((k.tw + 31) / 32, x.yblocks, x.layers);
@@ -420,7 +420,7 @@ extern "C" int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* d
       for (int i = 0; i < x.layers; i++) ks[i] = make_accum_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(AccumK), x.layers, x.scratch(), st, "gtao_accumulate"))) return rc;
     }
-    kv = (const AccumK*)x.scratch();
+    kv = (const AccumK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((accumulated->width + 31) / 32, x.yblocks, x.layers);

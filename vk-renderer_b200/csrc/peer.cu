@@ -74,6 +74,15 @@ extern "C" int vkr_peer_push_rows(const VkrImage* img, uint32_t lod, uint32_t ro
                  "peer_push_rows");
 }
 
+extern "C" int vkr_peer_push_2d(const void* src, uint64_t src_pitch, void* peer_dst, uint64_t dst_pitch, uint64_t width_bytes, uint64_t rows, void* stream) {
+  if (!src || !peer_dst || src_pitch < width_bytes || dst_pitch < width_bytes) { set_error("peer_push_2d: bad arguments"); return VKR_ERR_INVALID_ARGUMENT; }
+  if (!width_bytes || !rows) return VKR_OK;
+  if (src_pitch == width_bytes && dst_pitch == width_bytes)      // one contiguous block: a single DMA descriptor
+    return cuda_rc(cudaMemcpyAsync(peer_dst, src, (size_t)(width_bytes * rows), cudaMemcpyDefault, (cudaStream_t)stream), "peer_push_2d");
+  return cuda_rc(cudaMemcpy2DAsync(peer_dst, (size_t)dst_pitch, src, (size_t)src_pitch, (size_t)width_bytes, (size_t)rows, cudaMemcpyDefault, (cudaStream_t)stream),
+                 "peer_push_2d");
+}
+
 extern "C" int vkr_peer_signal(uint32_t* flag, uint32_t value, void* stream) {
   if (!flag) { set_error("peer_signal: null flag"); return VKR_ERR_INVALID_ARGUMENT; }
   peer_signal_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value);

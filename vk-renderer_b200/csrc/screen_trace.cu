@@ -245,7 +245,7 @@ extern "C" int vkr_screen_trace_main_ex(const VkrScreenTraceParams* p, const Vkr
       for (int i = 0; i < x.layers; i++) ks[i] = make_st_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(StK), x.layers, x.scratch(), st, "screen_trace_main"))) return rc;
     }
-    kv = (const StK*)x.scratch();
+    kv = (const StK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   const float* srgb = srgb_decode_table_device();

@@ -246,7 +246,7 @@ extern "C" int vkr_deferred_shading_ex(const VkrShadingParams* p, const VkrImage
       for (int i = 0; i < x.layers; i++) ks[i] = make_shade_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(ShadeK), x.layers, x.scratch(), st, "deferred_shading"))) return rc;
     }
-    kv = (const ShadeK*)x.scratch();
+    kv = (const ShadeK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_color->width + 31) / 32, x.yblocks, x.layers);

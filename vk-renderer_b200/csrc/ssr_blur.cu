@@ -345,7 +345,7 @@ extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, c
       for (int i = 0; i < x.layers; i++) ks[i] = make_blur_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(BlurK), x.layers, x.scratch(), st, "sssr_blur"))) return rc;
     }
-    kv = (const BlurK*)x.scratch();
+    kv = (const BlurK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_blurred->width + BLUR_TW - 1) / BLUR_TW, x.yblocks, x.layers);

@@ -166,7 +166,7 @@ extern "C" int vkr_sssr_filter_ex(const VkrTraceParams* p, const VkrImage* rays,
       for (int i = 0; i < x.layers; i++) ks[i] = make_filter_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(FilterK), x.layers, x.scratch(), st, "sssr_filter"))) return rc;
     }
-    kv = (const FilterK*)x.scratch();
+    kv = (const FilterK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_reflections->width + FT_W - 1) / FT_W, x.yblocks, x.layers);

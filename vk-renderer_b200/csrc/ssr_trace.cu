@@ -7,6 +7,9 @@
 #include "brdf.cuh"
 #include "march.cuh"
 
+#ifndef TRACE_WARP_SHAPE
+#define TRACE_WARP_SHAPE 162
+#endif
 #ifndef TRACE_UNROLL_A
 #define TRACE_UNROLL_A 1
 #endif
@@ -40,7 +43,13 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
     normal = layer_of(normal, z); material = layer_of(material, z); pdf = layer_of(pdf, z); out_rays = layer_of(out_rays, z); out_occl = layer_of(out_occl, z);
   }
   const TraceK& k = LAYERED ? kl : k0;
+#if TRACE_WARP_SHAPE == 84      // a warp covers 8 x 4 pixels: neighbouring rays march alike, so a compact footprint idles fewer lanes
+  const int px = blockIdx.x * 16 + ((threadIdx.x >> 5) & 1) * 8 + (threadIdx.x & 7), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 6) * 4 + ((threadIdx.x >> 3) & 3);
+#elif TRACE_WARP_SHAPE == 48    // 4 x 8
+  const int px = blockIdx.x * 16 + ((threadIdx.x >> 5) & 3) * 4 + (threadIdx.x & 3), py = VKR_BLOCK_Y * 8 + ((threadIdx.x >> 2) & 7);
+#else                           // 16 x 2
   const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 4);
+#endif
   if (px >= out_rays.w || py >= out_rays.h) return;
   const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
   const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
@@ -207,7 +216,7 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
       for (int i = 0; i < x.layers; i++) ks[i] = make_trace_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(TraceK), x.layers, x.scratch(), st, "sssr_trace"))) return rc;
     }
-    kv = (const TraceK*)x.scratch();
+    kv = (const TraceK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   PyramidView P;

@@ -161,7 +161,7 @@ extern "C" int vkr_taa_resolve_ex(const VkrTaaParams* p, const VkrImage* history
       for (int i = 0; i < x.layers; i++) ks[i] = make_taa_k(p + i);
       if ((rc = upload_params(ks.data(), sizeof(TaaK), x.layers, x.scratch(), st, "taa_resolve"))) return rc;
     }
-    kv = (const TaaK*)x.scratch();
+    kv = (const TaaK*)x.scratch() + x.first();
     if (x.prepare_only()) return VKR_OK;
   }
   dim3 grid((out_target->width + 31) / 32, x.yblocks, x.layers);

@@ -435,7 +435,7 @@ def taa_resolve(p, history, prev_depth, depth, velocity, color, out, stream=None
 # ---- extended launches: array layers and row windows (include/vkr_passes.h VkrLaunchExt) ---------------
 class LaunchExt(C.Structure):
     _fields_ = [("layers", C.c_uint32), ("row_begin", C.c_uint32), ("row_end", C.c_uint32), ("flags", C.c_uint32), ("layer_stride", C.c_uint64 * 10),
-                ("params_scratch", C.c_void_p)]
+                ("params_scratch", C.c_void_p), ("first_param", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 PARAMS_SCRATCH_STRIDE = 256
@@ -497,13 +497,30 @@ class ImageArray:
         return im
 
 
+class LayerRange:
+    """Layers [first, first + count) of an ImageArray as the `_ex` entries want them: descriptor of the first layer of the range
+    plus the array's layer stride (shares storage)."""
+
+    def __init__(self, arr, first, count):
+        assert 0 <= first and first + count <= arr.layers
+        self.desc = VkrImage.from_buffer_copy(arr.desc)
+        self.desc.base = arr.desc.base + first * arr.layer_stride
+        self.layer_stride, self.layers = arr.layer_stride, count
+        self._keep = arr
+
+    @property
+    def ptr(self):
+        return C.byref(self.desc)
+
+
 EXT_PREPARE_ONLY, EXT_PARAMS_PREPARED = 1, 2
 
 
-def make_ext(images, layers=1, rows=None, scratch=None, flags=0):
+def make_ext(images, layers=1, rows=None, scratch=None, flags=0, first_param=0):
     """VkrLaunchExt for a call whose VkrImage arguments are `images` (ImageArray or Image, in argument order)."""
     e = LaunchExt()
     e.layers = layers
+    e.first_param = first_param
     e.flags = flags
     if rows is not None:
         e.row_begin, e.row_end = rows

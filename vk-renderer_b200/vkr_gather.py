@@ -1,0 +1,104 @@
+"""The final gather of sharded per-unit results as peer stores over NVLink (BASELINE.json configs[3]: the batched probe views).
+
+Every rank owns, inside a cudaIpc slab (include/vkr_peer.h), two gather buffers per result tensor — (n_units, row_bytes) each,
+used alternately by even and odd epochs — and maps every other rank's slab.  Per epoch (= frame) a rank copies its block of rows
+into the same rows of every peer's buffer with the COPY ENGINES (vkr_peer_push_2d: cudaMemcpyAsync on peer-mapped memory, no SM
+involved) and then raises its flag in that peer's slab; the gathered epoch is complete on a rank once its world - 1 flags have
+reached the epoch.  Nothing synchronises the host and nothing runs on the SMs except one-thread flag kernels, so the gather costs
+the passes that run beside it no issue slots — an NCCL all_gather of the same 64 MB per frame takes about 7 % of them
+(DESIGN.md §5).  Reuse of a buffer needs no further handshake: a rank pushes epoch e only after it has seen every peer's flag
+for e - 1, and a peer raises that flag behind everything its `after_stream` held when it called push(e - 1).  So the one rule for
+a consumer is: read epoch e - 2 (gathered(e - 2, stream)) on a stream that push(e - 1) is then given as `after_stream` — consume
+the previous epoch, then push the next one.  The SOURCE blocks of an epoch may be overwritten once sources_free(stream) has made
+the writer wait for that epoch's copies.
+"""
+import ctypes as C
+
+import torch
+
+import vkr
+from vkr_tiles import _P, PeerSlab
+from vkr_views import shard_range
+
+
+class PeerGather:
+    def __init__(self, n_units, row_bytes, rank, world, allgather_bytes, device, timeout_ms=2000):
+        """row_bytes: bytes per unit of each result tensor, e.g. [65536, 65536].  allgather_bytes(b) -> list over ranks (host side,
+        any transport: it only carries the 64-byte IPC handles once)."""
+        self.n_units, self.row_bytes, self.rank, self.world = n_units, list(row_bytes), rank, world
+        self.device, self.timeout = torch.device(device), timeout_ms
+        self.first, self.end = shard_range(n_units, world, rank)
+        sizes = [n_units * rb for rb in self.row_bytes]
+        self.slab = PeerSlab(2 * sum((s + 255) & ~255 for s in sizes), self.device)
+        assert world * 4 <= PeerSlab.FLAG_BYTES
+        self.bufs = [[self.slab.carve(s).view(n_units, rb) for s, rb in zip(sizes, self.row_bytes)] for _ in range(2)]
+        handles = allgather_bytes(self.slab.handle_bytes())
+        for r in range(world):
+            if r != rank:
+                self.slab.open_peer(r, handles[r])
+        self.epoch = 0
+        self.xfer = torch.cuda.Stream(device=self.device)
+        self._ready = torch.cuda.Event()
+        self._sent = [torch.cuda.Event(), torch.cuda.Event()]   # behind the copies of the last even / odd epoch
+
+    def _flag(self, base, src_rank):
+        return base + 4 * src_rank
+
+    def _wait_epoch(self, epoch, st):
+        for r in range(self.world):
+            if r != self.rank:
+                vkr.check(_P.vkr_peer_wait(C.c_void_p(self._flag(self.slab.ptr, r)), epoch, self.timeout, st))
+
+    def push(self, blocks, after_stream):
+        """blocks: this rank's (units_r, >= row_bytes) uint8 views, one per result tensor (rows may be strided).  Queues, behind
+        everything `after_stream` holds now, the copy of the blocks into every rank's buffers of the new epoch.  Returns the epoch."""
+        self.epoch += 1
+        e, st = self.epoch, C.c_void_p(self.xfer.cuda_stream)
+        self._ready.record(after_stream)
+        self.xfer.wait_event(self._ready)
+        if e > 1:
+            self._wait_epoch(e - 1, st)            # every peer has finished with epoch e - 2, the last tenant of this buffer
+        units = self.end - self.first
+        for t, (blk, rb) in enumerate(zip(blocks, self.row_bytes)):
+            assert blk.shape[0] == units and blk.shape[1] >= rb and blk.stride(1) == 1
+            src, pitch = blk.data_ptr(), blk.stride(0)
+            own = self.bufs[e & 1][t]
+            for r in range(self.world):
+                base = self.slab.ptr if r == self.rank else self.slab.peers[r]
+                dst = base + (own.data_ptr() - self.slab.ptr) + self.first * rb
+                vkr.check(_P.vkr_peer_push_2d(C.c_void_p(src), pitch, C.c_void_p(dst), rb, rb, units, st))
+        self._sent[e & 1].record(self.xfer)
+        for r in range(self.world):
+            if r != self.rank:
+                vkr.check(_P.vkr_peer_signal(C.c_void_p(self._flag(self.slab.peers[r], self.rank)), e, st))
+        return e
+
+    def sources_free(self, stream, epoch=None):
+        """Make `stream` wait until the copies of `epoch` (default: the one before the last pushed — with results that alternate
+        between two images, the image the next frame writes) have read their source blocks."""
+        e = self.epoch - 1 if epoch is None else epoch
+        if e >= 1 and e > self.epoch - 2:
+            stream.wait_event(self._sent[e & 1])
+
+    def gathered(self, epoch, stream=None):
+        """Holds `stream` (default: the transfer stream) until `epoch` is complete on this rank and returns its (n_units, row_bytes)
+        tensors.  Consume them on a stream that is (or is ordered before) the `after_stream` of push(epoch + 1): that push's
+        flag is what lets the peers overwrite this buffer with epoch + 2."""
+        st = self.xfer if stream is None else stream
+        if stream is not None:                       # own rows arrive through the transfer stream
+            ev = torch.cuda.Event()
+            ev.record(self.xfer)
+            st.wait_event(ev)
+        self._wait_epoch(epoch, C.c_void_p(st.cuda_stream))
+        return self.bufs[epoch & 1]
+
+    def finish(self):
+        """Wait (stream-side) for the last epoch to be complete everywhere it lands here; returns its tensors."""
+        return self.gathered(self.epoch) if self.epoch else self.bufs[0]
+
+    def wait_failures(self):
+        return int(_P.vkr_peer_wait_failed())
+
+    def close(self, barrier=None):
+        self.bufs = None
+        self.slab.close(barrier)

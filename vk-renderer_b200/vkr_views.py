@@ -128,24 +128,63 @@ class ViewBatch:
             ps.append(view_params(dp, self.frame, self.counter, 0.0 if jitters is None else jitters[i]))
         return {k: vkr.params_array(type(ps[0][k]), [p[k] for p in ps]) for k in ps[0]}
 
-    def passes(self, P, flags=0, param_set=0):
+    def passes(self, P, flags=0, param_set=0, aux_stream=None, group_streams=None):
         """Hi-Z, SSSR trace/filter/blur, GTAO main/filter/accumulate for every view: 8 launches in total.
         flags: vkr.EXT_PREPARE_ONLY uploads the per-view parameter blocks of `param_set` without launching,
-        vkr.EXT_PARAMS_PREPARED launches on blocks prepared earlier (pure kernel launches: CUDA-graph capturable)."""
+        vkr.EXT_PARAMS_PREPARED launches on blocks prepared earlier (pure kernel launches: CUDA-graph capturable).
+        aux_stream: issue the SSR filter + blur on a second stream beside the three GTAO passes (both branches only need the
+        trace's outputs; the same split RenderGraph::submit derives for the chain), joined back before returning.  With a few
+        dozen views per launch every kernel is only a handful of waves, and the two branches fill each other's tails.
+        group_streams: [(main, aux), ...] — with EXT_PARAMS_PREPARED the views are split into len(group_streams) + 1 contiguous
+        layer ranges, each running the whole chain on its own pair of streams (the first range on self.stream / aux_stream):
+        views are independent, so the ranges fill each other's launch gaps and tails.  Everything joins self.stream at the end."""
         V, st = self.V, self.stream
-        ext = lambda imgs, slot: vkr.make_ext(imgs, layers=V, scratch=self._scratch(param_set * 7 + slot), flags=flags if V > 1 else 0)  # noqa: E731
-        vkr.hiz_build_ex(self.depth, self.normal, self.velocity, self.dn, self.dv, ext([self.depth, self.normal, self.velocity, self.dn, self.dv], 0), st)
-        vkr.sssr_trace_ex(P["trace"], self.depth, self.dn, self.material, self.halton, self.pdf, self.rays, self.raw,
-                          ext([self.depth, self.dn, self.material, self.pdf, self.rays, self.raw], 1), st)
-        vkr.sssr_filter_ex(P["trace"], self.rays, self.depth, self.albedo, self.normal, self.material, self.reflections,
-                           ext([self.rays, self.depth, self.albedo, self.normal, self.material, self.reflections], 2), st)
-        vkr.sssr_blur_ex(P["blur"], self.depth, self.normal, self.reflections, self.material, self.blurred_history, self.dv, self.prev_depth, self.blurred,
-                         ext([self.depth, self.normal, self.reflections, self.material, self.blurred_history, self.dv, self.prev_depth, self.blurred], 3), st)
-        vkr.gtao_main_ex(P["gtao"], self.depth, self.normal, self.material, self.pdf, self.raw,
-                         ext([self.depth, self.normal, self.material, self.pdf, self.raw], 4), 1, st)
-        vkr.gtao_filter_ex(P["gtao"], self.depth, self.raw, self.filtered, ext([self.depth, self.raw, self.filtered], 5), 1, st)
-        vkr.gtao_accumulate_ex(P["accum"], self.depth, self.prev_depth, self.filtered, self.accumulated_ao, self.dv, self.accumulated_history,
-                               ext([self.depth, self.prev_depth, self.filtered, self.accumulated_ao, self.dv, self.accumulated_history], 6), 1, st)
+        prepared = bool(flags & vkr.EXT_PARAMS_PREPARED) and V > 1
+        lanes = [(st, aux_stream)] + (list(group_streams) if (group_streams and prepared) else [])
+        G = len(lanes)
+        if G > 1 and V < 2 * G:
+            lanes, G = lanes[:1], 1
+        if G > 1:
+            ev0 = torch.cuda.Event()
+            ev0.record(st)
+        for g, (sm, sa) in enumerate(lanes):
+            first, count = (V * g) // G, (V * (g + 1)) // G - (V * g) // G
+            if g > 0:
+                sm.wait_event(ev0)
+
+            def R(a):                                          # the range's view of an array image (plain images are shared)
+                return vkr.LayerRange(a, first, count) if (G > 1 and isinstance(a, vkr.ImageArray)) else a
+
+            def ext(imgs, slot):
+                return vkr.make_ext(imgs, layers=count, scratch=self._scratch(param_set * 7 + slot), flags=flags if V > 1 else 0,
+                                    first_param=first if G > 1 else 0)
+
+            depth, normal, velocity, dn, dv, material, albedo = (R(x) for x in (self.depth, self.normal, self.velocity, self.dn, self.dv, self.material, self.albedo))
+            rays, raw, reflections, blurred, blurred_history = (R(x) for x in (self.rays, self.raw, self.reflections, self.blurred, self.blurred_history))
+            prev_depth, filtered, accumulated_ao, accumulated_history = (R(x) for x in (self.prev_depth, self.filtered, self.accumulated_ao, self.accumulated_history))
+            vkr.hiz_build_ex(depth, normal, velocity, dn, dv, ext([depth, normal, velocity, dn, dv], 0), sm)
+            vkr.sssr_trace_ex(P["trace"], depth, dn, material, self.halton, self.pdf, rays, raw, ext([depth, dn, material, self.pdf, rays, raw], 1), sm)
+            fork = sa is not None and not (flags & vkr.EXT_PREPARE_ONLY)
+            s2 = sa if fork else sm
+            if fork:
+                ev = torch.cuda.Event()
+                ev.record(sm)
+                s2.wait_event(ev)
+            vkr.sssr_filter_ex(P["trace"], rays, depth, albedo, normal, material, reflections, ext([rays, depth, albedo, normal, material, reflections], 2), s2)
+            vkr.sssr_blur_ex(P["blur"], depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred,
+                             ext([depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred], 3), s2)
+            vkr.gtao_main_ex(P["gtao"], depth, normal, material, self.pdf, raw, ext([depth, normal, material, self.pdf, raw], 4), 1, sm)
+            vkr.gtao_filter_ex(P["gtao"], depth, raw, filtered, ext([depth, raw, filtered], 5), 1, sm)
+            vkr.gtao_accumulate_ex(P["accum"], depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history,
+                                   ext([depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history], 6), 1, sm)
+            if fork:
+                ev2 = torch.cuda.Event()
+                ev2.record(s2)
+                sm.wait_event(ev2)
+            if g > 0:
+                evg = torch.cuda.Event()
+                evg.record(sm)
+                st.wait_event(evg)
 
     def end_frame(self):
         """The remaps of src/main.cpp:416-420 that concern these passes."""
