@@ -38,6 +38,11 @@ class PeerGather:
                 self.slab.open_peer(r, handles[r])
         self.epoch = 0
         self.xfer = torch.cuda.Stream(device=self.device)
+        # one stream per peer: copies to different peers run on different copy engines and NVLink paths at the same time
+        # (on ONE stream the 2 x (world - 1) copies serialise: 72 GB/s out of a rank at 8 GPUs, slower than the frame)
+        self.pstreams = {r: torch.cuda.Stream(device=self.device) for r in range(world) if r != rank}
+        self._go = torch.cuda.Event()
+        self._pdone = {r: torch.cuda.Event() for r in self.pstreams}
         self._ready = torch.cuda.Event()
         self._sent = [torch.cuda.Event(), torch.cuda.Event()]   # behind the copies of the last even / odd epoch
 
@@ -59,18 +64,24 @@ class PeerGather:
         if e > 1:
             self._wait_epoch(e - 1, st)            # every peer has finished with epoch e - 2, the last tenant of this buffer
         units = self.end - self.first
-        for t, (blk, rb) in enumerate(zip(blocks, self.row_bytes)):
-            assert blk.shape[0] == units and blk.shape[1] >= rb and blk.stride(1) == 1
-            src, pitch = blk.data_ptr(), blk.stride(0)
-            own = self.bufs[e & 1][t]
-            for r in range(self.world):
-                base = self.slab.ptr if r == self.rank else self.slab.peers[r]
-                dst = base + (own.data_ptr() - self.slab.ptr) + self.first * rb
-                vkr.check(_P.vkr_peer_push_2d(C.c_void_p(src), pitch, C.c_void_p(dst), rb, rb, units, st))
-        self._sent[e & 1].record(self.xfer)
+        self._go.record(self.xfer)
         for r in range(self.world):
+            if r == self.rank:
+                s, sp, base = self.xfer, st, self.slab.ptr
+            else:
+                s, base = self.pstreams[r], self.slab.peers[r]
+                s.wait_event(self._go)
+                sp = C.c_void_p(s.cuda_stream)
+            for t, (blk, rb) in enumerate(zip(blocks, self.row_bytes)):
+                assert blk.shape[0] == units and blk.shape[1] >= rb and blk.stride(1) == 1
+                dst = base + (self.bufs[e & 1][t].data_ptr() - self.slab.ptr) + self.first * rb
+                vkr.check(_P.vkr_peer_push_2d(C.c_void_p(blk.data_ptr()), blk.stride(0), C.c_void_p(dst), rb, rb, units, sp))
             if r != self.rank:
-                vkr.check(_P.vkr_peer_signal(C.c_void_p(self._flag(self.slab.peers[r], self.rank)), e, st))
+                self._pdone[r].record(s)
+                vkr.check(_P.vkr_peer_signal(C.c_void_p(self._flag(base, self.rank)), e, sp))
+        for r in self.pstreams:
+            self.xfer.wait_event(self._pdone[r])
+        self._sent[e & 1].record(self.xfer)
         return e
 
     def sources_free(self, stream, epoch=None):
@@ -100,5 +111,7 @@ class PeerGather:
         return int(_P.vkr_peer_wait_failed())
 
     def close(self, barrier=None):
+        for s in list(self.pstreams.values()) + [self.xfer]:
+            s.synchronize()
         self.bufs = None
         self.slab.close(barrier)
