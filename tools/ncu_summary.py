@@ -1,6 +1,6 @@
 """Summarise an `ncu --set full` report of the chain into profiles/<name>_summary.json and refresh profiles/traffic.json.
 
-  python tools/ncu_summary.py gpurun_out/r01e_full.ncu-rep profiles/r01e_ncu_full_4k_summary.json "<cmd>" "<note>" [3840x2160]
+  python tools/ncu_summary.py gpurun_out/r01e_full.ncu-rep profiles/r01e_ncu_full_4k_summary.json "<cmd>" "<note>" [3840x2160] [notraffic]
 
 One entry per kernel (first launch of each name in the report): duration, DRAM bytes, cache hit rates, issue-active,
 pipe utilisation, achieved occupancy, registers, executed warp instructions.
@@ -62,12 +62,13 @@ for r in rows[2:]:
             traffic[task] = traffic.get(task, 0.0) + (rd + wr) * 1e6       # hiz: tile kernel only (the tail kernel adds ~12 KB)
             winst[task] = winst.get(task, 0.0) + (kernels[-1]["warp_inst"] or 0.0)
 json.dump({"cmd": cmd, "size": size, "note": note, "kernels": kernels}, open(out, "w"), indent=1)
-tpath = os.path.join(os.path.dirname(out), "traffic.json")
-tj = json.load(open(tpath)) if os.path.exists(tpath) else {}
-tj[size] = traffic
-tj[size + ":warp_inst"] = winst                 # executed warp instructions per launch (smsp__inst_executed.sum)
-tj["source"] = f"{out} (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
-json.dump(tj, open(tpath, "w"), indent=1)
+if not (len(sys.argv) > 6 and sys.argv[6] == "notraffic"):     # a report of kernels outside the chain leaves traffic.json alone
+    tpath = os.path.join(os.path.dirname(out), "traffic.json")
+    tj = json.load(open(tpath)) if os.path.exists(tpath) else {}
+    tj[size] = traffic
+    tj[size + ":warp_inst"] = winst                 # executed warp instructions per launch (smsp__inst_executed.sum)
+    tj["source"] = f"{out} (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
+    json.dump(tj, open(tpath, "w"), indent=1)
 for kk in kernels:
     print(f"{kk['kernel'][:44]:44s} {kk['time_us']:8.1f} us  issue {kk['issue_active_pct']:5.1f}%  fma {kk['pipe_fma_cycles_pct']:5.1f}%  warps {kk['warps_active_pct']:5.1f}%  "
           f"regs {kk['regs']:.0f}  dram {kk['dram_read_MB'] + kk['dram_write_MB']:7.1f} MB  inst {kk['warp_inst'] / 1e6:7.1f}M")
