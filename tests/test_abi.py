@@ -88,3 +88,41 @@ int main(void) {
     subprocess.run(["gcc", "-O2", "-mfma", "-ffp-contract=off", "-o", str(exe), str(src), "-lm"], check=True)
     r = subprocess.run([str(exe)], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.strip() == "0", r.stdout
+
+
+def test_new_entries_validate_arguments_before_touching_the_device():
+    """The tile-path and capture entries reject bad arguments with VKR_ERR_INVALID_ARGUMENT / VKR_ERR_UNSUPPORTED and a message,
+    on a machine without a GPU too (validation comes before any CUDA call)."""
+    import vkr
+    L = vkr.lib
+    L.vkr_last_error.restype = C.c_char_p
+    mat = vkr.Image(64, 64, vkr.R8G8B8A8_SRGB, device="cpu")
+    wrong = vkr.Image(64, 64, vkr.R8G8B8A8_UNORM, device="cpu")
+    buf = (C.c_int32 * 64)()
+    ind = (C.c_uint32 * 3)()
+    p = vkr.ClassifyParams(32, 32, 1.0, 0.5)
+    assert L.vkr_sssr_clear_indirect(None, ind, None) == -1
+    assert L.vkr_sssr_classification(C.byref(p), wrong.ptr, buf, buf, ind, ind, None) == -1      # material must be RGBA8_SRGB
+    assert b"sssr_classification" in L.vkr_last_error()
+    assert L.vkr_sssr_classification(C.byref(vkr.ClassifyParams(0, 32, 1.0, 0.5)), mat.ptr, buf, buf, ind, ind, None) == -1
+    tp = vkr.TraceParams()
+    d = vkr.Image(64, 64, vkr.D24_UNORM_S8_UINT, 7, device="cpu")
+    dn = vkr.Image(32, 32, vkr.R16G16_UNORM, device="cpu")
+    rays = vkr.Image(32, 32, vkr.R16G16B16A16_UNORM, device="cpu")
+    assert L.vkr_sssr_trace_indirect(C.byref(tp), 2, d.ptr, dn.ptr, mat.ptr, buf, buf, ind, 16, rays.ptr, None) == -1   # reflection_type > 1
+    assert L.vkr_sssr_trace_indirect(C.byref(tp), 0, d.ptr, dn.ptr, mat.ptr, buf, buf, ind, 0, rays.ptr, None) == 0     # empty list capacity: no-op
+    planes = vkr.Image(4, 4, vkr.R32G32B32A32_SFLOAT, device="cpu")
+    assert L.vkr_sssr_tile_regression(None, d.ptr, planes.ptr, None) == -1
+    assert L.vkr_sssr_tile_regression(C.byref(vkr.RegressionParams()), d.ptr, rays.ptr, None) == -1                    # planes must be RGBA32F
+    assert L.vkr_blit_image(d.ptr, mat.ptr, None) == -4                                                                  # depth is not a blit source
+    assert L.vkr_blit_image(None, mat.ptr, None) == -1
+    out = (C.c_uint8 * (64 * 64 * 8))()
+    assert L.vkr_readback_pack(mat.ptr, 1, 0, out, None) == -1                                                           # mip out of range
+    assert L.vkr_readback_pack(mat.ptr, 0, 3, out, None) == -1                                                           # unknown mode
+    assert L.vkr_readback_pack(rays.ptr, 0, 1, out, None) == -4                                                          # fix-up modes need 4-byte texels
+    e = vkr.LaunchExt()
+    e.first_param = 3                                                                                                    # needs layers > 1 + PARAMS_PREPARED
+    raw = vkr.Image(32, 32, vkr.R16G16B16A16_SFLOAT, device="cpu")
+    filt = vkr.Image(32, 32, vkr.R16_SFLOAT, device="cpu")
+    assert L.vkr_gtao_filter_ex(C.byref(vkr.GtaoParams()), d.ptr, raw.ptr, filt.ptr, 1, C.byref(e), None) == -1
+    assert b"first_param" in L.vkr_last_error()
