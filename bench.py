@@ -89,7 +89,7 @@ class ClockSampler(threading.Thread):
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.002)
+                time.sleep(0.005)       # NVML queries take driver locks the launch path also wants: sample sparsely
         except Exception as e:  # NVML missing: report that instead of inventing numbers
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
