@@ -59,6 +59,26 @@ __device__ __forceinline__ f3 sampleGGXVNDF(f3 Ve, float alpha_x, float alpha_y,
   return norm3(mk3(FM(alpha_x, Nh.x), FM(alpha_y, Nh.y), gmax(0.0f, Nh.z)));
 }
 
+
+// value-only restatement of sampleGGXVNDF (FMA contraction, single-MUFU rsqrt / sqrt; sin / cos stay the accurate forms:
+// the direction they produce steers an up to 80-cell march)
+__device__ __forceinline__ f3 sampleGGXVNDF_fast(f3 Ve, float alpha_x, float alpha_y, float U1, float U2) {
+  f3 Vh = norm3f(mk3(alpha_x * Ve.x, alpha_y * Ve.y, Ve.z));
+  float lensq = fmaf(Vh.x, Vh.x, Vh.y * Vh.y);
+  float il = rsqrt_fast(lensq);
+  f3 T1 = lensq > 0 ? mk3(-Vh.y * il, Vh.x * il, 0) : mk3(1, 0, 0);
+  f3 T2 = mk3(Vh.y * T1.z - T1.y * Vh.z, Vh.z * T1.x - T1.z * Vh.x, Vh.x * T1.y - T1.x * Vh.y);
+  float r = sqrt_fast(U1);
+  float sp, cp;
+  sincosf(FM(2.0f * VKR_PI, U2), &sp, &cp);
+  float t1 = r * cp, t2 = r * sp;
+  float s = 0.5f * (1.0f + Vh.z);
+  t2 = fmaf(1.0f - s, sqrt_fast(fmaf(-t1, t1, 1.0f)), s * t2);
+  float nz = sqrt_fast(fmaxf(0.0f, fmaf(-t2, t2, fmaf(-t1, t1, 1.0f))));
+  f3 Nh = mk3(fmaf(t1, T1.x, fmaf(t2, T2.x, nz * Vh.x)), fmaf(t1, T1.y, fmaf(t2, T2.y, nz * Vh.y)), fmaf(t1, T1.z, fmaf(t2, T2.z, nz * Vh.z)));
+  return norm3f(mk3(alpha_x * Nh.x, alpha_y * Nh.y, fmaxf(0.0f, Nh.z)));
+}
+
 // trace.comp:143-154 == gtao/main.comp:69-80
 __device__ __forceinline__ f3 get_tangent(f3 n) {
   float max_xy = gmax(fabsf(n.x), fabsf(n.y));

@@ -348,6 +348,15 @@ __device__ __forceinline__ f3 reconstruct_fast(float u, float v, float d, const 
   float z = linearize_fast(d, c);
   return mk3((1.0f - 2.f * u) * (z * c.aspect_tg), (1.0f - 2.f * v) * (z * c.tg), z);
 }
+// project_view_vec with MUFU reciprocals (value-only); the camera-only quotients are uniform
+__device__ __forceinline__ f3 project_fast(f3 v, const CamK& c) {
+  const float fmn = c.zfar - c.znear;
+  const float A = c.zfar / fmn, B = c.zfar * c.znear / fmn;
+  const float rz = rcp_fast(v.z);
+  const float itg = rcp_fast(c.tg);
+  const float pu = -v.x * rz * (itg * rcp_fast(c.aspect)), pv = -v.y * rz * itg;
+  return mk3(fmaf(0.5f, pu, 0.5f), fmaf(0.5f, pv, 0.5f), fmaf(B, rz, A));
+}
 __device__ __forceinline__ f3 decode_normal_fast(float u, float v) {
   u = fmaf(2.f, u, -1.f); v = fmaf(2.f, v, -1.f);
   f3 n = mk3(u, v, 1.0f - fabsf(u) - fabsf(v));

@@ -13,6 +13,9 @@
 #ifndef TRACE_UNROLL_A
 #define TRACE_UNROLL_A 1
 #endif
+#ifndef TRACE_V2
+#define TRACE_V2 0   /* 1 = the re-stated march below; default flips once its GPU parity run is committed */
+#endif
 namespace vkr {
 
 struct TraceK {
@@ -181,6 +184,301 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 }
 
 }  // namespace vkr
+
+// ================================================================================================
+// Version 2 of the march (default, TRACE_V2=1).  Same algorithm, re-stated for the sm_100a issue pipes:
+//  * the cell index of a level-m step comes out of ONE FFMA with round-down:
+//      cell * 2^m = RD(W * x + 1.5 * 2^(23+m)) - 1.5 * 2^(23+m)
+//    (the magic constant makes the unit in the last place 2^m, so rounding down IS the floor; the integer index is the
+//    difference of the two bit patterns).  No FRND / F2I on the quarter-rate conversion pipe and no per-level resolution
+//    registers: the level is carried by the magic constant alone (level +-1 = exponent +-1).
+//  * the ray is parameterised by t only; x, y, z and the horizon's (1 - 2u) * aspect * tan terms are FFMAs of t.
+//  * the level table {base, pitch, extent} lives in shared memory instead of lane-indexed constant loads.
+//  * the fast loops run while the ray is inside the screen minus 2^-20; leaving it (at most once per ray) falls into a
+//    slow tail that restates the shader's out-of-range / truncation behaviour literally (texelFetch at trunc(), App. A.3).
+// Precision policy: the step arithmetic is contracted (<= 1 rounding per uv instead of 2), the cell
+// index is the floor of the exactly rounded-down product.  The depth fed to the horizon keeps the oracle's bits (exact
+// D24 decode, unfused d*(f-n) - f: that difference is ill-conditioned, see linearize_fast).
+// TRACE_FAST_SETUP=1 also evaluates the ray set-up and the occlusion epilogue with FMA contraction and single-MUFU
+// reciprocals / square roots; the Halton hash stays bit-defined.
+#ifndef TRACE_FAST_SETUP
+#define TRACE_FAST_SETUP 1
+#endif
+#ifndef TRACE_MIN_CTAS
+#define TRACE_MIN_CTAS 1
+#endif
+namespace vkr {
+
+#define TR_MAGIC0 12582912.0f          /* 1.5 * 2^23 */
+#define TR_MAGIC0_BITS 0x4B400000
+
+struct RayK {                          // per-ray constants of the march
+  float ox, oy, oz, dx, dy, dz;        // origin, direction (uv, depth)
+  float idx, idy, idz;                 // 1 / direction (MAX_T for 0)
+  float fox, foy;                      // floor offsets (0 or 1)
+  float cx, cy;                        // uv_offset - origin
+  float t_exit;                        // the fast loops are valid while t < t_exit
+};
+
+struct HorK {                          // horizon sample: v = reconstruct(uv(t), z) - view_vec
+  float a1, a0, b1, b0;                // (1 - 2u) * aspect * tg = a1 * t + a0 ; (1 - 2v) * tg = b1 * t + b0
+  f3 vv, n;
+};
+
+__device__ __forceinline__ void horizon_sample(const HorK& H, const CamF& camf, float t, float sz, float& h) {
+  const float z = linearize_fast(sz, camf);
+  const float vx = fmaf(fmaf(t, H.a1, H.a0), z, -H.vv.x), vy = fmaf(fmaf(t, H.b1, H.b0), z, -H.vv.y), vz = z - H.vv.z;
+  const float d2 = fmaf(vz, vz, fmaf(vy, vy, vx * vx));
+  if (d2 < 0.09f) h = fmaxf(h, fmaf(H.n.z, vz, fmaf(H.n.y, vy, H.n.x * vx)) * rsqrt_fast(d2));
+}
+
+// one step on level m (magic = 1.5 * 2^(23+m)); returns above_surface
+template <bool PINNED>
+__device__ __forceinline__ bool fast_step(const RayK& r, const uint4* __restrict__ lvl, float ssx, float ssy, float rinvx0, float rinvy0, float magic,
+                                          float& t, bool& skipped, float& sz_out) {
+  const float px = fmaf(t, r.dx, r.ox), py = fmaf(t, r.dy, r.oy);
+  const float mx = __fmaf_rd(ssx, px, magic), my = __fmaf_rd(ssy, py, magic);
+  const int mb = __float_as_int(magic);
+  const int xi = __float_as_int(mx) - mb, yi = __float_as_int(my) - mb;            // cell index on this level (>= 0 inside the screen)
+  const uint4 L = PINNED ? lvl[0] : lvl[(mb >> 23) - 150];
+  const uint32_t* base = (const uint32_t*)(((unsigned long long)L.y << 32) | L.x);
+  float sz = 0.0f;
+  if (PINNED || ((unsigned)xi < (L.w & 0xFFFFu) && (unsigned)yi < (L.w >> 16))) {  // level 0: res is the integer extent, inside the screen = inside the level
+    const uint32_t texel = (uint32_t)yi * L.z + (uint32_t)xi;                        // 32-bit index, widened once
+    sz = d24_to_float(__ldg(base + texel));
+  }
+  const float p2 = PINNED ? 1.0f : __int_as_float(mb - (TR_MAGIC0_BITS - 0x3F800000));   // 2^m
+  const float ex = fmaf(fmaf(p2, r.fox, mx - magic), rinvx0, r.cx), ey = fmaf(fmaf(p2, r.foy, my - magic), rinvy0, r.cy);   // xy_plane - origin
+  const float tx = ex * r.idx, ty = ey * r.idy;
+  float tz = (sz - r.oz) * r.idz;
+  tz = r.dz > 0 ? tz : MAX_T_FLOAT;
+  const float t_min = fminf(fminf(tx, ty), tz);
+  const bool above = sz > fmaf(t, r.dz, r.oz);
+  skipped = above && (t_min != tz);
+  t = above ? t_min : t;
+  sz_out = sz;
+  return above;
+}
+
+template <bool LAYERED>
+__global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
+                                                          const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
+  __shared__ uint4 lvl[16];
+  TraceK kl;
+  unsigned long long poff = 0;
+  if (LAYERED) {
+    const int z = blockIdx.z;
+    kl = kv[z];
+    poff = (unsigned long long)z * P.mip[0].ls;
+    normal = layer_of(normal, z); material = layer_of(material, z); pdf = layer_of(pdf, z); out_rays = layer_of(out_rays, z); out_occl = layer_of(out_occl, z);
+  }
+  const TraceK& k = LAYERED ? kl : k0;
+  if (threadIdx.x < 16) {
+    const int m = threadIdx.x;
+    uint4 e = make_uint4(0u, 0u, 0u, 0u);                   // levels past the view: extent 0 -> texelFetch returns 0
+    if (m < P.count) {
+      const unsigned long long b = (unsigned long long)(P.mip[m].p + poff);
+      e = make_uint4((uint32_t)b, (uint32_t)(b >> 32), P.mip[m].pitch >> 2, (uint32_t)P.mip[m].w | ((uint32_t)P.mip[m].h << 16));
+    }
+    lvl[m] = e;
+  }
+  __syncthreads();
+  const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 4);
+  if (px >= out_rays.w || py >= out_rays.h) return;
+  const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
+  const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
+  const CamK cam = k.cam;
+  const CamF camf = make_camf(cam);
+
+  float roughness = sample_srgb8(material, su, sv, srgb).y;                                     // :49-53
+  float mg = gmix(0.0f, k.max_roughness, roughness);
+  roughness = FM(mg, mg);
+
+  Mip d0 = P.mip[0];
+  d0.p += poff;
+  const float pixel_depth = sample_d24(d0, su, sv);
+  const uint32_t base_index = (uint32_t)(rand_hash(su, sv) * 128.0f);                           // :61-63
+  const uint32_t index = (base_index + k.frame_random) & 127u;
+  const float4 hv = __ldg(halton + index);
+  f3 pixel_normal, w0, R, origin, direction;
+  const f3 view_vec = reconstruct_view_vec(su, sv, pixel_depth, cam);                           // exact: one side of the oracle-bit horizon difference
+#if TRACE_FAST_SETUP
+  {
+    pixel_normal = norm3f(mul_m3f(k.normal_mat, sample_gbuffer_normal_fast(normal, su, sv)));
+    f3 tangent = get_tangent(pixel_normal);
+    f3 bitangent = norm3f(cross3(pixel_normal, tangent));
+    tangent = norm3f(cross3(bitangent, pixel_normal));
+    w0 = -norm3f(view_vec);
+    f3 view_dir = mk3(dot3f(w0, tangent), dot3f(w0, bitangent), dot3f(w0, pixel_normal));
+    f3 brdf_norm = sampleGGXVNDF_fast(view_dir, roughness, roughness, hv.x, hv.y);
+    f3 N = mk3(fmaf(brdf_norm.x, tangent.x, fmaf(brdf_norm.y, bitangent.x, brdf_norm.z * pixel_normal.x)),
+               fmaf(brdf_norm.x, tangent.y, fmaf(brdf_norm.y, bitangent.y, brdf_norm.z * pixel_normal.y)),
+               fmaf(brdf_norm.x, tangent.z, fmaf(brdf_norm.y, bitangent.z, brdf_norm.z * pixel_normal.z)));
+    const float two_ndi = 2.0f * dot3f(N, view_vec);
+    R = mk3(fmaf(-two_ndi, N.x, view_vec.x), fmaf(-two_ndi, N.y, view_vec.y), fmaf(-two_ndi, N.z, view_vec.z));
+    origin = project_fast(mk3(fmaf(0.001f, pixel_normal.x, view_vec.x), fmaf(0.001f, pixel_normal.y, view_vec.y), fmaf(0.001f, pixel_normal.z, view_vec.z)), cam);
+    origin.z -= 0.0001f;
+    f3 e = project_fast(mk3(view_vec.x + R.x, view_vec.y + R.y, view_vec.z + R.z), cam);
+    direction = mk3(e.x - origin.x, e.y - origin.y, e.z - origin.z);
+    const float s = (1.0f - origin.z) * rcp_fast(direction.z);
+    direction = mk3(direction.x * s, direction.y * s, direction.z * s);
+  }
+#else
+  {
+    pixel_normal = norm3(mul_m4(k.normal_mat, sample_gbuffer_normal(normal, su, sv), 0.f));
+    f3 tangent = get_tangent(pixel_normal);
+    f3 bitangent = norm3(cross3(pixel_normal, tangent));
+    tangent = norm3(cross3(bitangent, pixel_normal));
+    w0 = -norm3(view_vec);
+    f3 view_dir = mk3(dot3(w0, tangent), dot3(w0, bitangent), dot3(w0, pixel_normal));
+    f3 brdf_norm = sampleGGXVNDF(view_dir, roughness, roughness, hv.x, hv.y);
+    f3 N = brdf_norm.x * tangent + brdf_norm.y * bitangent + brdf_norm.z * pixel_normal;
+    R = reflect3(view_vec, N);
+    origin = project_view_vec(view_vec + 0.001f * pixel_normal, cam);                            // :79-84
+    origin.z = FS(origin.z, 0.0001f);
+    direction = project_view_vec(view_vec + R, cam) - origin;
+    direction = direction * (FS(1.f, origin.z) / direction.z);
+  }
+#endif
+  // ---- hierarchical_raymarch_find_hor, trace.comp:206-268 ------------------------------------
+  const float ssx = (float)d0.w, ssy = (float)d0.h;
+  const float rinvx0 = 1.0f / ssx, rinvy0 = 1.0f / ssy;
+  RayK r;
+  r.ox = origin.x; r.oy = origin.y; r.oz = origin.z; r.dx = direction.x; r.dy = direction.y; r.dz = direction.z;
+#if TRACE_FAST_SETUP
+  r.idx = direction.x != 0 ? rcp_fast(direction.x) : MAX_T_FLOAT; r.idy = direction.y != 0 ? rcp_fast(direction.y) : MAX_T_FLOAT;
+  r.idz = direction.z != 0 ? rcp_fast(direction.z) : MAX_T_FLOAT;
+#else
+  r.idx = direction.x != 0 ? 1.0f / direction.x : MAX_T_FLOAT; r.idy = direction.y != 0 ? 1.0f / direction.y : MAX_T_FLOAT;
+  r.idz = direction.z != 0 ? 1.0f / direction.z : MAX_T_FLOAT;
+#endif
+  const float uox = direction.x < 0 ? -(0.005f / ssx) : (0.005f / ssx), uoy = direction.y < 0 ? -(0.005f / ssy) : (0.005f / ssy);
+  r.fox = direction.x < 0 ? 0.f : 1.f; r.foy = direction.y < 0 ? 0.f : 1.f;
+  r.cx = uox - origin.x; r.cy = uoy - origin.y;
+  {                                                    // the ray stays inside [2^-20, 1 - 2^-20]^2 while t < t_exit
+    const float eps = 9.5367431640625e-07f;
+    const float bx = direction.x < 0 ? eps : 1.0f - eps, by = direction.y < 0 ? eps : 1.0f - eps;
+    const float ex = direction.x != 0 ? (bx - origin.x) * r.idx : MAX_T_FLOAT, ey = direction.y != 0 ? (by - origin.y) * r.idy : MAX_T_FLOAT;
+    r.t_exit = fminf(ex, ey);
+    const bool inside = origin.x > eps && origin.x < 1.0f - eps && origin.y > eps && origin.y < 1.0f - eps;
+    if (!inside) r.t_exit = -1.0f;
+  }
+  HorK H;
+  H.a1 = -2.0f * direction.x * camf.aspect_tg; H.a0 = (1.0f - 2.0f * origin.x) * camf.aspect_tg;
+  H.b1 = -2.0f * direction.y * camf.tg; H.b0 = (1.0f - 2.0f * origin.y) * camf.tg;
+  H.vv = view_vec; H.n = pixel_normal;
+
+  float t;
+  {                                                    // initial_advance_ray, screen_trace.glsl:8-15
+    const float ex = fmaf(floorf(ssx * origin.x) + r.fox, rinvx0, r.cx), ey = fmaf(floorf(ssy * origin.y) + r.foy, rinvy0, r.cy);
+    t = fminf(ex * r.idx, ey * r.idy);
+  }
+  float h = 0.f;
+  int i = 0;
+  int mip = 0;
+  // Steps 0..14 stay on level 0 (:250).  A ray found below the surface there never moves again (t frozen, the same
+  // horizon sample every step) and leaves the march at step 15: it is finished.
+  bool done = false;
+  for (; i < 15 && t < r.t_exit; ++i) {
+    bool skipped; float sz;
+    const bool above = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, t, skipped, sz);
+    horizon_sample(H, camf, t, sz, h);
+    if (!above) { done = true; break; }
+  }
+  if (!done && i >= 15) {
+    float magic = TR_MAGIC0;
+    while (i < 80 && magic >= TR_MAGIC0 && t < r.t_exit) {
+      bool skipped; float sz;
+      fast_step<false>(r, lvl, ssx, ssy, rinvx0, rinvy0, magic, t, skipped, sz);
+      magic = __int_as_float(__float_as_int(magic) + (skipped ? 0x00800000 : -0x00800000));
+      ++i;
+      if (magic <= 2.0f * TR_MAGIC0) horizon_sample(H, camf, t, sz, h);
+    }
+    mip = (__float_as_int(magic) >> 23) - 150;
+  }
+  // Slow tail: the ray is at the screen border or outside.  Literal texelFetch semantics: index = trunc(res * uv) (so the
+  // strip (-1, 0) still reads cell 0), out of range = 0; floor() for the plane (screen_trace.glsl:19).
+  while (!done && i < 80 && mip >= 0) {
+    const float S = __int_as_float((127 + mip) << 23), s = __int_as_float((127 - mip) << 23);   // 2^mip, 2^-mip
+    const float pxx = fmaf(t, r.dx, r.ox), pyy = fmaf(t, r.dy, r.oy);
+    const float mpx = (ssx * s) * pxx, mpy = (ssy * s) * pyy;
+    const int xi = (int)mpx, yi = (int)mpy;
+    const uint4 L = lvl[min(mip, 15)];
+    float sz = 0.0f;
+    if ((unsigned)xi < (L.w & 0xFFFFu) && (unsigned)yi < (L.w >> 16))
+      sz = d24_to_float(__ldg((const uint32_t*)(((unsigned long long)L.y << 32) | L.x) + ((uint32_t)yi * L.z + (uint32_t)xi)));
+    const float ex = fmaf((floorf(mpx) + r.fox) * S, rinvx0, r.cx), ey = fmaf((floorf(mpy) + r.foy) * S, rinvy0, r.cy);
+    const float tx = ex * r.idx, ty = ey * r.idy;
+    float tz = (sz - r.oz) * r.idz;
+    tz = r.dz > 0 ? tz : MAX_T_FLOAT;
+    const float t_min = fminf(fminf(tx, ty), tz);
+    const bool above = sz > fmaf(t, r.dz, r.oz);
+    const bool skipped = above && (t_min != tz);
+    t = above ? t_min : t;
+    if (i >= 15) mip += skipped ? 1 : -1;
+    ++i;
+    if (mip <= 1) horizon_sample(H, camf, t, sz, h);
+  }
+  const f3 out_ray = mk3(fmaf(t, r.dx, r.ox), fmaf(t, r.dy, r.oy), fmaf(t, r.dz, r.oz));
+  bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
+
+  {                                                                                              // :94-99
+    float sx = fabsf(out_ray.x - origin.x) * tsx, sy = fabsf(out_ray.y - origin.y) * tsy;
+    if (fmaxf(sx, sy) < 2.0f) valid_hit = false;
+  }
+  if (valid_hit) {                                                                               // :101-109
+#if TRACE_FAST_SETUP
+    f3 hit_normal = mul_m3f(k.normal_mat, sample_gbuffer_normal_fast(normal, out_ray.x, out_ray.y));
+    if (dot3f(hit_normal, R) > 0 || dot3f(pixel_normal, R) < 0) valid_hit = false;
+#else
+    f3 hit_normal = mul_m4(k.normal_mat, sample_gbuffer_normal(normal, out_ray.x, out_ray.y), 0.f);
+    if (dot3(hit_normal, R) > 0 || dot3(pixel_normal, R) < 0) valid_hit = false;
+#endif
+  }
+  if (valid_hit) {                                                                               // :111-118
+    float hit_depth = sample_d24(d0, out_ray.x, out_ray.y);
+    float hit_z = linearize_fast(hit_depth, camf);
+    float ray_z = linearize_fast(out_ray.z, camf);
+    if (ray_z > hit_z + 0.3f || ray_z < hit_z - 0.1f) valid_hit = false;
+  }
+  {                                                                                              // :120-121, RGBA16_UNORM
+    uint32_t lo = to_unorm(out_ray.x, 65535.f) | (to_unorm(out_ray.y, 65535.f) << 16);
+    uint32_t hi = to_unorm(out_ray.z, 65535.f) | (to_unorm(valid_hit ? pixel_depth : 1.0f, 65535.f) << 16);
+    *((uint2*)(out_rays.p + (size_t)py * out_rays.pitch) + px) = make_uint2(lo, hi);
+  }
+  {                                                                                              // :123-139, value-only
+#if TRACE_FAST_SETUP
+    f3 slice_normal = norm3f(cross3(w0, R));
+    const float pn = dot3f(pixel_normal, slice_normal);
+    f3 normal_projected = mk3(fmaf(-pn, slice_normal.x, pixel_normal.x), fmaf(-pn, slice_normal.y, pixel_normal.y), fmaf(-pn, slice_normal.z, pixel_normal.z));
+    f3 X = norm3f(cross3(slice_normal, w0));
+    const float np2 = dot3f(normal_projected, normal_projected);
+    const float rnp = rsqrt_fast(np2);
+    float n = VKR_PI / 2.0f - acosf(dot3f(normal_projected, X) * rnp);
+    float hh = acosf(h);
+    hh = gmin(n + gmin(hh - n, VKR_PI / 2.0f), hh);
+    float pdfv = sampleGGXdirPDF(pdf, w0, pixel_normal, R, roughness);
+    float occlusion = ((1.0f / VKR_PI) * 0.25f) * (np2 * rnp) * gmax(-__cosf(2.f * hh - n) + __cosf(n) + 2.f * hh * __sinf(n), 0.f);
+#else
+    f3 slice_normal = norm3(cross3(w0, R));
+    f3 normal_projected = pixel_normal - dot3(pixel_normal, slice_normal) * slice_normal;
+    f3 X = norm3(cross3(slice_normal, w0));
+    float n = FS(VKR_PI / 2.0f, acosf(dot3(norm3(normal_projected), X)));
+    float hh = acosf(h);
+    hh = gmin(FA(n, gmin(FS(hh, n), VKR_PI / 2.0f)), hh);
+    float pdfv = sampleGGXdirPDF(pdf, w0, pixel_normal, R, roughness);
+    float occlusion = FM(FM(FM(1.0f / VKR_PI, len3(normal_projected)), 0.25f), gmax(FA(FA(-cosf(FS(FM(2.f, hh), n)), cosf(n)), FM(FM(2.f, hh), sinf(n))), 0.f));
+#endif
+    float result = isnan(occlusion) ? 0.0f : occlusion;
+#ifdef VKR_TRACE_STATS
+    *((uint2*)(out_occl.p + (size_t)py * out_occl.pitch) + px) = make_uint2(pack_half2(result, pdfv), pack_half2((float)i, (float)(done ? -1 : mip)));
+#else
+    *((uint2*)(out_occl.p + (size_t)py * out_occl.pitch) + px) = make_uint2(pack_half2(result, pdfv), 0u);
+#endif
+  }
+}
+
+}  // namespace vkr
 using namespace vkr;
 
 static TraceK make_trace_k(const VkrTraceParams* p) {
@@ -225,7 +523,11 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
   const float* srgb = srgb_decode_table_device();
   if (!srgb) { set_error("sssr_trace: sRGB table upload failed"); return VKR_ERR_CUDA; }
   dim3 grid((out_rays->width + 15) / 16, x.yblocks, x.layers);
+#if TRACE_V2
+  auto kern = kv ? sssr_trace2_kernel<true> : sssr_trace2_kernel<false>;
+#else
   auto kern = kv ? sssr_trace_kernel<true> : sssr_trace_kernel<false>;
+#endif
   kern<<<grid, 128, 0, st>>>(k, kv, LaunchX{x.yb0}, P, make_mip(dnormal, 0, x, 1), make_mip(material, 0, x, 2), (const float4*)halton_vec4x128,
                              make_mip(pdf_lut, 0, x, 3), make_mip(out_rays, 0, x, 4), make_mip(out_occlusion, 0, x, 5), srgb);
   return check_launch("sssr_trace_kernel");
