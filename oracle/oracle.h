@@ -205,6 +205,12 @@ float orc_probe_half_roundtrip(float v);
 float orc_probe_srgb_decode(uint32_t code);
 float orc_probe_srgb_encode(float linear);
 
+/* G-buffer producer conventions (passes_gbuf.cpp): the jitter table of reference src/main.cpp:93-108 and the vertex /
+ * fragment arithmetic of shaders/gbuf/opaque_taa.vert:37-43, opaque_taa.frag:45 for one world-space point. */
+void orc_taa_offset(uint32_t index, uint32_t w, uint32_t h, float* out_jitter4);
+void orc_gbuf_point(const float* view_projection16, const float* prev_view_projection16, const float* jitter4,
+                    const float* world_pos3, float* out_position4, float* out_velocity2);
+
 #ifdef __cplusplus
 }
 #endif

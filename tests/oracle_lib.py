@@ -79,6 +79,8 @@ _sig("orc_probe_project", FP, FP, FP, restype=None)
 _sig("orc_probe_half_roundtrip", C.c_float, restype=C.c_float)
 _sig("orc_probe_srgb_decode", U, restype=C.c_float)
 _sig("orc_probe_srgb_encode", C.c_float, restype=C.c_float)
+_sig("orc_taa_offset", U, U, U, FP, restype=None)
+_sig("orc_gbuf_point", FP, FP, FP, FP, FP, FP, restype=None)
 
 
 def fptr(a):
