@@ -207,6 +207,9 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 #ifndef TRACE_MIN_CTAS
 #define TRACE_MIN_CTAS 1
 #endif
+#ifndef TRACE_CTA_ROWS
+#define TRACE_CTA_ROWS 8                /* 16 x TRACE_CTA_ROWS rays per CTA (one 16 x 2 strip per warp) */
+#endif
 namespace vkr {
 
 #define TR_MAGIC0 12582912.0f          /* 1.5 * 2^23 */
@@ -220,23 +223,23 @@ struct RayK {                          // per-ray constants of the march
   float t_exit;                        // the fast loops are valid while t < t_exit
 };
 
-struct HorK {                          // horizon sample: v = reconstruct(uv(t), z) - view_vec
-  float a1, a0, b1, b0;                // (1 - 2u) * aspect * tg = a1 * t + a0 ; (1 - 2v) * tg = b1 * t + b0
-  f3 vv, n;
-};
-
-__device__ __forceinline__ void horizon_sample(const HorK& H, const CamF& camf, float t, float sz, float& h) {
+// Horizon sample (trace.comp:258-262): v = reconstruct(uv, sz) - view_vec at the ray's CURRENT uv, h = max(h, n.v / |v|) if
+// |v| < 0.3.  |v| >= |v.z|, so a sample whose view z is 0.3 or more away is dropped before the rest is evaluated; a NaN sz
+// ("no sample owed") drops out at the same test.
+__device__ __forceinline__ void horizon_sample(const f3& vv, const f3& n, const CamF& camf, float px, float py, float sz, float& h) {
   const float z = linearize_fast(sz, camf);
-  const float vx = fmaf(fmaf(t, H.a1, H.a0), z, -H.vv.x), vy = fmaf(fmaf(t, H.b1, H.b0), z, -H.vv.y), vz = z - H.vv.z;
-  const float d2 = fmaf(vz, vz, fmaf(vy, vy, vx * vx));
-  if (d2 < 0.09f) h = fmaxf(h, fmaf(H.n.z, vz, fmaf(H.n.y, vy, H.n.x * vx)) * rsqrt_fast(d2));
+  const float vz = z - vv.z;
+  if (fabsf(vz) < 0.3f) {
+    const float vx = fmaf(fmaf(-2.0f * camf.aspect_tg, px, camf.aspect_tg), z, -vv.x), vy = fmaf(fmaf(-2.0f * camf.tg, py, camf.tg), z, -vv.y);
+    const float d2 = fmaf(vz, vz, fmaf(vy, vy, vx * vx));
+    if (d2 < 0.09f) h = fmaxf(h, fmaf(n.z, vz, fmaf(n.y, vy, n.x * vx)) * rsqrt_fast(d2));
+  }
 }
 
 // one step on level m (magic = 1.5 * 2^(23+m)); returns above_surface
 template <bool PINNED>
 __device__ __forceinline__ bool fast_step(const RayK& r, const uint4* __restrict__ lvl, float ssx, float ssy, float rinvx0, float rinvy0, float magic,
-                                          float& t, bool& skipped, float& sz_out) {
-  const float px = fmaf(t, r.dx, r.ox), py = fmaf(t, r.dy, r.oy);
+                                          float px, float py, float& t, bool& skipped, float& sz_out) {
   const float mx = __fmaf_rd(ssx, px, magic), my = __fmaf_rd(ssy, py, magic);
   const int mb = __float_as_int(magic);
   const int xi = __float_as_int(mx) - mb, yi = __float_as_int(my) - mb;            // cell index on this level (>= 0 inside the screen)
@@ -261,7 +264,7 @@ __device__ __forceinline__ bool fast_step(const RayK& r, const uint4* __restrict
 }
 
 template <bool LAYERED>
-__global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
+__global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
                                                           const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
   __shared__ uint4 lvl[16];
   TraceK kl;
@@ -283,7 +286,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     lvl[m] = e;
   }
   __syncthreads();
-  const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = VKR_BLOCK_Y * 8 + (threadIdx.x >> 4);
+  const int px = blockIdx.x * 16 + (threadIdx.x & 15), py = VKR_BLOCK_Y * TRACE_CTA_ROWS + (threadIdx.x >> 4);
   if (px >= out_rays.w || py >= out_rays.h) return;
   const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
   const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
@@ -300,7 +303,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
   const uint32_t base_index = (uint32_t)(rand_hash(su, sv) * 128.0f);                           // :61-63
   const uint32_t index = (base_index + k.frame_random) & 127u;
   const float4 hv = __ldg(halton + index);
-  f3 pixel_normal, w0, R, origin, direction;
+  f3 pixel_normal, R, origin, direction;
   const f3 view_vec = reconstruct_view_vec(su, sv, pixel_depth, cam);                           // exact: one side of the oracle-bit horizon difference
 #if TRACE_FAST_SETUP
   {
@@ -308,7 +311,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     f3 tangent = get_tangent(pixel_normal);
     f3 bitangent = norm3f(cross3(pixel_normal, tangent));
     tangent = norm3f(cross3(bitangent, pixel_normal));
-    w0 = -norm3f(view_vec);
+    const f3 w0 = -norm3f(view_vec);
     f3 view_dir = mk3(dot3f(w0, tangent), dot3f(w0, bitangent), dot3f(w0, pixel_normal));
     f3 brdf_norm = sampleGGXVNDF_fast(view_dir, roughness, roughness, hv.x, hv.y);
     f3 N = mk3(fmaf(brdf_norm.x, tangent.x, fmaf(brdf_norm.y, bitangent.x, brdf_norm.z * pixel_normal.x)),
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     f3 tangent = get_tangent(pixel_normal);
     f3 bitangent = norm3(cross3(pixel_normal, tangent));
     tangent = norm3(cross3(bitangent, pixel_normal));
-    w0 = -norm3(view_vec);
+    const f3 w0 = -norm3(view_vec);
     f3 view_dir = mk3(dot3(w0, tangent), dot3(w0, bitangent), dot3(w0, pixel_normal));
     f3 brdf_norm = sampleGGXVNDF(view_dir, roughness, roughness, hv.x, hv.y);
     f3 N = brdf_norm.x * tangent + brdf_norm.y * bitangent + brdf_norm.z * pixel_normal;
@@ -363,36 +366,37 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     const bool inside = origin.x > eps && origin.x < 1.0f - eps && origin.y > eps && origin.y < 1.0f - eps;
     if (!inside) r.t_exit = -1.0f;
   }
-  HorK H;
-  H.a1 = -2.0f * direction.x * camf.aspect_tg; H.a0 = (1.0f - 2.0f * origin.x) * camf.aspect_tg;
-  H.b1 = -2.0f * direction.y * camf.tg; H.b0 = (1.0f - 2.0f * origin.y) * camf.tg;
-  H.vv = view_vec; H.n = pixel_normal;
-
   float t;
   {                                                    // initial_advance_ray, screen_trace.glsl:8-15
     const float ex = fmaf(floorf(ssx * origin.x) + r.fox, rinvx0, r.cx), ey = fmaf(floorf(ssy * origin.y) + r.foy, rinvy0, r.cy);
     t = fminf(ex * r.idx, ey * r.idy);
   }
-  float h = 0.f;
+  // The horizon sample of a step is taken at the position the ray has AFTER that step (:256-262).  It is evaluated at the
+  // top of the next step, where that position's uv is needed anyway; `owed` carries the step's depth (NaN = nothing owed).
+  const float NOTHING = __int_as_float(0x7FC00000);
+  float h = 0.f, owed = NOTHING;
   int i = 0;
   int mip = 0;
   // Steps 0..14 stay on level 0 (:250).  A ray found below the surface there never moves again (t frozen, the same
   // horizon sample every step) and leaves the march at step 15: it is finished.
   bool done = false;
   for (; i < 15 && t < r.t_exit; ++i) {
-    bool skipped; float sz;
-    const bool above = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, t, skipped, sz);
-    horizon_sample(H, camf, t, sz, h);
+    const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
+    horizon_sample(view_vec, pixel_normal, camf, cpx, cpy, owed, h);
+    bool skipped;
+    const bool above = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, cpx, cpy, t, skipped, owed);
     if (!above) { done = true; break; }
   }
   if (!done && i >= 15) {
     float magic = TR_MAGIC0;
     while (i < 80 && magic >= TR_MAGIC0 && t < r.t_exit) {
+      const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
+      if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, cpx, cpy, owed, h);
       bool skipped; float sz;
-      fast_step<false>(r, lvl, ssx, ssy, rinvx0, rinvy0, magic, t, skipped, sz);
+      fast_step<false>(r, lvl, ssx, ssy, rinvx0, rinvy0, magic, cpx, cpy, t, skipped, sz);
       magic = __int_as_float(__float_as_int(magic) + (skipped ? 0x00800000 : -0x00800000));
       ++i;
-      if (magic <= 2.0f * TR_MAGIC0) horizon_sample(H, camf, t, sz, h);
+      owed = magic <= 2.0f * TR_MAGIC0 ? sz : NOTHING;
     }
     mip = (__float_as_int(magic) >> 23) - 150;
   }
@@ -401,11 +405,24 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
   while (!done && i < 80 && mip >= 0) {
     const float S = __int_as_float((127 + mip) << 23), s = __int_as_float((127 - mip) << 23);   // 2^mip, 2^-mip
     const float pxx = fmaf(t, r.dx, r.ox), pyy = fmaf(t, r.dy, r.oy);
+    if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, pxx, pyy, owed, h);
     const float mpx = (ssx * s) * pxx, mpy = (ssy * s) * pyy;
     const int xi = (int)mpx, yi = (int)mpy;
     const uint4 L = lvl[min(mip, 15)];
+    const bool oobx = (unsigned)xi >= (L.w & 0xFFFFu), ooby = (unsigned)yi >= (L.w >> 16);
+    if ((oobx && (pxx >= 1.0f || mpx <= -1.0f)) || (ooby && (pyy >= 1.0f || mpy <= -1.0f))) {
+      // Out of range along one axis on this level AND on every finer one (uv >= 1 with cell >= extent here: the cell index
+      // at least doubles per level while the extent at most doubles; res * uv <= -1: ever more negative as res doubles).
+      // Every remaining fetch returns 0, which is never above the ray: t stays, the level counts down to -1, and the same
+      // sample (depth 0) is offered to the horizon at each level <= 1 -- once is enough, if the step budget lets the march
+      // get that far: the first such step is number max(mip - 1, 1) from here (step 1 at once while the level is pinned).
+      const int first = (i < 15) ? 1 : max(mip - 1, 1);
+      owed = (i + first <= 80) ? 0.0f : NOTHING;
+      done = true;
+      break;
+    }
     float sz = 0.0f;
-    if ((unsigned)xi < (L.w & 0xFFFFu) && (unsigned)yi < (L.w >> 16))
+    if (!oobx && !ooby)
       sz = d24_to_float(__ldg((const uint32_t*)(((unsigned long long)L.y << 32) | L.x) + ((uint32_t)yi * L.z + (uint32_t)xi)));
     const float ex = fmaf((floorf(mpx) + r.fox) * S, rinvx0, r.cx), ey = fmaf((floorf(mpy) + r.foy) * S, rinvy0, r.cy);
     const float tx = ex * r.idx, ty = ey * r.idy;
@@ -417,9 +434,10 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     t = above ? t_min : t;
     if (i >= 15) mip += skipped ? 1 : -1;
     ++i;
-    if (mip <= 1) horizon_sample(H, camf, t, sz, h);
+    owed = mip <= 1 ? sz : NOTHING;
   }
   const f3 out_ray = mk3(fmaf(t, r.dx, r.ox), fmaf(t, r.dy, r.oy), fmaf(t, r.dz, r.oz));
+  if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, out_ray.x, out_ray.y, owed, h);
   bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
 
   {                                                                                              // :94-99
@@ -448,6 +466,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
   }
   {                                                                                              // :123-139, value-only
 #if TRACE_FAST_SETUP
+    const f3 w0 = -norm3f(view_vec);                  // recomputed: not kept alive across the march
     f3 slice_normal = norm3f(cross3(w0, R));
     const float pn = dot3f(pixel_normal, slice_normal);
     f3 normal_projected = mk3(fmaf(-pn, slice_normal.x, pixel_normal.x), fmaf(-pn, slice_normal.y, pixel_normal.y), fmaf(-pn, slice_normal.z, pixel_normal.z));
@@ -460,6 +479,7 @@ __global__ void __launch_bounds__(128, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK
     float pdfv = sampleGGXdirPDF(pdf, w0, pixel_normal, R, roughness);
     float occlusion = ((1.0f / VKR_PI) * 0.25f) * (np2 * rnp) * gmax(-__cosf(2.f * hh - n) + __cosf(n) + 2.f * hh * __sinf(n), 0.f);
 #else
+    const f3 w0 = -norm3(view_vec);
     f3 slice_normal = norm3(cross3(w0, R));
     f3 normal_projected = pixel_normal - dot3(pixel_normal, slice_normal) * slice_normal;
     f3 X = norm3(cross3(slice_normal, w0));
@@ -503,7 +523,11 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
     return VKR_ERR_SIZE_MISMATCH;
   }
   ExtInfo x;
+#if TRACE_V2
+  int rc = resolve_ext(ext, out_rays->height, TRACE_CTA_ROWS, &x, "sssr_trace");
+#else
   int rc = resolve_ext(ext, out_rays->height, 8, &x, "sssr_trace");
+#endif
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   TraceK k = make_trace_k(p);
@@ -528,7 +552,8 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
 #else
   auto kern = kv ? sssr_trace_kernel<true> : sssr_trace_kernel<false>;
 #endif
-  kern<<<grid, 128, 0, st>>>(k, kv, LaunchX{x.yb0}, P, make_mip(dnormal, 0, x, 1), make_mip(material, 0, x, 2), (const float4*)halton_vec4x128,
+  const int threads = TRACE_V2 ? 16 * TRACE_CTA_ROWS : 128;
+  kern<<<grid, threads, 0, st>>>(k, kv, LaunchX{x.yb0}, P, make_mip(dnormal, 0, x, 1), make_mip(material, 0, x, 2), (const float4*)halton_vec4x128,
                              make_mip(pdf_lut, 0, x, 3), make_mip(out_rays, 0, x, 4), make_mip(out_occlusion, 0, x, 5), srgb);
   return check_launch("sssr_trace_kernel");
 }
