@@ -73,7 +73,8 @@ def test_lut_kernels(cuda, oracle_luts):
 
 
 # 328x200: the half-res images are 164x100, so the 32-wide and 16-high tiles of trace / blur / GTAO end ragged
-@pytest.mark.parametrize("w,h,frames,view", [(1280, 720, 3, 0), (640, 360, 4, 3), (256, 256, 3, 5), (328, 200, 3, 2)])
+# 1920x1080 and 3840x2160 are BASELINE.json configs[1] and configs[2]: the sizes every bench number is quoted on
+@pytest.mark.parametrize("w,h,frames,view", [(1280, 720, 3, 0), (640, 360, 4, 3), (256, 256, 3, 5), (328, 200, 3, 2), (1920, 1080, 2, 1), (3840, 2160, 2, 0)])
 def test_pass_level_parity(cuda, oracle_luts, w, h, frames, view):
     import torch
     scene = vkr.synth_scene(view, 64)
@@ -106,7 +107,8 @@ def test_pass_level_parity(cuda, oracle_luts, w, h, frames, view):
     assert not failures, failures
 
 
-@pytest.mark.parametrize("w,h,frames", [(640, 360, 8)])
+# 64 frames: the length of BASELINE.json configs[2]'s TAA sequence (at 1280x720 so that the CPU side stays ~20 s)
+@pytest.mark.parametrize("w,h,frames", [(640, 360, 8), (1280, 720, 64)])
 def test_free_running_chain(cuda, w, h, frames):
     """Both sides end to end on their own state: own LUTs (256^2 here to bound CPU time), own histories."""
     import torch
@@ -122,10 +124,11 @@ def test_free_running_chain(cuda, w, h, frames):
             m = parity.compare_image(o, co[o], oo[o])
             report.append(dict(frame=f, image=o, **m))
     os.makedirs(OUT, exist_ok=True)
-    with open(os.path.join(OUT, "parity_chain.json"), "w") as fh:
+    with open(os.path.join(OUT, f"parity_chain_{w}x{h}x{frames}.json"), "w") as fh:
         json.dump(report, fh, indent=1)
     for r in report:
-        print(r)
+        if r["frame"] < 2 or r["frame"] == frames - 1:
+            print(r)
     # integer outputs stay bit-exact; fp outputs: PSNR must hold and must not drift with the frame index
     for r in report:
         if r["image"] in ("depth", "dn", "dv") and r["mismatches"]:
@@ -134,7 +137,8 @@ def test_free_running_chain(cuda, w, h, frames):
     # handful of texels is inside it (<= 1e-4 of texels) and decays with 0.9^k afterwards.
     # no drift: the last frame is not worse than the worst earlier frame by more than 3 dB, and stays above the floor.
     for r in report:
-        if r["frame"] >= 1 and r["image"] in parity.TOLERANCES and r["image"] not in ("depth", "dn", "dv", "rays", "raw"):
+        # rays / raw included: the trace and GTAO main read no history, so both chains feed them identical bytes every frame
+        if r["frame"] >= 1 and r["image"] in parity.TOLERANCES and r["image"] not in ("depth", "dn", "dv"):
             if not parity.TOLERANCES[r["image"]](r):
                 failures.append(r)
     for o in ("accumulated_ao", "blurred", "color", "taa"):

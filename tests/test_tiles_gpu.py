@@ -25,11 +25,12 @@ def test_tile_rows_partition():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("world,w,h,frames", [(2, 512, 384, 3), (3, 384, 320, 2)])
-def test_row_tiled_frames_are_bit_identical(cuda, world, w, h, frames):
-    port = 29900 + (os.getpid() + world) % 500
+# the last case also compares every rank's rows with the CPU oracle's whole frame at 1920x1080 (tests/parity.py tolerances)
+@pytest.mark.parametrize("world,w,h,frames,mode", [(2, 512, 384, 3, ""), (3, 384, 320, 2, ""), (2, 1920, 1080, 2, "oracle")])
+def test_row_tiled_frames_are_bit_identical(cuda, world, w, h, frames, mode):
+    port = 29900 + (os.getpid() + world + w) % 500
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(ROOT, "tests", "tiles_worker.py"), ROOT, str(w), str(h), str(frames)]
+           "--master-port", str(port), os.path.join(ROOT, "tests", "tiles_worker.py"), ROOT, str(w), str(h), str(frames)] + ([mode] if mode else [])
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("ok") == world

@@ -15,7 +15,8 @@ import vkr_views
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("w,h,views,frames", [(128, 64, [3, 11, 12, 40, 7], 3), (256, 256, [0, 5], 2)])
+# views 64..127 at 256x256: rank 1's shard of BASELINE.json configs[3] (512 probe views over 8 GPUs) in one batch
+@pytest.mark.parametrize("w,h,views,frames", [(128, 64, [3, 11, 12, 40, 7], 3), (256, 256, [0, 5], 2), (256, 256, list(range(64, 128)), 2)])
 def test_batched_views_match_oracle(cuda, w, h, views, frames):
     import torch
     ob = chain.OracleBackend()
