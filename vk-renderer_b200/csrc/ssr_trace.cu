@@ -14,7 +14,7 @@
 #define TRACE_UNROLL_A 1
 #endif
 #ifndef TRACE_V2
-#define TRACE_V2 0   /* 1 = the re-stated march below; default flips once its GPU parity run is committed */
+#define TRACE_V2 1   /* the re-stated march below (profiles/r02a_trace_variants.txt, r02c_trace_variants.txt); 0 = round 1's kernel */
 #endif
 namespace vkr {
 
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 #define TRACE_FAST_SETUP 1
 #endif
 #ifndef TRACE_MIN_CTAS
-#define TRACE_MIN_CTAS 1
+#define TRACE_MIN_CTAS 9                 /* 56 registers, no spill in the plain kernel: 0.3553 -> 0.3522 ms at 4K */
 #endif
 #ifndef TRACE_CTA_ROWS
 #define TRACE_CTA_ROWS 8                /* 16 x TRACE_CTA_ROWS rays per CTA (one 16 x 2 strip per warp) */
