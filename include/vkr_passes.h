@@ -198,6 +198,11 @@ uint32_t vkr_format_texel_size(uint32_t format);
  * returns the allocation size in bytes (0 on bad arguments).  Replaces VMA image creation
  * behind RenderGraph::create_image (reference src/rendergraph/rendergraph.cpp:341-369). */
 uint64_t vkr_image_layout(uint32_t width, uint32_t height, uint32_t format, uint32_t mip_count, VkrImage* img);
+/* The rule every pass entry applies to its VkrImage arguments: base, mip_offset[i] and row_pitch[i] 16-byte aligned
+ * (rows are read as 128-bit vectors), row_pitch[i] >= width_i * texel size, known format, 1 <= mip_count <= VKR_MAX_MIPS.
+ * VKR_OK or VKR_ERR_INVALID_ARGUMENT (vkr_last_error() names the field).  No reference counterpart: there a VkImage
+ * cannot be mis-described (gpu::ImageInfo, reference src/gpu/resource_info.hpp:11-45). */
+int vkr_image_validate(const VkrImage* img);
 /* floor(log2(max(w,h))) + 1 — the mip count Gbuffer gives its depth images
  * (reference src/scene_renderer.cpp:13). */
 uint32_t vkr_full_mip_count(uint32_t width, uint32_t height);

@@ -126,3 +126,45 @@ def test_new_entries_validate_arguments_before_touching_the_device():
     filt = vkr.Image(32, 32, vkr.R16_SFLOAT, device="cpu")
     assert L.vkr_gtao_filter_ex(C.byref(vkr.GtaoParams()), d.ptr, raw.ptr, filt.ptr, 1, C.byref(e), None) == -1
     assert b"first_param" in L.vkr_last_error()
+
+
+def test_misaligned_or_short_pitched_images_are_refused():
+    """the kernels read rows as 128-bit vectors, so an image whose base / mip offset / pitch is not
+    16-byte aligned, or whose pitch does not hold a row, must come back as VKR_ERR_INVALID_ARGUMENT naming the field --
+    from every pass entry (they share image_ok) and from vkr_image_validate -- instead of faulting on the device."""
+    import torch
+    import vkr
+    L = vkr.lib
+    L.vkr_last_error.restype = C.c_char_p
+    L.vkr_image_validate.restype = C.c_int
+    L.vkr_image_validate.argtypes = [C.POINTER(vkr.VkrImage)]
+    INVALID = -1
+    w, h = 30, 8                                        # 30 texels x 4 bytes = 120: a tight pitch is not a multiple of 16
+
+    def img(fmt=vkr.R8G8B8A8_SRGB, ww=w, hh=h):
+        return vkr.Image(ww, hh, fmt, device="cpu")
+
+    good = img()
+    assert L.vkr_image_validate(good.ptr) == 0
+    # (a) base offset by 4 bytes
+    buf = torch.zeros(good.buf.numel() + 16, dtype=torch.uint8)
+    off = vkr.Image.over(buf[4:], w, h, vkr.R8G8B8A8_SRGB)
+    if off.desc.base % 16 == 0:                          # the allocation itself happened to sit at 16k + 12
+        off = vkr.Image.over(buf[8:], w, h, vkr.R8G8B8A8_SRGB)
+    assert L.vkr_image_validate(off.ptr) == INVALID and b"base" in L.vkr_last_error()
+    # (b) tight pitch w*4 with w % 4 != 0
+    tight = img()
+    tight.desc.row_pitch[0] = w * 4
+    assert L.vkr_image_validate(tight.ptr) == INVALID and b"row_pitch[0] = 120" in L.vkr_last_error()
+    # (c) pitch aligned but shorter than a row; (d) mip offset not aligned
+    short = img()
+    short.desc.row_pitch[0] = 112
+    assert L.vkr_image_validate(short.ptr) == INVALID and b"smaller than a row" in L.vkr_last_error()
+    depth = vkr.Image(32, 32, vkr.D24_UNORM_S8_UINT, 3, device="cpu")
+    depth.desc.mip_offset[1] += 4
+    assert L.vkr_image_validate(depth.ptr) == INVALID and b"mip_offset[1]" in L.vkr_last_error()
+    # the pass entries apply the same rule before any CUDA call: TAA with a tight-pitched colour image
+    hist, out = img(vkr.R16G16B16A16_SFLOAT), img(vkr.R16G16B16A16_SFLOAT)
+    pd, d, vel = img(vkr.D24_UNORM_S8_UINT), img(vkr.D24_UNORM_S8_UINT), img(vkr.R16G16_SFLOAT)
+    rc = L.vkr_taa_resolve(C.byref(vkr.TaaParams()), hist.ptr, pd.ptr, d.ptr, vel.ptr, tight.ptr, out.ptr, None)
+    assert rc == INVALID and b"image layout: row_pitch[0] = 120" in L.vkr_last_error(), (rc, L.vkr_last_error())

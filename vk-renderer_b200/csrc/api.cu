@@ -9,12 +9,24 @@
 namespace vkr {
 
 static thread_local char g_err[512] = "";
+static thread_local char g_image_problem[192] = "";
+
+void note_image_problem(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_image_problem, sizeof(g_image_problem), fmt, ap);
+  va_end(ap);
+}
 
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
-  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  int n = vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+  if (g_image_problem[0] && n >= 0 && n < (int)sizeof(g_err) - 4) {      // image_ok() said why: keep it with the caller's message
+    snprintf(g_err + n, sizeof(g_err) - n, " [image layout: %s]", g_image_problem);
+    g_image_problem[0] = 0;
+  }
 }
 
 int check_launch(const char* what) {
@@ -130,6 +142,15 @@ uint32_t vkr_format_texel_size(uint32_t f) {
     case VKR_FORMAT_R32G32B32A32_SFLOAT: return 16;
   }
   return 0;
+}
+
+int vkr_image_validate(const VkrImage* img) {
+  if (!img || !img->base || !img->width || !img->height || img->mip_count < 1 || img->mip_count > VKR_MAX_MIPS) {
+    vkr::set_error("image_validate: null image, null base, zero extent or mip_count outside [1, %d]", VKR_MAX_MIPS);
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  if (!vkr::image_layout_ok(img)) { vkr::set_error("image_validate: layout refused"); return VKR_ERR_INVALID_ARGUMENT; }
+  return VKR_OK;
 }
 
 uint32_t vkr_full_mip_count(uint32_t w, uint32_t h) {

@@ -31,8 +31,28 @@ struct Mip {
 
 inline int mip_dim(uint32_t d, uint32_t lod) { uint32_t v = d >> lod; return v ? (int)v : 1; }
 
+// Why an image was refused, kept for the next set_error() on this thread (appended to the caller's message).
+void note_image_problem(const char* fmt, ...);
+
+// The kernels read rows as 128-bit (64-bit for RGBA16) vectors and index rows by pitch: base, every mip offset and every
+// row pitch must be 16-byte aligned and a row must hold its texels.  vkr_image_layout() produces exactly that; an image
+// described by hand (vkr_app_bind_gbuffer, a direct C-ABI caller) is refused here instead of faulting on the device.
+inline bool image_layout_ok(const VkrImage* im) {
+  const uint32_t bpp = vkr_format_texel_size(im->format);
+  if (!bpp) { note_image_problem("unknown format %u", im->format); return false; }
+  if ((uintptr_t)im->base & 15u) { note_image_problem("base %p is not 16-byte aligned", im->base); return false; }
+  for (uint32_t i = 0; i < im->mip_count; i++) {
+    const uint32_t w = mip_dim(im->width, i);
+    if (im->mip_offset[i] & 15u) { note_image_problem("mip_offset[%u] = %llu is not 16-byte aligned", i, (unsigned long long)im->mip_offset[i]); return false; }
+    if (im->row_pitch[i] & 15u) { note_image_problem("row_pitch[%u] = %u is not a multiple of 16", i, im->row_pitch[i]); return false; }
+    if (im->row_pitch[i] < w * bpp) { note_image_problem("row_pitch[%u] = %u is smaller than a row of %u texels x %u bytes", i, im->row_pitch[i], w, bpp); return false; }
+  }
+  return true;
+}
+
 inline bool image_ok(const VkrImage* im, uint32_t format) {
-  return im && im->base && im->format == format && im->mip_count >= 1 && im->mip_count <= VKR_MAX_MIPS && im->width && im->height;
+  return im && im->base && im->format == format && im->mip_count >= 1 && im->mip_count <= VKR_MAX_MIPS && im->width && im->height &&
+         image_layout_ok(im);
 }
 
 inline Mip make_mip(const VkrImage* im, uint32_t lod) {

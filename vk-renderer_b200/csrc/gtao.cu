@@ -275,27 +275,30 @@ __global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k0, const A
   const float su = pixel_uv(px, dim.w, dim.rw), sv = pixel_uv(py, dim.h, dim.rh);
   const CamF cam = make_camf(k.cam);
   const float2 vel = SAME ? unpack_rg16f(ld32(velocity, px, py)) : sample_rg16f(velocity, su, sv);
-  const float pu = su + vel.x, pv = sv + vel.y;
+  const float pu = FA(su, vel.x), pv = FA(sv, vel.y);
   bool reprojected = false;
   float valid_samples = 1.0f;
   if (pu >= 0 && pv >= 0 && pu <= 1 && pv <= 1) {
-    const f3 v_world_prev = mul_m4f(k.prev_inverse_camera, reconstruct_fast(pu, pv, sample_d24(prev_depth, pu, pv), cam));
-    const Mat4& M = k.mvp;
-    const float cx = fmaf(M.m[8], v_world_prev.z, fmaf(M.m[4], v_world_prev.y, fmaf(M.m[0], v_world_prev.x, M.m[12])));
-    const float cy = fmaf(M.m[9], v_world_prev.z, fmaf(M.m[5], v_world_prev.y, fmaf(M.m[1], v_world_prev.x, M.m[13])));
-    const float cz = fmaf(M.m[10], v_world_prev.z, fmaf(M.m[6], v_world_prev.y, fmaf(M.m[2], v_world_prev.x, M.m[14])));
-    const float cw = fmaf(M.m[11], v_world_prev.z, fmaf(M.m[7], v_world_prev.y, fmaf(M.m[3], v_world_prev.x, M.m[15])));
-    const float iw = rcp_fast(cw);
-    const float wu = fmaf(0.5f * iw, cx, 0.5f), wv = fmaf(0.5f * iw, cy, 0.5f);
-    const float ndz = cz / cw;                                              // feeds the ill-conditioned linearisation: IEEE
-    const float dx = fabsf(wu - su) * tw, dy = fabsf(wv - sv) * th;
-    const float current_z = linearize_fast(sample_d24(depth, su, sv), cam);
-    const float prev_z = linearize_fast(ndz, cam);
-    const float depth_err = fabsf(prev_z - current_z);
-    const float vel_delta = fmaxf(fabsf(vel.x) * tw, fabsf(vel.y) * th);
-    const float error = fmaf(0.1f, vel_delta, depth_err);
+    // accum.comp:51-71.  `reprojected` is a discontinuous choice whose inputs (depth, prev_depth, velocity, camera) are bit-identical
+    // on both sides of a parity run, and the running average it gates has a 1/N memory that the bilinear history fetch then
+    // spreads: a texel that flips here is still visible -- and wider -- 50 frames later (tests/test_parity_gpu.py, 64-frame
+    // chain: 3 % of the texels beyond 2e-3 at frame 63 with the value-only arithmetic this block used to have).  So the whole
+    // decision path carries the oracle's bits: unfused products and sums in the shader's order, correctly rounded quotients.
+    const float d_prev = sample_d24(prev_depth, pu, pv);
+    const float z_cam = linearize_rn(d_prev, cam);                                                 // gbuffer_encode.glsl:53-69
+    const f3 v_camera = mk3(FM(-FS(FM(2.f, pu), 1.f), FM(FM(z_cam, k.cam.aspect), k.cam.tg)), FM(-FS(FM(2.f, pv), 1.f), FM(z_cam, k.cam.tg)), z_cam);
+    const f3 v_world_prev = mul_m4(k.prev_inverse_camera, v_camera, 1.0f);
+    const float4 clip = mul_m4_4(k.mvp, v_world_prev, 1.0f);
+    const float ndx = div_rn_normal(clip.x, clip.w), ndy = div_rn_normal(clip.y, clip.w), ndz = div_rn_normal(clip.z, clip.w);
+    const float wu = FA(FM(0.5f, ndx), 0.5f), wv = FA(FM(0.5f, ndy), 0.5f);
+    const float dx = FM(fabsf(FS(wu, su)), tw), dy = FM(fabsf(FS(wv, sv)), th);
+    const float current_z = linearize_rn(sample_d24(depth, su, sv), cam);
+    const float prev_z = linearize_rn(ndz, cam);
+    const float depth_err = fabsf(FS(prev_z, current_z));
+    const float vel_delta = gmax(FM(fabsf(vel.x), tw), FM(fabsf(vel.y), th));
+    const float error = FA(FM(0.1f, vel_delta), depth_err);
     valid_samples = fminf(fmaxf(1.f - error, 0.8f), 1.f);
-    reprojected = (fmaxf(dx, dy) <= 2.0f) && (depth_err < 0.2f);
+    reprojected = (gmax(dx, dy) <= 2.0f) && (depth_err < 0.2f);
   }
   const float new_ao = __half2float(*((const __half*)(filtered.p + (size_t)py * filtered.pitch) + px));
   float computed_ao = new_ao;

@@ -51,6 +51,7 @@ void RenderGraph::rebind_image(ImageResourceId id, const VkrImage& external) {
   const VkrImage& cur = image(id);
   if (!external.base || external.width != cur.width || external.height != cur.height || external.format != cur.format || external.mip_count != cur.mip_count)
     throw std::runtime_error("rebind_image: external image does not match the slot's descriptor");
+  if (vkr_image_validate(&external) != VKR_OK) throw std::runtime_error(std::string("rebind_image: ") + vkr_last_error());
   slots[id.get_index()].desc = external;
 }
 
