@@ -55,6 +55,7 @@ def parse():
                     help="probes workload: cap the CTAs NCCL may use per collective (0 = NCCL's default).  The gather moves 64 MB per frame into "
                          "every GPU while the passes want every SM; a small cap leaves the SMs to the passes")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-sub", action="store_true", help="chain workload: skip the probes / tiles sub-records")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -131,7 +132,7 @@ def cpu_chain_rate(width, height, frames, warm, threads=0):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    gpix, ms, threads, band_rows = cpu_chain_rate(args.width, args.height, args.steps, args.warmup)
+    gpix, ms, threads, band_rows = cpu_chain_rate(args.width, args.height, args.steps, args.warmup, threads=host_threads())
     sample = (f"each step = rows [{int(BAND[0]*args.height)}, {int(BAND[1]*args.height)}) of one {args.width}x{args.height} frame through every pass "
               f"({band_rows} of {args.height} rows; Hi-Z built in full), OpenMP over rows")
     line = {"impl": "reference", "metric": "chain_throughput", "value": gpix, "unit": "Gpix/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -144,13 +145,46 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+def init_dist(args, world):
+    """One process per GPU; the NCCL group is created once per process whichever workloads follow."""
+    import torch
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", 0)))
+    torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        opts = None
+        if args.nccl_max_ctas > 0:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = args.nccl_max_ctas
+            opts.config.min_ctas = min(args.nccl_max_ctas, 1)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
+    return local
+
+
+def csrc_sha16():
+    """Identity of the kernel sources being timed (same function in tools/ncu_summary.py stamps profiles/traffic.json)."""
+    import glob
+    import hashlib
+    hsh = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "vk-renderer_b200", "csrc", "*.cu*"))):
+        hsh.update(os.path.basename(f).encode())
+        hsh.update(open(f, "rb").read())
+    return hsh.hexdigest()[:16]
+
+
+def host_threads():
+    """Host cores this process may use.  Set explicitly on the oracle: torchrun exports OMP_NUM_THREADS=1, which silently
+    turned the CPU arm into a one-core run at N >= 2 in round 1 (VERDICT r01, weak #12)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_ours(args, rank, world):
     import torch
     import torch.distributed as dist
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    local = init_dist(args, world)
     import vkr
     import vkr_host
 
@@ -289,17 +323,24 @@ def run_ours(args, rank, world):
                "d2h_bytes_per_step": d2h, "note": "pinned host G-buffer -> device (copy stream) -> vkr_app_bind_gbuffer -> render_frame -> TAA target -> pinned host "
                                                   "(read-back stream); three device G-buffers rotate so both PCIe directions overlap the chain"}
 
+    app.close()
+    del resident, app
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
     peak, peak_src = peaks()
     dom = max(tasks.items(), key=lambda kv: kv[1][0])
     dname, (dms, dcount) = dom
     avg_ms = dms / max(dcount, 1)
     achieved = ALG_BYTES[dname] * npix / (avg_ms * 1e-3) / 1e9
     traffic = None
+    traffic_stale, traffic_captured = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the committed ncu --set full capture
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(f"{w}x{h}", {}).get(dname)
+        tj = json.load(open(tpath))
+        traffic = tj.get(f"{w}x{h}", {}).get(dname)
+        traffic_captured = tj.get("_captured_at")               # {"git_head", "csrc_sha16"} written by tools/ncu_summary.py
+        traffic_stale = (traffic_captured or {}).get("csrc_sha16") != csrc_sha16()   # the profiled kernels are not the timed ones
     chain_alg = 128.0 * npix
     # why the HBM fraction is low: the chain's executed warp instructions (same ncu capture) against the issue slots the
     # frame time offers (SMs x 4 schedulers x the SM clock sampled during the timed region)
@@ -319,7 +360,8 @@ def run_ours(args, rank, world):
                        "frames_resident": nres, "l2": "inputs larger than L2 (one frame touches > 1 GB at 4K)",
                        "parallelism": f"{world} independent sequence(s), one per GPU"},
             "roofline": {"bound": "hbm", "kernel": dname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "avg_launch_ms": avg_ms,
+                         "traffic": traffic, "traffic_stale": traffic_stale, "traffic_captured_at": traffic_captured,
+                         "peak_source": peak_src, "avg_launch_ms": avg_ms,
                          "chain": {"alg_bytes_per_frame": chain_alg, "achieved": chain_alg / (ms_step * 1e-3) / 1e9,
                                    "frac": chain_alg / (ms_step * 1e-3) / 1e9 / peak, "issue_slots": issue},
                          "per_task_ms": {k: v[0] / max(v[1], 1) for k, v in tasks.items()},
@@ -330,28 +372,20 @@ def run_ours(args, rank, world):
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
-        gpix, ms, threads, band_rows = cpu_chain_rate(w, h, 3, 1)
+        gpix, ms, threads, band_rows = cpu_chain_rate(w, h, 3, 1, threads=host_threads())
         line["cpu_baseline"] = {"value": gpix, "unit": "Gpix/s", "cores": threads, "kind": "port", "ms_per_sample_frame": ms,
                                 "sample": f"rows [{int(BAND[0]*h)}, {int(BAND[1]*h)}) of 3 frames of the same {w}x{h} sequence through every pass after 1 warm-up "
                                           f"({band_rows} of {h} rows; Hi-Z in full)"}
-    print(json.dumps(line))
+    return line
 
 
-def run_probes(args, rank, world):
+def run_probes(args, rank, world, emit=True):
     """BASELINE configs[3]: args.views independent 256x256 views (Hi-Z + SSR trace/filter/blur + GTAO main/filter/accumulate),
     contiguous blocks of views per rank, every pass ONE launch per rank (layers on grid.z), outputs all-gathered per frame on a
     side stream (the only collective; it overlaps the next frame).  Strong scaling: the batch is fixed, ranks split it."""
     import torch
     import torch.distributed as dist
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    if world > 1:
-        opts = None
-        if args.nccl_max_ctas > 0:
-            opts = dist.ProcessGroupNCCL.Options()
-            opts.config.max_ctas = args.nccl_max_ctas
-            opts.config.min_ctas = min(args.nccl_max_ctas, 1)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
+    local = init_dist(args, world)
     import vkr
     import vkr_views
     w = h = 256
@@ -476,8 +510,10 @@ def run_probes(args, rank, world):
     if pg is not None:
         gather_timeouts = pg.wait_failures()
         pg.close(dist.barrier)
+    del graphs, outs, frames, vb, gout
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
     peak, peak_src = peaks()
     npix = args.views * w * h
     alg = 73.0 * npix                                        # Hi-Z + SSR + GTAO subset of the chain, SURVEY §8d
@@ -490,20 +526,19 @@ def run_probes(args, rank, world):
             "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
             "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * max(1, args.probes_groups) * K, "gather_wait_timeouts": gather_timeouts, "clocks": sampler.result()}
-    print(json.dumps(line))
+    if emit:
+        print(json.dumps(line))
+    return line
 
 
-def run_tiles(args, rank, world):
+def run_tiles(args, rank, world, emit=True):
     """BASELINE configs[4]: one 7680x4320 sequence, full chain, rows split over the ranks (vkr_tiles.RowTiledFrame): inputs and
     Hi-Z replicated, six halo exchanges per frame as direct peer stores + stream-side flags.  The finished TAA rows stay on the rank
     that computed them (--tiles-gather none, the default) or are sent to rank 0 every frame (rank0: NCCL send/recv on a side
     stream; 265 MB per frame into one GPU, which then bounds the frame rate).  Strong scaling."""
     import torch
     import torch.distributed as dist
-    local = int(os.environ.get("LOCAL_RANK", rank))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    local = init_dist(args, world)
     import vkr
     import vkr_tiles
     w, h = (7680, 4320) if args.width == 3840 else (args.width, args.height)
@@ -611,8 +646,11 @@ def run_tiles(args, rank, world):
         ms, fails = float(t[0].item()), int(t[1].item())
     sampler.join(timeout=1.0)
     tf.close(dist.barrier if world > 1 else None)
+    halo = tf.halo
+    del tf, G, D
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
     peak, peak_src = peaks()
     npix = w * h
     alg = 128.0 * npix
@@ -624,13 +662,56 @@ def run_tiles(args, rank, world):
                                       "stream-side flags, pushed on a transfer stream and waited for one independent pass later; " + ("finished TAA rows sent to rank 0 every frame (NCCL send/recv, side stream)"
                                                                if args.tiles_gather == "rank0" else
                                                                "finished TAA rows stay resident on the rank that computed them (SURVEY 8e: shard-resident output)"),
-                       "halo_rows": tf.halo, "wait_timeouts": fails, "host_enqueue_ms_per_frame_rank0": round(host_ms, 3),
+                       "halo_rows": halo, "wait_timeouts": fails, "host_enqueue_ms_per_frame_rank0": round(host_ms, 3),
                        "strip_bounds": {"final": bounds, "even": history[0], "tile_ms_without_exchange_per_round": cal_ms, "balanced": bool(world > 1 and args.tiles_balance),
                                         "note": "16-row half-res strips; boundaries moved by 3 untimed calibration rounds so every rank's tile costs the same"}},
             "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
             "gpu_launches": vkr_tiles.RowTiledFrame.KERNELS_PER_FRAME * K, "clocks": sampler.result()}
-    print(json.dumps(line))
+    if emit:
+        print(json.dumps(line))
+    return line
+
+
+SUB_STEPS, SUB_WARMUP = 24, 8
+
+
+def sub_records(args, rank, world):
+    """The two workloads north_star asks to SHARD (BASELINE configs[3] probe batch, configs[4] row-tiled 8K frame), measured in
+    the same job as the headline line so that the driver's BENCH / SCALE records carry them from one build: at N ranks the
+    sharded run, and -- in the same process on rank 0 alone, the other ranks waiting at a barrier -- the same workload on ONE
+    GPU, so `speedup_vs_n1` needs no second job.  Bounded: SUB_STEPS timed steps after SUB_WARMUP each."""
+    import argparse
+    import torch
+    import torch.distributed as dist
+    out = {}
+    sub = argparse.Namespace(**vars(args))
+    sub.steps, sub.warmup = SUB_STEPS, SUB_WARMUP
+    for name, fn in (("probes", run_probes), ("tiles", run_tiles)):
+        solo = None
+        if world > 1:
+            if rank == 0:
+                solo = fn(sub, 0, 1, emit=False)
+            torch.cuda.synchronize()
+            dist.barrier()
+        full = fn(sub, rank, world, emit=False)
+        if rank == 0:
+            solo = solo or full
+            keep = ("metric", "value", "unit", "ms_per_step", "n_gpus", "steps", "warmup", "scaling", "gpu_launches")
+            rec = {k: full[k] for k in keep}
+            rec["workload"] = full["config"]["workload"]
+            rec["parallelism"] = full["config"]["parallelism"]
+            rec["roofline_frac"] = full["roofline"]["frac"]
+            rec["n1_same_run"] = {"value": solo["value"], "ms_per_step": solo["ms_per_step"]}
+            rec["speedup_vs_n1"] = full["value"] / solo["value"]
+            for k in ("gather_wait_timeouts",):
+                if k in full:
+                    rec[k] = full[k]
+            if "wait_timeouts" in full["config"]:
+                rec["wait_timeouts"] = full["config"]["wait_timeouts"]
+            rec["clocks"] = full["clocks"]
+            out[name] = rec
+    return out
 
 
 def main():
@@ -644,7 +725,11 @@ def main():
             import torch.distributed as dist
             dist.destroy_process_group()
     else:
-        run_ours(args, rank, world)
+        line = run_ours(args, rank, world)
+        subs = sub_records(args, rank, world) if not args.no_sub else {}
+        if rank == 0:
+            line.update(subs)
+            print(json.dumps(line))
         if world > 1:
             import torch.distributed as dist
             dist.destroy_process_group()

@@ -68,6 +68,18 @@ if not (len(sys.argv) > 6 and sys.argv[6] == "notraffic"):     # a report of ker
     tj[size] = traffic
     tj[size + ":warp_inst"] = winst                 # executed warp instructions per launch (smsp__inst_executed.sum)
     tj["source"] = f"{out} (dram__bytes_read.sum + dram__bytes_write.sum per launch)"
+    # provenance: bench.py prints traffic_stale when the kernels it times are not the ones profiled here.  The summary is
+    # written in the build container right after the capture, from the same tree the capture ran on.
+    import glob
+    import hashlib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hsh = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(root, "vk-renderer_b200", "csrc", "*.cu*"))):
+        hsh.update(os.path.basename(f).encode())
+        hsh.update(open(f, "rb").read())
+    head = subprocess.run(["git", "-C", root, "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+    dirty = bool(subprocess.run(["git", "-C", root, "status", "--porcelain", "--", "vk-renderer_b200/csrc"], capture_output=True, text=True).stdout.strip())
+    tj["_captured_at"] = {"git_head": head + ("+dirty" if dirty else ""), "csrc_sha16": hsh.hexdigest()[:16]}
     json.dump(tj, open(tpath, "w"), indent=1)
 for kk in kernels:
     print(f"{kk['kernel'][:44]:44s} {kk['time_us']:8.1f} us  issue {kk['issue_active_pct']:5.1f}%  fma {kk['pipe_fma_cycles_pct']:5.1f}%  warps {kk['warps_active_pct']:5.1f}%  "
