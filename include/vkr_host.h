@@ -80,6 +80,11 @@ const char* vkr_app_last_tasks(VkrApp* app);
  * second stream (independent branches of a frame run side by side; option "graph.concurrent_branches", default 1; always '0'
  * while task timing is on). */
 const char* vkr_app_last_lanes(VkrApp* app);
+/* How the rendergraph's submits reached the GPU so far: out4 = {frames launched as ONE CUDA graph (captured per frame, applied
+ * to the instantiated graph with cudaGraphExecUpdate), graph instantiations, submits issued eagerly (the first frame, frames
+ * with a read-back task, task timing on, single-stream mode), captures that failed}.  Option "graph.frame_graph" (default 1)
+ * switches the graph path.  Reference analogue: one command buffer per frame, src/rendergraph/rendergraph.cpp:271-337. */
+int vkr_app_frame_graph_stats(VkrApp* app, uint64_t* out4);
 /* The parameter blocks the optional "SSAO" / "SSR" tasks of the last frame were given (options alt.ssao / alt.ssr; the
  * passes of reference src/ssao.cpp and src/ssr.cpp, which the reference's frame loop does not schedule). */
 int vkr_app_alt_params(VkrApp* app, VkrSsaoParams* ssao_out, VkrSsrParams* ssr_out);
@@ -98,7 +103,8 @@ int vkr_app_screen_trace_params(VkrApp* app, VkrScreenTraceParams* out);
 /* alt.ssr_tiles: AdvancedSSR::run also issues SSSR_Clear, SSSR_Classification, SSSR_Tile_Regression and the indirect SSSR_trace
  * (reference src/advanced_ssr.cpp:547-550, commented out there); ssr.glossy_roughness_value = the classification threshold. */
 /* Runtime switches mirroring the ImGui state of the reference passes. fused_hiz: one launch for the
- * whole DownsamplePass instead of the per-task calls.  graph.concurrent_branches: see vkr_app_last_lanes. */
+ * whole DownsamplePass instead of the per-task calls.  graph.concurrent_branches: see vkr_app_last_lanes.
+ * graph.frame_graph: see vkr_app_frame_graph_stats. */
 int vkr_app_set_option(VkrApp* app, const char* name, float value);
 
 #ifdef __cplusplus

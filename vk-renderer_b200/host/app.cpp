@@ -408,11 +408,19 @@ void* vkr_app_stream(VkrApp* app) { return app ? app->render_graph.stream() : nu
 const char* vkr_app_last_tasks(VkrApp* app) { return app ? app->task_names.c_str() : ""; }
 const char* vkr_app_last_lanes(VkrApp* app) { return app ? app->task_lanes.c_str() : ""; }
 
+int vkr_app_frame_graph_stats(VkrApp* app, uint64_t* out4) {
+  if (!app || !out4) return VKR_ERR_INVALID_ARGUMENT;
+  const auto& st = app->render_graph.frame_graph_stats();
+  out4[0] = st.launches; out4[1] = st.instantiations; out4[2] = st.eager_submits; out4[3] = st.capture_failures;
+  return VKR_OK;
+}
+
 int vkr_app_set_option(VkrApp* app, const char* name, float v) {
   if (!app || !name) return VKR_ERR_INVALID_ARGUMENT;
   std::string n = name;
   if (n == "fused_hiz") app->downsample_pass.fused = v != 0.f;
   else if (n == "graph.concurrent_branches") app->render_graph.enable_concurrent_branches(v != 0.f);
+  else if (n == "graph.frame_graph") app->render_graph.enable_frame_graph(v != 0.f);
   else if (n == "gtao.mis") app->gtao.mis_gtao = v != 0.f;
   else if (n == "gtao.two_directions") app->gtao.two_directions = v != 0.f;
   else if (n == "gtao.only_reflections") app->gtao.only_reflections = v != 0.f;

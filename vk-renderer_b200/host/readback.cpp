@@ -75,6 +75,7 @@ ReadBackID ReadBackSystem::read_image(RenderGraph& graph, ImageResourceId image,
           cudaEventRecord(ev, (cudaStream_t)ctx.stream) != cudaSuccess)
         throw std::runtime_error{"ImageRead: device-to-host copy failed"};
     });
+  graph.mark_last_task_not_capturable();   // records an event the host waits on in after_submit(): the frame is issued eagerly
   return id;
 }
 

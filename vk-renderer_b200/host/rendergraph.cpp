@@ -38,6 +38,7 @@ RenderGraph::~RenderGraph() {
   for (void* e : event_pool_) cudaEventDestroy((cudaEvent_t)e);
   for (void* e : sync_events_) cudaEventDestroy((cudaEvent_t)e);
   if (aux_stream_) cudaStreamDestroy((cudaStream_t)aux_stream_);
+  if (graph_exec_) cudaGraphExecDestroy((cudaGraphExec_t)graph_exec_);
 }
 
 void* RenderGraph::get_event() {
@@ -156,9 +157,59 @@ void RenderGraph::submit() {
         t->write_commands(resources, cmd);
       }
     }
+    fg_stats_.eager_submits++;
     return;
   }
 
+  bool capture = frame_graph_ && warmed_;
+  for (auto& t : run) capture = capture && t->capturable;
+  if (capture) {
+    cudaStream_t st = (cudaStream_t)stream_;
+    if (cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+      cudaGraph_t g = nullptr;
+      bool ok = true;
+      try {
+        issue(run, resources);
+      } catch (...) {
+        cudaStreamEndCapture(st, &g);
+        if (g) cudaGraphDestroy(g);
+        cudaGetLastError();
+        throw;
+      }
+      ok = cudaStreamEndCapture(st, &g) == cudaSuccess && g != nullptr;
+      if (ok) {
+        cudaGraphExec_t exec = (cudaGraphExec_t)graph_exec_;
+        if (exec) {
+          cudaGraphExecUpdateResultInfo info;
+          if (cudaGraphExecUpdate(exec, g, &info) != cudaSuccess) {          // topology changed (another task list): start over
+            cudaGetLastError();
+            cudaGraphExecDestroy(exec);
+            exec = nullptr;
+          }
+        }
+        if (!exec) {
+          ok = cudaGraphInstantiate(&exec, g, 0) == cudaSuccess;
+          if (ok) fg_stats_.instantiations++;
+        }
+        graph_exec_ = ok ? exec : nullptr;
+        cudaGraphDestroy(g);
+        if (ok) ok = cudaGraphLaunch(exec, st) == cudaSuccess;
+      }
+      if (ok) { fg_stats_.launches++; return; }
+      cudaGetLastError();
+    }
+    // capture / instantiate / launch refused: nothing of this frame reached the GPU; issue it eagerly and stop trying
+    fg_stats_.capture_failures++;
+    frame_graph_ = false;
+    last_names.clear();
+    last_lanes.clear();
+  }
+  issue(run, resources);
+  warmed_ = true;                       // lazily built tables, module loads and the second stream exist from now on
+  fg_stats_.eager_submits++;
+}
+
+void RenderGraph::issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResources& resources) {
   // Two lanes.  Dependencies at whole-image granularity from the declared uses: a read depends on the image's last
   // writer; a write on its last writer and on every reader since.
   if (!aux_stream_) {

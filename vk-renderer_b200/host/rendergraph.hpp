@@ -134,6 +134,7 @@ struct BaseTask {
   virtual ~BaseTask() {}
   std::string name;
   std::vector<ImageUse> uses;   // filled by the builder while the task is declared
+  bool capturable = true;       // false: records events the host waits on / touches host state -> the frame is issued eagerly
 };
 
 template <typename TaskData>
@@ -175,6 +176,17 @@ struct RenderGraph {
   // concurrent branches off, everything runs on the one stream.
   void submit();
   void enable_concurrent_branches(bool on) { concurrent_ = on; }
+  // Frame graph (default on): from the second submit on, the two-lane issue sequence is stream-captured every frame and
+  // applied to ONE instantiated CUDA graph with cudaGraphExecUpdate (same topology; kernel parameters, grids and the
+  // ping-ponged image pointers change), then launched: the whole frame reaches the GPU as one unit, so the gaps between
+  // its ~10 kernels no longer depend on how fast this thread enqueues them (reference analogue: one command buffer per
+  // frame, src/rendergraph/rendergraph.cpp:271-337).  Frames that hold a task marked not capturable, per-task timing and
+  // single-stream mode are issued eagerly as before; a refused update re-instantiates, a failed capture turns the
+  // feature off and re-issues the frame eagerly (the chain's tasks are pure C-ABI calls).
+  void enable_frame_graph(bool on) { frame_graph_ = on; }
+  void mark_last_task_not_capturable() { if (!tasks.empty()) tasks.back()->capturable = false; }
+  struct FrameGraphStats { uint64_t launches = 0, instantiations = 0, eager_submits = 0, capture_failures = 0; };
+  const FrameGraphStats& frame_graph_stats() const { return fg_stats_; }
   // lane (0 = the graph's stream, 1 = the second one) each task of the last submit ran on
   const std::vector<int>& last_task_lanes() const { return last_lanes; }
   void wait_idle();
@@ -224,6 +236,10 @@ struct RenderGraph {
   std::vector<std::string> last_names;
   std::vector<int> last_lanes;
   bool concurrent_ = true;
+  void issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResources& resources);   // the two-lane issue sequence
+  bool frame_graph_ = true, warmed_ = false;
+  void* graph_exec_ = nullptr;          // cudaGraphExec_t, updated every captured frame
+  FrameGraphStats fg_stats_;
   void* aux_stream_ = nullptr;          // created on first use
   std::vector<void*> sync_events_;      // cudaEventDisableTiming, one per task of a submit, reused
   void* stream_ = nullptr;

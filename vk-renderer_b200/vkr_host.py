@@ -45,6 +45,8 @@ lib.vkr_app_last_tasks.restype = C.c_char_p
 lib.vkr_app_last_tasks.argtypes = [C.c_void_p]
 lib.vkr_app_last_lanes.restype = C.c_char_p
 lib.vkr_app_last_lanes.argtypes = [C.c_void_p]
+lib.vkr_app_frame_graph_stats.restype = C.c_int
+lib.vkr_app_frame_graph_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
 lib.vkr_app_set_option.restype = C.c_int
 lib.vkr_app_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_float]
 
@@ -171,6 +173,12 @@ class App:
     def last_lanes(self):
         """Stream lane (0 or 1) of each task of the last frame, in the order of last_tasks()."""
         return [int(c) for c in lib.vkr_app_last_lanes(self.h).decode()]
+
+    def frame_graph_stats(self):
+        """dict(launches, instantiations, eager_submits, capture_failures) of the rendergraph's submits (include/vkr_host.h)."""
+        out = (C.c_uint64 * 4)()
+        _check(lib.vkr_app_frame_graph_stats(self.h, out))
+        return dict(launches=int(out[0]), instantiations=int(out[1]), eager_submits=int(out[2]), capture_failures=int(out[3]))
 
     def image_desc(self, name):
         d = vkr.VkrImage()
