@@ -40,7 +40,13 @@ struct BlurK {
 #define BLUR_SPAN_X (BLUR_TW + 2 * BLUR_RMAX)
 #define BLUR_PAIRS (BLUR_TH / 2 + BLUR_RMAX)
 #define BLUR_PLANE (BLUR_SPAN_X * BLUR_PAIRS)
-#define BLUR_SMEM_BYTES (BLUR_PLANE * (3 * 16 + 8))
+// BLUR_BLUE_HALF: the {b, b'} plane as half2 (the colours are unorm8 texels: the fp16 error is 0.06 LSB).  57 456 -> 53 352
+// bytes per CTA, which is what lets a FOURTH CTA fit an SM's 228 KB (4 x (56 KB + 1 KB reserved)); with the 64-register cap
+// of BLUR_MIN_CTAS = 4 the barrier-separated phases of the CTAs cover each other's load latency better.
+#ifndef BLUR_BLUE_HALF
+#define BLUR_BLUE_HALF 0
+#endif
+#define BLUR_SMEM_BYTES (BLUR_PLANE * (3 * 16 + (BLUR_BLUE_HALF ? 4 : 8)))
 
 // blur.comp:110-115 — exact depth footprint and z denominator (thresholded downstream), value-only otherwise
 __device__ __forceinline__ f3 world_pos_lod(const Mip& depth1, const Mat4& inv, float u, float v, const CamF& cam) {
@@ -77,7 +83,11 @@ __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0,
   float4* const sA = s_blur;                          // {nx, nx' | ny, ny'}
   float4* const sB = sA + BLUR_PLANE;                 // {nz, nz' | depth, depth'}
   float4* const sC = sB + BLUR_PLANE;                 // {r, r' | g, g'}
+#if BLUR_BLUE_HALF
+  __half2* const sD = (__half2*)(sC + BLUR_PLANE);    // {b, b'} as half2
+#else
   float2* const sD = (float2*)(sC + BLUR_PLANE);      // {b, b'}
+#endif
   __shared__ int s_rmax;
   BlurK kl;
   if (LAYERED) {
@@ -142,7 +152,11 @@ __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0,
     sA[o] = make_float4(v[0][0], v[1][0], v[0][1], v[1][1]);
     sB[o] = make_float4(v[0][2], v[1][2], v[0][3], v[1][3]);
     sC[o] = make_float4(v[0][4], v[1][4], v[0][5], v[1][5]);
+#if BLUR_BLUE_HALF
+    sD[o] = __floats2half2_rn(v[0][6], v[1][6]);
+#else
     sD[o] = make_float2(v[0][6], v[1][6]);
+#endif
   }
   __syncthreads();
 
@@ -170,8 +184,13 @@ __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0,
   const ulonglong2* const pA = (const ulonglong2*)sA;
   const ulonglong2* const pB = (const ulonglong2*)sB;
   const ulonglong2* const pC = (const ulonglong2*)sC;
+#if BLUR_BLUE_HALF
+  const __half2* const pD = sD;
+#define BLUR_LOAD(T, IDX) { (T).A = pA[IDX]; (T).B = pB[IDX]; (T).C = pC[IDX]; const float2 bb = __half22float2(pD[IDX]); (T).D = pk(bb.x, bb.y).v; }
+#else
   const unsigned long long* const pD = (const unsigned long long*)sD;
 #define BLUR_LOAD(T, IDX) { (T).A = pA[IDX]; (T).B = pB[IDX]; (T).C = pC[IDX]; (T).D = pD[IDX]; }
+#endif
   if (__all_sync(0xFFFFFFFFu, r[0] == wr && r[1] == wr)) {
     // every pixel of the warp has the warp's radius (one material under the warp: the common case): the window is
     // the same for all lanes and only its first and last pair can hold a row outside a pixel's -r .. r
