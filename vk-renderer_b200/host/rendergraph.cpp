@@ -223,13 +223,27 @@ void RenderGraph::issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResou
     sync_events_.push_back(e);
   }
   const int n = (int)run.size();
+  // Hazards are keyed on the MEMORY a use touches, not on the slot index: two slots rebound to the same external allocation,
+  // or layer views of one array image, are one resource.
+  std::vector<const void*> res_keys;
+  auto res_index = [&](uint32_t slot) -> size_t {
+    const void* key = slot >= kBufferSlotBase ? buffers[slot - kBufferSlotBase].ptr : slots[slot].desc.base;
+    for (size_t i = 0; i < res_keys.size(); i++) if (res_keys[i] == key) return i;
+    res_keys.push_back(key);
+    return res_keys.size() - 1;
+  };
   const size_t n_res = slots.size() + buffers.size();
-  auto res_index = [&](uint32_t slot) -> size_t { return slot >= kBufferSlotBase ? slots.size() + (slot - kBufferSlotBase) : slot; };
   std::vector<int> last_writer(n_res, -1), lane(n, 0);
   std::vector<std::vector<int>> readers(n_res);
+  int last_barrier = -1;                 // last task that declared nothing: ordered against everything before AND after it
   void* lane_stream[2] = {stream_, aux_stream_};
   int lane_last[2] = {-1, -1};
   bool aux_used = false;
+  // whatever happens below (a task may throw), the second stream is joined back into the graph's stream before we leave
+  struct Join {
+    RenderGraph* g; bool* used; int* last; 
+    ~Join() { if (*used && *last >= 0) { cudaStreamWaitEvent((cudaStream_t)g->stream_, (cudaEvent_t)g->sync_events_[*last], 0); } }
+  } join{this, &aux_used, &lane_last[1]};
   // the aux lane starts after everything already queued on the graph's stream
   cuda_check(cudaEventRecord((cudaEvent_t)sync_events_[n], (cudaStream_t)stream_), "cudaEventRecord");
   cuda_check(cudaStreamWaitEvent((cudaStream_t)aux_stream_, (cudaEvent_t)sync_events_[n], 0), "cudaStreamWaitEvent");
@@ -249,6 +263,7 @@ void RenderGraph::issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResou
       else l = 1 - lane[i - 1];
     }
     if (t.uses.empty()) for (int d = 0; d < i; d++) add(d);
+    add(last_barrier);
     lane[i] = l;
     for (int d : deps)
       if (lane[d] != l) cuda_check(cudaStreamWaitEvent((cudaStream_t)lane_stream[l], (cudaEvent_t)sync_events_[d], 0), "cudaStreamWaitEvent");
@@ -257,6 +272,7 @@ void RenderGraph::issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResou
     cuda_check(cudaEventRecord((cudaEvent_t)sync_events_[i], (cudaStream_t)lane_stream[l]), "cudaEventRecord");
     lane_last[l] = i;
     aux_used |= l == 1;
+    if (t.uses.empty()) last_barrier = i;
     for (const ImageUse& u : t.uses) {
       if (u.write) { last_writer[res_index(u.slot)] = i; readers[res_index(u.slot)].clear(); }
       else readers[res_index(u.slot)].push_back(i);
@@ -264,7 +280,6 @@ void RenderGraph::issue(std::vector<std::unique_ptr<BaseTask>>& run, RenderResou
     last_names.push_back(t.name);
     last_lanes.push_back(l);
   }
-  if (aux_used) cuda_check(cudaStreamWaitEvent((cudaStream_t)stream_, (cudaEvent_t)sync_events_[lane_last[1]], 0), "cudaStreamWaitEvent");
 }
 
 void RenderGraph::wait_idle() { cuda_check(cudaStreamSynchronize((cudaStream_t)stream_), "cudaStreamSynchronize"); }

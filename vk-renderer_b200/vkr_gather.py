@@ -17,7 +17,7 @@ import ctypes as C
 import torch
 
 import vkr
-from vkr_tiles import _P, PeerSlab
+from vkr_tiles import _P, PeerSlab, PeerWaitTimeout, peer_wait_failures_total
 from vkr_views import shard_range
 
 
@@ -27,6 +27,7 @@ class PeerGather:
         any transport: it only carries the 64-byte IPC handles once)."""
         self.n_units, self.row_bytes, self.rank, self.world = n_units, list(row_bytes), rank, world
         self.device, self.timeout = torch.device(device), timeout_ms
+        self._fail_base = peer_wait_failures_total()
         self.first, self.end = shard_range(n_units, world, rank)
         sizes = [n_units * rb for rb in self.row_bytes]
         self.slab = PeerSlab(2 * sum((s + 255) & ~255 for s in sizes), self.device)
@@ -108,10 +109,15 @@ class PeerGather:
         return self.gathered(self.epoch) if self.epoch else self.bufs[0]
 
     def wait_failures(self):
-        return int(_P.vkr_peer_wait_failed())
+        """Timed-out peer waits in this process since this gather was created (synchronises the device)."""
+        return peer_wait_failures_total() - self._fail_base
 
     def close(self, barrier=None):
+        """Joins, releases the slab and RAISES PeerWaitTimeout if any wait gave up (the epochs read after it were stale)."""
         for s in list(self.pstreams.values()) + [self.xfer]:
             s.synchronize()
+        fails = self.wait_failures()
         self.bufs = None
         self.slab.close(barrier)
+        if fails:
+            raise PeerWaitTimeout(f"{fails} peer wait(s) timed out on rank {self.rank}: gathered blocks were stale")

@@ -38,6 +38,28 @@ for _n, _a in [("vkr_peer_alloc", [C.c_uint64, C.POINTER(C.c_void_p)]), ("vkr_pe
     getattr(_P, _n).argtypes = _a
 
 
+class PeerWaitTimeout(RuntimeError):
+    """A stream-side wait for a peer's flag gave up (include/vkr_peer.h): the pass behind it ran on stale halo / gather rows."""
+
+
+class MotionOutOfHalo(RuntimeError):
+    """A frame moved further per frame than the halos of the row-tiled frame were sized for (motion_rows)."""
+
+
+_wait_failures_total = 0
+
+
+def peer_wait_failures_total():
+    """The device-side counter of timed-out waits is read-and-cleared by vkr_peer_wait_failed(); every user of the peer layer in
+    this process (RowTiledFrame, PeerGather) goes through this running total instead, so that they do not steal each other's
+    counts.  Synchronises the device."""
+    global _wait_failures_total
+    n = int(_P.vkr_peer_wait_failed())
+    if n > 0:
+        _wait_failures_total += n
+    return _wait_failures_total
+
+
 class _CudaMem:
     def __init__(self, ptr, nbytes):
         self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
@@ -154,6 +176,9 @@ class RowTiledFrame:
         if self.a >= self.b:
             raise vkr.VkrError(f"rank {rank} of {world} owns no rows of a {w}x{h} frame: use fewer ranks")
         self.halo = dict(rays=1, reflections=11, blurred=2, raw=2, accumulated_ao=motion_rows, taa=2 * motion_rows + 2)
+        self.motion_rows = motion_rows
+        self._fail_base = peer_wait_failures_total()
+        self._vmax = torch.zeros((), dtype=torch.float16, device=device)   # running max |velocity.y| (uv units) of the frames rendered
         self.gb = vkr.Gbuffer(w, h, device=device)
         self.gb.prev_depth.buf.view(torch.int32).fill_(0x00FFFFFF)   # clear_depth(prev_depth, 1.0), src/main.cpp:306
         shared = [("rays", w2, h2, vkr.R16G16B16A16_UNORM), ("raw", w2, h2, vkr.R16G16B16A16_SFLOAT), ("reflections", w2, h2, vkr.R8G8B8A8_UNORM),
@@ -234,6 +259,13 @@ class RowTiledFrame:
         self.epoch += 1
         P = vkr_views.view_params(dp, self.frame, self.counter, gtao_angle_jitter)
         gb, st = self.gb, self.stream
+        # own rows equal the single-GPU frame only while the reprojection reach stays inside the exchanged halos: |velocity.y| <=
+        # motion_rows half-res rows.  Folded into a running maximum on the compute stream (one 2-byte-per-texel reduction, no
+        # host sync); close() / check_motion() compare it with the bound and raise MotionOutOfHalo.
+        v = gb.velocity_vectors
+        with torch.cuda.stream(self._compute_stream()):
+            vy = v.buf[:v.desc.row_pitch[0] * v.height].view(torch.float16).view(v.height, -1)[:, 1:2 * v.width:2]
+            self._vmax = torch.maximum(self._vmax, vy.abs().amax())
         half = vkr.make_ext([], rows=(self.a, self.b))
         full = vkr.make_ext([], rows=self.own_rows(full_res=True))
         self._compute_stream().wait_stream(self.xfer)            # last frame's pushes read images this frame overwrites
@@ -278,7 +310,18 @@ class RowTiledFrame:
         return 2 * self.a, (self.h if self.b >= self.h // 2 else 2 * self.b)
 
     def wait_failures(self):
-        return int(_P.vkr_peer_wait_failed())
+        """Timed-out peer waits in this process since this frame object was created (synchronises the device)."""
+        return peer_wait_failures_total() - self._fail_base
+
+    def motion_rows_seen(self):
+        """Largest |velocity.y| of the frames rendered so far, in half-res rows (synchronises)."""
+        return float(self._vmax.item()) * (self.h // 2)
+
+    def check_motion(self):
+        seen = self.motion_rows_seen()
+        if seen > self.motion_rows:
+            raise MotionOutOfHalo(f"a frame moved {seen:.2f} half-res rows; the halos were sized for motion_rows={self.motion_rows}: "
+                                  f"tile seams read history rows that were never exchanged")
 
     def finish(self):
         """Wait (on the compute stream) for the neighbours' last TAA halo: after this every exchanged row of the last frame is in place."""
@@ -286,9 +329,15 @@ class RowTiledFrame:
             self.wait("taa", self.epoch)
 
     def close(self, barrier=None):
+        """Joins, releases the slab, and RAISES if the sequence was not valid: a peer wait that timed out (PeerWaitTimeout) or
+        motion beyond the halos (MotionOutOfHalo) would otherwise leave a plausible-looking wrong frame behind."""
         torch.cuda.synchronize()
+        fails = self.wait_failures()
         if barrier is not None:
             barrier()                                            # nobody is still pushing into our slab
         self.slab.close(barrier)
+        if fails:
+            raise PeerWaitTimeout(f"{fails} peer wait(s) timed out on rank {self.rank}: halo rows were stale")
+        self.check_motion()
 
     KERNELS_PER_FRAME = 10   # hiz tile + tail, trace, filter, blur, gtao main/filter/accumulate, shading, taa (+ signal/wait kernels)
