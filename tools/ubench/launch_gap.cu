@@ -1,0 +1,95 @@
+// launch_gap.cu — what does a kernel boundary cost on this box?
+// The chain is ~10 dependent kernels per 1.2 ms frame; round-2 scaling runs showed identical kernel times but 0.12 ms more per
+// frame on the 8-GPU box than on the 1- and 2-GPU boxes, at every N.  This measures, on ONE GPU of whatever box it runs on:
+//   (1) N dependent empty kernels on one stream: time per kernel (launch throughput when the host runs ahead);
+//   (2) the same N kernels as one CUDA graph: time per node;
+//   (3) N dependent ~100 us spin kernels, stream and graph: (total - N * kernel time) / N = the gap between dependent kernels;
+//   (4) fork/join: two streams joined by events per pair of kernels (the rendergraph's two lanes), stream and graph.
+// nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench/bin/launch_gap tools/ubench/launch_gap.cu
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
+
+__global__ void empty_kernel() {}
+__global__ void spin_kernel(long long cycles, int* sink) {
+  const long long t0 = clock64();
+  while (clock64() - t0 < cycles) {}
+  if (cycles < 0) *sink = 1;
+}
+
+static float elapsed(cudaEvent_t a, cudaEvent_t b) { float ms; CK(cudaEventElapsedTime(&ms, a, b)); return ms; }
+
+int main() {
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, 0));
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  printf("device %s, %d device(s) visible, %d SMs\n", prop.name, ndev, prop.multiProcessorCount);
+  cudaStream_t s, s2;
+  CK(cudaStreamCreate(&s)); CK(cudaStreamCreate(&s2));
+  cudaEvent_t a, b;
+  CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+  int* sink; CK(cudaMalloc(&sink, 4));
+  const int N = 1000;
+  const dim3 grid(prop.multiProcessorCount * 4), block(128);
+
+  for (int rep = 0; rep < 2; rep++) {                       // second pass is the warm one
+    // (1) stream, empty
+    CK(cudaEventRecord(a, s));
+    for (int i = 0; i < N; i++) empty_kernel<<<grid, block, 0, s>>>();
+    CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float t_stream = elapsed(a, b) * 1e3f / N;
+    // (2) graph, empty
+    cudaGraph_t g; cudaGraphExec_t ge;
+    CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+    for (int i = 0; i < N; i++) empty_kernel<<<grid, block, 0, s>>>();
+    CK(cudaStreamEndCapture(s, &g)); CK(cudaGraphInstantiate(&ge, g, 0));
+    CK(cudaGraphLaunch(ge, s)); CK(cudaStreamSynchronize(s));
+    CK(cudaEventRecord(a, s)); CK(cudaGraphLaunch(ge, s)); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float t_graph = elapsed(a, b) * 1e3f / N;
+    CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g));
+    // (3) ~100 us kernels
+    const long long cyc = (long long)(100e-6 * prop.clockRate * 1e3);
+    const int M = 100;
+    CK(cudaEventRecord(a, s)); spin_kernel<<<grid, block, 0, s>>>(cyc, sink); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    CK(cudaEventRecord(a, s)); spin_kernel<<<grid, block, 0, s>>>(cyc, sink); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float one = elapsed(a, b) * 1e3f;
+    CK(cudaEventRecord(a, s));
+    for (int i = 0; i < M; i++) spin_kernel<<<grid, block, 0, s>>>(cyc, sink);
+    CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float gap_stream = (elapsed(a, b) * 1e3f - M * one) / M;
+    CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+    for (int i = 0; i < M; i++) spin_kernel<<<grid, block, 0, s>>>(cyc, sink);
+    CK(cudaStreamEndCapture(s, &g)); CK(cudaGraphInstantiate(&ge, g, 0));
+    CK(cudaGraphLaunch(ge, s)); CK(cudaStreamSynchronize(s));
+    CK(cudaEventRecord(a, s)); CK(cudaGraphLaunch(ge, s)); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float gap_graph = (elapsed(a, b) * 1e3f - M * one) / M;
+    CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g));
+    // (4) fork / join per pair: s: K ; s2 waits, K ; s waits s2 — the two-lane pattern, M/2 times
+    cudaEvent_t ev[2];
+    CK(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+    auto forkjoin = [&]() {
+      for (int i = 0; i < M / 2; i++) {
+        spin_kernel<<<grid, block, 0, s>>>(cyc, sink);
+        CK(cudaEventRecord(ev[0], s)); CK(cudaStreamWaitEvent(s2, ev[0], 0));
+        spin_kernel<<<grid, block, 0, s2>>>(cyc, sink);
+        CK(cudaEventRecord(ev[1], s2)); CK(cudaStreamWaitEvent(s, ev[1], 0));
+      }
+    };
+    CK(cudaEventRecord(a, s)); forkjoin(); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float gap_fj_stream = (elapsed(a, b) * 1e3f - M * one) / M;
+    CK(cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed));
+    forkjoin();
+    CK(cudaStreamEndCapture(s, &g)); CK(cudaGraphInstantiate(&ge, g, 0));
+    CK(cudaGraphLaunch(ge, s)); CK(cudaStreamSynchronize(s));
+    CK(cudaEventRecord(a, s)); CK(cudaGraphLaunch(ge, s)); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+    const float gap_fj_graph = (elapsed(a, b) * 1e3f - M * one) / M;
+    CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g));
+    if (rep == 1)
+      printf("empty kernel: %.2f us each in a stream, %.2f us each in a graph | gap between dependent ~%.0f us kernels: stream %.2f us, graph %.2f us | "
+             "across two streams (event fork/join): stream %.2f us, graph %.2f us\n", t_stream, t_graph, one, gap_stream, gap_graph, gap_fj_stream, gap_fj_graph);
+  }
+  return 0;
+}
