@@ -68,13 +68,24 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+    """Samples SM clock and throttle reasons through NVML while the timed region runs.
+
+    NVML queries take the driver's global lock, which the submission path of EVERY process on the box also needs: in round 1
+    (and in this round's first 8-GPU run) every rank polled its GPU every 5 ms and the replica workload lost 9 % at N >= 4 with
+    unchanged kernel times and clocks (profiles/r02l_*, r02n_*).  So: only rank 0 samples (its own GPU; the line it prints is
+    the only consumer), every BENCH_CLOCK_INTERVAL_MS (default 20 ms), and BENCH_CLOCKS=off/all-ranks-5ms reproduce the A/B."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.reasons, self.max_mhz, self.stop_flag = index, [], set(), None, False
+        mode = os.environ.get("BENCH_CLOCKS", "rank0")
+        self.interval = float(os.environ.get("BENCH_CLOCK_INTERVAL_MS", "5" if mode == "all-ranks-5ms" else "20")) * 1e-3
+        self.enabled = mode != "off" and (mode == "all-ranks-5ms" or int(os.environ.get("RANK", 0)) == 0)
 
     def run(self):
+        if not self.enabled:
+            self.reasons.add("not_sampled_on_this_rank")
+            return
         try:
             import pynvml as nv
             nv.nvmlInit()
@@ -90,7 +101,7 @@ class ClockSampler(threading.Thread):
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
-                time.sleep(0.005)       # NVML queries take driver locks the launch path also wants: sample sparsely
+                time.sleep(self.interval)
         except Exception as e:  # NVML missing: report that instead of inventing numbers
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
 
