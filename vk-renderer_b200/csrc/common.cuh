@@ -404,6 +404,11 @@ __device__ __forceinline__ f3 sample_gbuffer_normal_fast(const Mip& m, float u, 
   return decode_normal_fast(e.x, e.y);
 }
 
+// t / d for a run-time d in staging loops: q = umulhi(t, ceil(2^32 / d)) is the exact quotient while t < 2^16 and d < 2^16
+// (two instructions instead of the ~20 of the generic 32-bit division; gtao.cu spent 5 % of its issue slots on one of those).
+__device__ __forceinline__ uint32_t div_magic(uint32_t d) { return 0xFFFFFFFFu / d + 1u; }        // d = 1 wraps to 0: see div_small
+__device__ __forceinline__ int div_small(int t, uint32_t magic) { return magic ? (int)__umulhi((uint32_t)t, magic) : t; }
+
 // ---- texel encode ----------------------------------------------------------------
 __device__ __forceinline__ uint32_t to_unorm(float v, float maxv) {   // clamp, NaN -> 0, floor(v*max + 0.5)
   if (!(v > 0.0f)) return 0u;

@@ -145,8 +145,9 @@ __global__ void __launch_bounds__(256, GTAO_MIN_CTAS) gtao_main_kernel(GtaoK k0,
   const int bw = s_box[2] - tile.ox + 1, bh = s_box[3] - tile.oy + 1;
   const bool use_tile = s_box[2] >= tile.ox && bw <= GT_SW && bh <= GT_SH && s_box[3] >= tile.oy;
   if (use_tile) {
+    const uint32_t bw_magic = div_magic((uint32_t)bw);                      // bw * bh <= GT_SW * GT_SH < 2^16
     for (int t = threadIdx.x; t < bw * bh; t += 256) {
-      const int ly = t / bw, lx = t - ly * bw;
+      const int ly = div_small(t, bw_magic), lx = t - ly * bw;
       const int qx = min(max(tile.ox + lx, 0), depth.w - 1), qy = min(max(tile.oy + ly, 0), depth.h - 1);   // clamp-to-edge per index
       s_tile[ly * GT_SW + lx] = d24_to_float(ld32(depth, qx, qy));
     }

@@ -131,8 +131,9 @@ __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0,
 
   // stage {normal, depth} and colour for every tap position of the tile, two rows per item
   const int ox = blockIdx.x * BLUR_TW - R, oy = VKR_BLOCK_Y * BLUR_TH - R;
+  const uint32_t span_magic = div_magic((uint32_t)span_x);             // span_x * pairs <= 54 * 19
   for (int t = threadIdx.x; t < span_x * pairs; t += 256) {
-    const int P = t / span_x, lx = t - P * span_x;
+    const int P = div_small(t, span_magic), lx = t - P * span_x;
     const int qx = ox + lx;
     float v[2][7];
 #pragma unroll
