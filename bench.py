@@ -143,6 +143,12 @@ def cpu_chain_rate(width, height, frames, warm, threads=0):
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    # This arm measures the CPU side only: lay out images and produce the input G-buffers with oracle/libvkr_hostonly.so (the
+    # same host helpers compiled without device code) so that the process never loads libvkr_b200.so.
+    os.environ["VKR_HOST_ONLY"] = "1"
+    if not os.path.exists(os.path.join(ROOT, "oracle", "libvkr_hostonly.so")):
+        import subprocess
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "libvkr_hostonly.so"], check=True, capture_output=True)
     gpix, ms, threads, band_rows = cpu_chain_rate(args.width, args.height, args.steps, args.warmup, threads=host_threads())
     sample = (f"each step = rows [{int(BAND[0]*args.height)}, {int(BAND[1]*args.height)}) of one {args.width}x{args.height} frame through every pass "
               f"({band_rows} of {args.height} rows; Hi-Z built in full), OpenMP over rows")
@@ -152,6 +158,7 @@ def run_reference(args, rank, world):
             "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {args.width}x{args.height} TAA sequence", "sample": sample},
             "cpu_baseline": {"value": gpix, "unit": "Gpix/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": gpix, "unit": "Gpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "native_libraries": sorted({os.path.relpath(ln.split()[-1], ROOT) for ln in open("/proc/self/maps") if "/libvkr" in ln or "/liboracle" in ln}),
             "note": "the reference's GLSL cannot run here (no Vulkan / glslc): this is the CPU restatement of its shaders (oracle/)"}
     print(json.dumps(line))
 

@@ -168,3 +168,42 @@ def test_misaligned_or_short_pitched_images_are_refused():
     pd, d, vel = img(vkr.D24_UNORM_S8_UINT), img(vkr.D24_UNORM_S8_UINT), img(vkr.R16G16_SFLOAT)
     rc = L.vkr_taa_resolve(C.byref(vkr.TaaParams()), hist.ptr, pd.ptr, d.ptr, vel.ptr, tight.ptr, out.ptr, None)
     assert rc == INVALID and b"image layout: row_pitch[0] = 120" in L.vkr_last_error(), (rc, L.vkr_last_error())
+
+
+def test_cpu_arm_never_loads_the_product_library(tmp_path):
+    """bench.py --impl reference lays out images and produces its input G-buffers through oracle/libvkr_hostonly.so (the host
+    helpers of csrc/api.cu, synth.cu, synth_scene.cu compiled by g++ with VKR_HOST_ONLY: no device code, no CUDA runtime call).
+    The process must map that and liboracle.so only, the twin must write the bytes the product's host twin writes, and a
+    compute entry must raise instead of silently doing nothing."""
+    import subprocess
+    import sys
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "libvkr_hostonly.so"], check=True, capture_output=True)
+    code = r"""
+import json, os, sys
+sys.argv = ['bench.py', '--impl', 'reference', '--steps', '1', '--warmup', '0', '--width', '256', '--height', '144']
+sys.path.insert(0, %r)
+import runpy
+runpy.run_path(os.path.join(%r, 'bench.py'), run_name='__main__')
+maps = open('/proc/self/maps').read()
+assert 'libvkr_b200' not in maps and 'libvkr_host.so' not in maps, 'product library mapped in the CPU arm'
+assert 'libvkr_hostonly.so' in maps and 'liboracle.so' in maps
+import vkr, numpy as np
+try:
+    vkr.lib.vkr_taa_resolve(None)
+    raise SystemExit('compute entry did not raise')
+except RuntimeError:
+    pass
+gb = vkr.Gbuffer(96, 64, device='cpu')
+vkr.synth_gbuffer(vkr.synth_scene(1, 16), vkr.synth_camera(1, 2, 96, 64, True), gb)
+np.save(%r, np.concatenate([i.buf.numpy() for i in gb.input_images()]))
+""" % (ROOT, ROOT, str(tmp_path / "ho.npy"))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env={**os.environ, "OMP_NUM_THREADS": "2"})
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+    import json
+    assert json.loads(line)["native_libraries"] == ["oracle/liboracle.so", "oracle/libvkr_hostonly.so"]
+    import numpy as np
+    import vkr
+    gb = vkr.Gbuffer(96, 64, device="cpu")
+    vkr.synth_gbuffer(vkr.synth_scene(1, 16), vkr.synth_camera(1, 2, 96, 64, True), gb)
+    assert np.array_equal(np.load(tmp_path / "ho.npy"), np.concatenate([i.buf.numpy() for i in gb.input_images()]))

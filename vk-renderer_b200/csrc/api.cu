@@ -29,6 +29,17 @@ void set_error(const char* fmt, ...) {
   }
 }
 
+// VKR_HOST_ONLY (oracle/Makefile, target libvkr_hostonly.so, compiled by g++): the layout / table / producer-twin helpers
+// without any device code or CUDA runtime call, so that bench.py's CPU arm can build its inputs without loading the product
+// library.  Never defined in the product build.
+CamK make_cam(float fovy, float aspect, float znear, float zfar) {
+  CamK c;
+  c.aspect = aspect; c.znear = znear; c.zfar = zfar;
+  c.tg = std::tan(fovy / 2);  // gbuffer_encode.glsl:60,:76 — hoisted, same float the shader would form
+  return c;
+}
+
+#ifndef VKR_HOST_ONLY
 int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
@@ -72,13 +83,6 @@ int upload_params(const void* host, size_t elem, int count, void* scratch, cudaS
   return VKR_OK;
 }
 
-CamK make_cam(float fovy, float aspect, float znear, float zfar) {
-  CamK c;
-  c.aspect = aspect; c.znear = znear; c.zfar = zfar;
-  c.tg = std::tan(fovy / 2);  // gbuffer_encode.glsl:60,:76 — hoisted, same float the shader would form
-  return c;
-}
-
 // sRGB EOTF table, built in double precision on the host, one copy per device.
 static std::mutex g_tab_mutex;
 static float* g_srgb_dev[64] = {nullptr};
@@ -111,10 +115,13 @@ __global__ void selftest_decode_kernel(unsigned long long* mismatches) {
   if (bad) atomicAdd(mismatches, (unsigned long long)bad);
 }
 
+#endif  // !VKR_HOST_ONLY
+
 }  // namespace vkr
 
 extern "C" {
 
+#ifndef VKR_HOST_ONLY
 /* Test hook: number of inputs for which the fast unorm decode differs from __fdiv_rn (must be 0);
  * negative on a CUDA error. */
 long long vkr_selftest_decode(void) {
@@ -128,6 +135,7 @@ long long vkr_selftest_decode(void) {
   if (e != cudaSuccess) { vkr::set_error("selftest_decode: %s", cudaGetErrorString(e)); return -1; }
   return (long long)h;
 }
+#endif  // !VKR_HOST_ONLY
 
 const char* vkr_version(void) { return "vkr_b200 0.1 (sm_100a)"; }
 const char* vkr_last_error(void) { return vkr::g_err; }

@@ -9,7 +9,9 @@
 // (__fmul_rn/__fsub_rn) so the discrete choice is identical to an unfused evaluation.
 #pragma once
 #include <cuda_runtime.h>
+#ifdef __CUDACC__
 #include "f32x2.cuh"
+#endif
 #include <cuda_fp16.h>
 #include <stdint.h>
 #include "../../include/vkr_passes.h"

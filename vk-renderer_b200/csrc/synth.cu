@@ -144,6 +144,7 @@ __host__ __device__ inline SynthOut synth_pixel(const VkrSynthScene& sc, const S
   return out;
 }
 
+#ifndef VKR_HOST_ONLY   // device side: absent from oracle/libvkr_hostonly.so (see api.cu)
 __global__ void __launch_bounds__(256) synth_kernel(const VkrSynthScene* __restrict__ scene_g, SynthFrameK f, Mip albedo, Mip normal, Mip material, Mip velocity, Mip depth) {
   __shared__ VkrSynthScene sc;
   for (int i = threadIdx.x; i < (int)(sizeof(VkrSynthScene) / 4); i += blockDim.x) ((uint32_t*)&sc)[i] = ((const uint32_t*)scene_g)[i];
@@ -184,6 +185,8 @@ __global__ void __launch_bounds__(256) synth_cube_kernel(const VkrSynthScene* __
   *((__half*)(dist.p + (size_t)face * dist.ls + (size_t)y * dist.pitch) + x) = __float2half_rn(distance);
 }
 
+#endif  // !VKR_HOST_ONLY
+
 static int synth_check(const VkrSynthScene* scene, const VkrDrawTAAParams* p, const VkrImage* albedo, const VkrImage* normal,
                        const VkrImage* material, const VkrImage* velocity, const VkrImage* depth) {
   if (!scene || !p || scene->object_count > VKR_SYNTH_MAX_OBJECTS || !image_ok(albedo, VKR_FORMAT_R8G8B8A8_SRGB) ||
@@ -216,6 +219,7 @@ static SynthFrameK make_frame(const VkrDrawTAAParams* p, uint32_t w, uint32_t h)
 }  // namespace vkr
 using namespace vkr;
 
+#ifndef VKR_HOST_ONLY
 extern "C" int vkr_synth_gbuffer(const VkrSynthScene* scene, const VkrDrawTAAParams* p, const VkrImage* albedo, const VkrImage* normal,
                                  const VkrImage* material, const VkrImage* velocity, const VkrImage* depth, void* stream) {
   int rc = synth_check(scene, p, albedo, normal, material, velocity, depth);
@@ -231,6 +235,7 @@ extern "C" int vkr_synth_gbuffer(const VkrSynthScene* scene, const VkrDrawTAAPar
   cudaFreeAsync(dscene, st);
   return rc;
 }
+#endif  // !VKR_HOST_ONLY
 
 extern "C" int vkr_synth_gbuffer_host(const VkrSynthScene* scene, const VkrDrawTAAParams* p, const VkrImage* albedo, const VkrImage* normal,
                                       const VkrImage* material, const VkrImage* velocity, const VkrImage* depth, int threads) {
@@ -258,6 +263,7 @@ extern "C" int vkr_synth_gbuffer_host(const VkrSynthScene* scene, const VkrDrawT
   return VKR_OK;
 }
 
+#ifndef VKR_HOST_ONLY
 extern "C" int vkr_synth_cubemap(const VkrSynthScene* scene, const float* position3, const VkrImage* cube_color, uint64_t color_face_stride,
                                  const VkrImage* cube_distance, uint64_t distance_face_stride, void* stream) {
   if (!scene || !position3 || scene->object_count > VKR_SYNTH_MAX_OBJECTS || !image_ok(cube_color, VKR_FORMAT_R8G8B8A8_SRGB) ||
@@ -282,3 +288,4 @@ extern "C" int vkr_synth_cubemap(const VkrSynthScene* scene, const float* positi
   cudaFreeAsync(dscene, st);
   return rc;
 }
+#endif  // !VKR_HOST_ONLY

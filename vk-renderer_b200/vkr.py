@@ -10,11 +10,40 @@ import numpy as np
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("VKR_B200_LIB") or os.path.join(_HERE, "libvkr_b200.so")   # override: kernel-variant experiments (tools/variant.sh)
+# VKR_HOST_ONLY=1 (set only by bench.py's CPU arm): bind oracle/libvkr_hostonly.so -- the layout / Halton / producer-twin helpers
+# compiled without any device code -- so that a process that measures the CPU side never loads the product library.  Every other
+# entry then raises on call.  Without that variable a missing product library is an ImportError: there is no fallback.
+HOST_ONLY = os.environ.get("VKR_HOST_ONLY") == "1"
+if HOST_ONLY:
+    LIB_PATH = os.path.join(os.path.dirname(_HERE), "oracle", "libvkr_hostonly.so")
+else:
+    LIB_PATH = os.environ.get("VKR_B200_LIB") or os.path.join(_HERE, "libvkr_b200.so")   # override: kernel-variant experiments (tools/variant.sh)
 if not os.path.exists(LIB_PATH):
     raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                       "(there is no CPU fallback for the vkr passes)")
-lib = C.CDLL(LIB_PATH)
+
+
+class _HostOnlyLib:
+    """The host-only library: symbols it lacks (every compute entry) become stubs that raise when called."""
+
+    def __init__(self, cdll):
+        object.__setattr__(self, "_cdll", cdll)
+
+    def __getattr__(self, name):
+        try:
+            f = getattr(self._cdll, name)
+        except AttributeError:
+            class _Missing:
+                restype = argtypes = None
+
+                def __call__(self, *a, **k):
+                    raise RuntimeError(f"{name} is not part of oracle/libvkr_hostonly.so (VKR_HOST_ONLY=1: no device code in this process)")
+            f = _Missing()
+        object.__setattr__(self, name, f)
+        return f
+
+
+lib = _HostOnlyLib(C.CDLL(LIB_PATH)) if HOST_ONLY else C.CDLL(LIB_PATH)
 
 # VkFormat values (include/vkr_passes.h VkrFormat)
 R8_UNORM, R8G8B8A8_UNORM, R8G8B8A8_SRGB = 9, 37, 43
