@@ -163,20 +163,58 @@ def run_reference(args, rank, world):
     print(json.dumps(line))
 
 
+_NCCL_GROUP = None
+
+
 def init_dist(args, world):
-    """One process per GPU; the NCCL group is created once per process whichever workloads follow."""
+    """One process per GPU.  The DEFAULT group is gloo: barriers and max-over-ranks carry no GPU data.  NCCL is created lazily
+    (nccl_group) by the one workload that really gathers device tensors, the probe batch.
+
+    Why: measured on the 8-GPU box this round (profiles/r02l, r02n, r02o): with an NCCL communicator of >= 4 ranks merely
+    INITIALISED in the process, the replica workload -- which exchanges nothing -- ran at 1.30-1.32 ms/frame instead of 1.18,
+    with identical kernel times and clocks (only the gaps between dependent kernels grew, ~12 us each; NVML sampling, NVLS and
+    P2P on/off made no difference), while eight independent processes without NCCL ran at 1.184 ms on every GPU.
+    BENCH_CONTROL=nccl restores the old behaviour for the A/B."""
     import torch
     import torch.distributed as dist
     local = int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", 0)))
     torch.cuda.set_device(local)
     if world > 1 and not dist.is_initialized():
-        opts = None
-        if args.nccl_max_ctas > 0:
-            opts = dist.ProcessGroupNCCL.Options()
-            opts.config.max_ctas = args.nccl_max_ctas
-            opts.config.min_ctas = min(args.nccl_max_ctas, 1)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
+        if os.environ.get("BENCH_CONTROL", "gloo") == "nccl":
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=_nccl_options(args))
+        else:
+            dist.init_process_group("gloo")
     return local
+
+
+def _nccl_options(args):
+    import torch.distributed as dist
+    if args.nccl_max_ctas <= 0:
+        return None
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.config.max_ctas = args.nccl_max_ctas
+    opts.config.min_ctas = min(args.nccl_max_ctas, 1)
+    return opts
+
+
+def nccl_group(args):
+    """The NCCL group for device-tensor collectives (None = the default group when that already is NCCL)."""
+    global _NCCL_GROUP
+    import torch.distributed as dist
+    if dist.get_backend() == "nccl":
+        return None
+    if _NCCL_GROUP is None:
+        _NCCL_GROUP = dist.new_group(backend="nccl", pg_options=_nccl_options(args))
+    return _NCCL_GROUP
+
+
+def reduce_max(values):
+    """MAX over ranks of a list of floats through the default (control) group."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor(values, dtype=torch.float64, device="cuda" if dist.get_backend() == "nccl" else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t.tolist()]
 
 
 def csrc_sha16():
@@ -230,9 +268,7 @@ def run_ours(args, rank, world):
     def max_over_ranks(x):
         if world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return reduce_max([x])[0]
 
     # ---- device-resident throughput: value ------------------------------------------------------------------------
     def step_resident(i):
@@ -376,7 +412,9 @@ def run_ours(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {w}x{h} TAA sequence with synthetic velocity (BASELINE configs[2])",
                        "frames_resident": nres, "l2": "inputs larger than L2 (one frame touches > 1 GB at 4K)",
-                       "parallelism": f"{world} independent sequence(s), one per GPU"},
+                       "parallelism": f"{world} independent sequence(s), one per GPU; control plane (barrier, max over ranks) on "
+                                      f"{os.environ.get('BENCH_CONTROL', 'gloo')}: nothing is exchanged, and an initialised NCCL communicator of >= 4 ranks "
+                                      f"costs this workload ~10 % (bench.py init_dist)"},
             "roofline": {"bound": "hbm", "kernel": dname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_stale": traffic_stale, "traffic_captured_at": traffic_captured,
                          "peak_source": peak_src, "avg_launch_ms": avg_ms,
@@ -449,6 +487,7 @@ def run_probes(args, rank, world, emit=True):
         vb.blurred, vb.blurred_history = vb.blurred_history, vb.blurred
         vb.accumulated_ao, vb.accumulated_history = vb.accumulated_history, vb.accumulated_ao
 
+    gather_group = nccl_group(args) if (world > 1 and args.probes_gather == "allgather") else None
     pg = None
     if world > 1 and args.probes_gather == "p2p":
         import vkr_gather
@@ -467,8 +506,8 @@ def run_probes(args, rank, world, emit=True):
             done.record(stream)
             side.wait_event(done)
             with torch.cuda.stream(side):
-                vkr_views.gather_blocks(ao, args.views, out=gout[0])
-                vkr_views.gather_blocks(refl, args.views, out=gout[1])
+                vkr_views.gather_blocks(ao, args.views, group=gather_group, out=gout[0])
+                vkr_views.gather_blocks(refl, args.views, group=gather_group, out=gout[1])
 
     def step(i):
         """Steps 0..nres-1 run eagerly, steps nres..2*nres-1 are captured into one CUDA graph each (the image bindings repeat
@@ -520,9 +559,7 @@ def run_probes(args, rank, world, emit=True):
         barrier()
     ms = e0.elapsed_time(e1)
     if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+        ms = reduce_max([ms])[0]
     sampler.join(timeout=1.0)
     gather_timeouts = 0
     if pg is not None:
@@ -613,6 +650,8 @@ def run_tiles(args, rank, world, emit=True):
         dist.all_gather_object(spans, (y0, y1))
     done = torch.cuda.Event()
 
+    rows_group = nccl_group(args) if (world > 1 and args.tiles_gather == "rank0") else None
+
     def rows_of(img, r0, r1):
         pitch = img.desc.row_pitch[0]
         return img.buf[r0 * pitch:r1 * pitch]
@@ -629,9 +668,9 @@ def run_tiles(args, rank, world, emit=True):
             with torch.cuda.stream(side):
                 if rank == 0:
                     for r in range(1, world):
-                        dist.recv(rows_of(out, *spans[r]), src=r)
+                        dist.recv(rows_of(out, *spans[r]), src=r, group=rows_group)
                 else:
-                    dist.send(rows_of(out, y0, y1), dst=0)
+                    dist.send(rows_of(out, y0, y1), dst=0, group=rows_group)
 
     def barrier():
         torch.cuda.synchronize()
@@ -659,9 +698,8 @@ def run_tiles(args, rank, world, emit=True):
     ms = e0.elapsed_time(e1)
     fails = tf.wait_failures()
     if world > 1:
-        t = torch.tensor([ms, float(fails)], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, fails = float(t[0].item()), int(t[1].item())
+        ms, fails = reduce_max([ms, float(fails)])
+        fails = int(fails)
     sampler.join(timeout=1.0)
     tf.close(dist.barrier if world > 1 else None)
     halo = tf.halo
@@ -705,7 +743,7 @@ def sub_records(args, rank, world):
     out = {}
     sub = argparse.Namespace(**vars(args))
     sub.steps, sub.warmup = SUB_STEPS, SUB_WARMUP
-    for name, fn in (("probes", run_probes), ("tiles", run_tiles)):
+    for name, fn in (("tiles", run_tiles), ("probes", run_probes)):     # tiles first: it needs no NCCL, and NCCL's presence costs ~10 %
         solo = None
         if world > 1:
             if rank == 0:
