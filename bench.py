@@ -248,6 +248,9 @@ def run_ours(args, rank, world):
     npix = w * h
     stream = torch.cuda.Stream()
     app = vkr_host.App(w, h, device=local, stream=stream)
+    for opt in filter(None, os.environ.get("BENCH_APP_OPTIONS", "").split(",")):     # e.g. graph.concurrent_branches=0,graph.frame_graph=0 (experiments)
+        name, val = opt.split("=")
+        app.set_option(name, float(val))
     scene = vkr.synth_scene(rank, 64)                     # every rank renders its own sequence
     nres = min(64, K + W)                                 # distinct frames of the sequence kept resident (wraps after 64)
     seq_params = [vkr.synth_camera(rank, f, w, h, True) for f in range(nres)]

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <unistd.h>
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
 
@@ -21,7 +22,7 @@ __global__ void spin_kernel(long long cycles, int* sink) {
 
 static float elapsed(cudaEvent_t a, cudaEvent_t b) { float ms; CK(cudaEventElapsedTime(&ms, a, b)); return ms; }
 
-int main() {
+int main(int argc, char** argv) {
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, 0));
   int ndev = 0;
@@ -35,7 +36,12 @@ int main() {
   const int N = 1000;
   const dim3 grid(prop.multiProcessorCount * 4), block(128);
 
-  for (int rep = 0; rep < 2; rep++) {                       // second pass is the warm one
+  // optional argv[1] = repetitions (default 2; the last one is reported; with several copies of this program started together on
+  // different GPUs a larger count keeps them overlapping) and argv[2] = a file to wait for (common start)
+  const int reps = argc > 1 ? atoi(argv[1]) : 2;
+  if (argc > 2) { while (access(argv[2], F_OK) != 0) usleep(1000); }
+  float acc[6] = {0, 0, 0, 0, 0, 0};
+  for (int rep = 0; rep < reps; rep++) {                    // the first pass is the cold one
     // (1) stream, empty
     CK(cudaEventRecord(a, s));
     for (int i = 0; i < N; i++) empty_kernel<<<grid, block, 0, s>>>();
@@ -87,9 +93,12 @@ int main() {
     CK(cudaEventRecord(a, s)); CK(cudaGraphLaunch(ge, s)); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
     const float gap_fj_graph = (elapsed(a, b) * 1e3f - M * one) / M;
     CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g));
-    if (rep == 1)
-      printf("empty kernel: %.2f us each in a stream, %.2f us each in a graph | gap between dependent ~%.0f us kernels: stream %.2f us, graph %.2f us | "
-             "across two streams (event fork/join): stream %.2f us, graph %.2f us\n", t_stream, t_graph, one, gap_stream, gap_graph, gap_fj_stream, gap_fj_graph);
+    if (rep >= 1) { acc[0] += t_stream; acc[1] += t_graph; acc[2] += gap_stream; acc[3] += gap_graph; acc[4] += gap_fj_stream; acc[5] += gap_fj_graph; }
+    if (rep == reps - 1) {
+      const float n = (float)(reps - 1);
+      printf("mean of %d passes | empty kernel: %.2f us each in a stream, %.2f us each in a graph | extra time per dependent ~%.0f us kernel: stream %.2f us, graph %.2f us | "
+             "across two streams (event fork/join): stream %.2f us, graph %.2f us\n", reps - 1, acc[0] / n, acc[1] / n, one, acc[2] / n, acc[3] / n, acc[4] / n, acc[5] / n);
+    }
   }
   return 0;
 }
