@@ -288,12 +288,15 @@ def run_ours(args, rank, world):
     # branches (SSR filter + blur | GTAO main, filter, accumulate) on two streams, so tasks overlap.
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
+    t_host0 = time.perf_counter()
     for i in range(W, W + K):
         step_resident(i)
+    host_ms = (time.perf_counter() - t_host0) * 1e3 / K       # CPU time to ENQUEUE one frame (not a GPU time): >= the GPU frame time means host-bound
     e1.record(stream)
     stream.synchronize()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
+    host_ms = max_over_ranks(host_ms)
     lanes = dict(zip(app.last_tasks(), app.last_lanes()))
     # Per-task durations need tasks that do not overlap: K more frames of the same sequence with task timing on, which puts
     # every task on the one stream with an event pair around it (these frames are not part of `value`).
@@ -380,6 +383,7 @@ def run_ours(args, rank, world):
                "d2h_bytes_per_step": d2h, "note": "pinned host G-buffer -> device (copy stream) -> vkr_app_bind_gbuffer -> render_frame -> TAA target -> pinned host "
                                                   "(read-back stream); three device G-buffers rotate so both PCIe directions overlap the chain"}
 
+    fg_stats = app.frame_graph_stats()
     app.close()
     del resident, app
     torch.cuda.empty_cache()
@@ -427,7 +431,8 @@ def run_ours(args, rank, world):
                          "per_task_source": f"{K} further frames with task timing on: one stream, an event pair around every task, "
                                             f"{ms_serial:.4f} ms/frame; in the timed region the rendergraph overlaps tasks on two streams",
                          "task_lanes": lanes},
-            "gpu_launches": KERNELS_PER_FRAME * K, "clocks": clocks}
+            "gpu_launches": KERNELS_PER_FRAME * K, "clocks": clocks,
+            "host_enqueue_ms_per_frame": host_ms, "frame_graph": fg_stats}
     if e2e:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
