@@ -282,6 +282,8 @@ def run_ours(args, rank, world):
     for i in range(W):
         step_resident(i)
     barrier()
+    if os.environ.get("BENCH_STAGGER_S"):                   # experiment: ranks run their timed regions one after the other
+        time.sleep(float(os.environ["BENCH_STAGGER_S"]) * rank)
     sampler = ClockSampler(local)
     sampler.start()
     # Timed region: EXACTLY K frames the way the host API runs them — the rendergraph issues the frame's independent

@@ -14,6 +14,10 @@
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1); } } while (0)
 
 __global__ void empty_kernel() {}
+// streams `n` float4 through the SMs: read + write, ~2 * 16 * n bytes of HBM traffic (a stand-in for the chain's kernels)
+__global__ void __launch_bounds__(256) copy_kernel(const float4* __restrict__ a, float4* __restrict__ b, size_t n) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) { float4 v = a[i]; v.x += 1.0f; b[i] = v; }
+}
 __global__ void spin_kernel(long long cycles, int* sink) {
   const long long t0 = clock64();
   while (clock64() - t0 < cycles) {}
@@ -93,6 +97,21 @@ int main(int argc, char** argv) {
     CK(cudaEventRecord(a, s)); CK(cudaGraphLaunch(ge, s)); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
     const float gap_fj_graph = (elapsed(a, b) * 1e3f - M * one) / M;
     CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g));
+    // (5) memory-streaming kernels (256 MB read + 256 MB written each, ~85 us): 100 dependent launches, ping-pong buffers
+    {
+      static float4 *bufA = nullptr, *bufB = nullptr;
+      const size_t n = (size_t)16 << 20;
+      if (!bufA) { CK(cudaMalloc(&bufA, n * 16)); CK(cudaMalloc(&bufB, n * 16)); CK(cudaMemset(bufA, 0, n * 16)); }
+      const dim3 cg(prop.multiProcessorCount * 8);
+      CK(cudaEventRecord(a, s)); copy_kernel<<<cg, 256, 0, s>>>(bufA, bufB, n); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+      CK(cudaEventRecord(a, s)); copy_kernel<<<cg, 256, 0, s>>>(bufA, bufB, n); CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+      const float onec = elapsed(a, b) * 1e3f;
+      CK(cudaEventRecord(a, s));
+      for (int i = 0; i < M; i++) copy_kernel<<<cg, 256, 0, s>>>((i & 1) ? bufB : bufA, (i & 1) ? bufA : bufB, n);
+      CK(cudaEventRecord(b, s)); CK(cudaEventSynchronize(b));
+      const float tot = elapsed(a, b) * 1e3f;
+      if (rep == reps - 1) printf("memory-streaming kernel: %.1f us alone, %.1f us each in a chain of %d dependent launches (extra %.2f us per launch)\n", onec, tot / M, M, tot / M - onec);
+    }
     if (rep >= 1) { acc[0] += t_stream; acc[1] += t_graph; acc[2] += gap_stream; acc[3] += gap_graph; acc[4] += gap_fj_stream; acc[5] += gap_fj_graph; }
     if (rep == reps - 1) {
       const float n = (float)(reps - 1);
