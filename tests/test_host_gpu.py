@@ -146,3 +146,20 @@ def test_frame_graph_frames_equal_eagerly_issued_frames(cuda):
     assert sa["instantiations"] <= 2, sa                      # the ping-pong swap must be absorbed by the update, not by re-instantiating
     assert sb["launches"] == 0 and sb["eager_submits"] >= frames
     a.close(); b.close()
+
+
+def test_rendergraph_barrier_task_orders_both_ways(cuda, tmp_path):
+    """tests/cpp/rendergraph_barrier.cpp against libvkr_host.so: a task that declares no uses sits between a declared writer and
+    a declared reader (which would otherwise go to the second stream), and a reader through a second slot rebound to the same
+    allocation must see the write (hazards keyed on memory) -- eager on the first frame, through the frame graph afterwards."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "vk-renderer_b200")
+    exe = str(tmp_path / "rg_barrier")
+    subprocess.run(["nvcc", "-std=c++17", "-O2", "-x", "cu", os.path.join(root, "tests", "cpp", "rendergraph_barrier.cpp"), "-I", os.path.join(pkg, "host"),
+                    "-I", os.path.join(root, "include"), "-L", pkg, "-lvkr_host", "-lvkr_b200", "-Xlinker", "-rpath", "-Xlinker", pkg, "-o", exe],
+                   check=True, capture_output=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    print(r.stdout)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout + r.stderr
