@@ -68,12 +68,9 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons through NVML while the timed region runs.
-
-    NVML queries take the driver's global lock, which the submission path of EVERY process on the box also needs: in round 1
-    (and in this round's first 8-GPU run) every rank polled its GPU every 5 ms and the replica workload lost 9 % at N >= 4 with
-    unchanged kernel times and clocks (profiles/r02l_*, r02n_*).  So: only rank 0 samples (its own GPU; the line it prints is
-    the only consumer), every BENCH_CLOCK_INTERVAL_MS (default 20 ms), and BENCH_CLOCKS=off/all-ranks-5ms reproduce the A/B."""
+    """Samples SM clock and throttle reasons through NVML while the timed region runs.  Only rank 0 samples (its own GPU; the
+    line it prints is the only consumer), every BENCH_CLOCK_INTERVAL_MS (default 20 ms); BENCH_CLOCKS=off / all-ranks-5ms exist
+    for the A/B that showed sampling does not affect the result (profiles/r02n_scale8_sampler_ab.txt)."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
@@ -167,14 +164,11 @@ _NCCL_GROUP = None
 
 
 def init_dist(args, world):
-    """One process per GPU.  The DEFAULT group is gloo: barriers and max-over-ranks carry no GPU data.  NCCL is created lazily
-    (nccl_group) by the one workload that really gathers device tensors, the probe batch.
-
-    Why: measured on the 8-GPU box this round (profiles/r02l, r02n, r02o): with an NCCL communicator of >= 4 ranks merely
-    INITIALISED in the process, the replica workload -- which exchanges nothing -- ran at 1.30-1.32 ms/frame instead of 1.18,
-    with identical kernel times and clocks (only the gaps between dependent kernels grew, ~12 us each; NVML sampling, NVLS and
-    P2P on/off made no difference), while eight independent processes without NCCL ran at 1.184 ms on every GPU.
-    BENCH_CONTROL=nccl restores the old behaviour for the A/B."""
+    """One process per GPU.  The DEFAULT group is gloo: barriers and max-over-ranks carry no GPU data, and the replica and
+    row-tile workloads exchange nothing through a collective.  NCCL is created lazily (nccl_group) by the one workload that
+    really gathers device tensors, the probe batch ("NCCL only for the final gather").  This is a matter of scope, not of
+    speed: the chain runs equally fast with either control plane (profiles/r02p_scale4_matrix.txt).  BENCH_CONTROL=nccl makes
+    NCCL the default group."""
     import torch
     import torch.distributed as dist
     local = int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", 0)))
@@ -251,9 +245,14 @@ def run_ours(args, rank, world):
     for opt in filter(None, os.environ.get("BENCH_APP_OPTIONS", "").split(",")):     # e.g. graph.concurrent_branches=0,graph.frame_graph=0 (experiments)
         name, val = opt.split("=")
         app.set_option(name, float(val))
-    scene = vkr.synth_scene(rank, 64)                     # every rank renders its own sequence
+    # Weak scaling = the SAME work per GPU at every N: every rank renders the same synthetic sequence (seed 0), independently.
+    # Rounds 1 and early 2 seeded scene and camera path with the rank; seeds >= 2 hold costlier content (longer marches, wider
+    # blurs: 1.31 vs 1.19 ms/frame), the line reports the max over ranks, and that alone was the "0.915 efficiency at N >= 4"
+    # (profiles/r02l .. r02r: not the box, not NVML, not NCCL, not host enqueue, not launch gaps, not concurrency).
+    seq_seed = int(os.environ.get("BENCH_SEQ_SEED", "0"))
+    scene = vkr.synth_scene(seq_seed, 64)
     nres = min(64, K + W)                                 # distinct frames of the sequence kept resident (wraps after 64)
-    seq_params = [vkr.synth_camera(rank, f, w, h, True) for f in range(nres)]
+    seq_params = [vkr.synth_camera(seq_seed, f, w, h, True) for f in range(nres)]
     jit = [float(((f * 2654435761) % 1000) / 1000.0 - 0.5) for f in range(nres)]   # stands in for rand()/RAND_MAX - 0.5
     resident = []
     with torch.cuda.stream(stream):
@@ -421,9 +420,8 @@ def run_ours(args, rank, world):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"full chain (Hi-Z+SSR+GTAO+lighting+TAA), {w}x{h} TAA sequence with synthetic velocity (BASELINE configs[2])",
                        "frames_resident": nres, "l2": "inputs larger than L2 (one frame touches > 1 GB at 4K)",
-                       "parallelism": f"{world} independent sequence(s), one per GPU; control plane (barrier, max over ranks) on "
-                                      f"{os.environ.get('BENCH_CONTROL', 'gloo')}: nothing is exchanged, and an initialised NCCL communicator of >= 4 ranks "
-                                      f"costs this workload ~10 % (bench.py init_dist)"},
+                       "parallelism": f"{world} independent replica(s) of the same sequence (seed {seq_seed}), one per GPU: fixed work per GPU; nothing is "
+                                      f"exchanged; barrier and max over ranks on {os.environ.get('BENCH_CONTROL', 'gloo')}"},
             "roofline": {"bound": "hbm", "kernel": dname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_stale": traffic_stale, "traffic_captured_at": traffic_captured,
                          "peak_source": peak_src, "avg_launch_ms": avg_ms,
