@@ -751,7 +751,7 @@ def sub_records(args, rank, world):
     out = {}
     sub = argparse.Namespace(**vars(args))
     sub.steps, sub.warmup = SUB_STEPS, SUB_WARMUP
-    for name, fn in (("tiles", run_tiles), ("probes", run_probes)):     # tiles first: it needs no NCCL, and NCCL's presence costs ~10 %
+    for name, fn in (("tiles", run_tiles), ("probes", run_probes)):     # tiles first: it needs no NCCL group at all
         solo = None
         if world > 1:
             if rank == 0:
