@@ -566,7 +566,10 @@ def run_probes(args, rank, world, emit=True):
         sampler.stop_flag = True
         barrier()
     ms = e0.elapsed_time(e1)
+    per_rank_ms = [ms / K]
     if world > 1:
+        per_rank_ms = [None] * world
+        dist.all_gather_object(per_rank_ms, ms / K)          # each rank's own frame time: shows shard imbalance, hidden in the max
         ms = reduce_max([ms])[0]
     sampler.join(timeout=1.0)
     gather_timeouts = 0
@@ -588,7 +591,8 @@ def run_probes(args, rank, world, emit=True):
                        "parallelism": f"views sharded over {world} rank(s); " + {"allgather": "all_gather of AO + reflections per frame on a side stream", "p2p": "AO + reflections pushed into every rank's cudaIpc slab per frame by the copy engines, stream-side flags (no collective, no SMs)", "none": "NO gather (diagnostic run)"}[args.probes_gather] + (f", NCCL capped at {args.nccl_max_ctas} CTAs" if args.nccl_max_ctas > 0 else "")},
             "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
-            "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * max(1, args.probes_groups) * K, "gather_wait_timeouts": gather_timeouts, "clocks": sampler.result()}
+            "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * max(1, args.probes_groups) * K, "gather_wait_timeouts": gather_timeouts, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms],
+            "clocks": sampler.result()}
     if emit:
         print(json.dumps(line))
     return line
@@ -705,7 +709,10 @@ def run_tiles(args, rank, world, emit=True):
         barrier()
     ms = e0.elapsed_time(e1)
     fails = tf.wait_failures()
+    per_rank_ms = [ms / K]
     if world > 1:
+        per_rank_ms = [None] * world
+        dist.all_gather_object(per_rank_ms, ms / K)
         ms, fails = reduce_max([ms, float(fails)])
         fails = int(fails)
     sampler.join(timeout=1.0)
@@ -731,7 +738,8 @@ def run_tiles(args, rank, world, emit=True):
                                         "note": "16-row half-res strips; boundaries moved by 3 untimed calibration rounds so every rank's tile costs the same"}},
             "roofline": {"bound": "hbm", "kernel": "whole step", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
-            "gpu_launches": vkr_tiles.RowTiledFrame.KERNELS_PER_FRAME * K, "clocks": sampler.result()}
+            "gpu_launches": vkr_tiles.RowTiledFrame.KERNELS_PER_FRAME * K, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms],
+            "clocks": sampler.result()}
     if emit:
         print(json.dumps(line))
     return line
@@ -768,7 +776,7 @@ def sub_records(args, rank, world):
             rec["roofline_frac"] = full["roofline"]["frac"]
             rec["n1_same_run"] = {"value": solo["value"], "ms_per_step": solo["ms_per_step"]}
             rec["speedup_vs_n1"] = full["value"] / solo["value"]
-            for k in ("gather_wait_timeouts",):
+            for k in ("gather_wait_timeouts", "per_rank_ms_per_step"):
                 if k in full:
                     rec[k] = full[k]
             if "wait_timeouts" in full["config"]:
