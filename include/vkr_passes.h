@@ -272,6 +272,24 @@ int vkr_sssr_trace_indirect(const VkrTraceParams* p, uint32_t reflection_type, c
 /* Task "SSSR_Tile_Regression" (:497-538, regression.comp): per half-res 8x8 tile the plane n with n . x = 1 through the tile's
  * camera-relative world positions (.xyz) and the mean squared residual (.w) -> out_planes R32G32B32A32_SFLOAT. */
 int vkr_sssr_tile_regression(const VkrRegressionParams* p, const VkrImage* depth, const VkrImage* out_planes, void* stream);
+/* The tile path of the trace in ONE call that allocates nothing: SSSR_Clear -> SSSR_Classification -> both indirect SSSR_trace
+ * dispatches, with the two tile lists, the two indirect commands and the sRGB decode table in a file-scope device array inside
+ * the library instead of caller-allocated buffers.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *  - Calls no cudaMalloc / cudaFree / allocating library routine.  The FIRST call on a device does the set-up (symbol address
+ *    lookup + a synchronous 1 KB table upload): make that call outside stream capture.
+ *  - Limit: ceil(w/8) * ceil(h/8) <= VKR_SSSR_STATIC_MAX_TILES for the w x h `out_rays` image (65 536 tiles: up to 2048 x 2048,
+ *    or the half-res rays of a 3840 x 2160 frame); larger extents return VKR_ERR_UNSUPPORTED with a message naming the limit.
+ *    Every GPU that loads the library holds the array (VKR_SSSR_STATIC_SCRATCH_BYTES, about 513 KB) until exit.
+ *  - Every call shares that array; the counters are cleared at the start of every call.  Calls that OVERLAP on the GPU (different
+ *    streams without an event between them, or several host threads on one device) race on it: serialise them.
+ *  - Inputs and output as vkr_sssr_classification + vkr_sssr_trace_indirect: classification runs over the extent of `out_rays`
+ *    with p->max_roughness and `glossy_value`; every pixel of `out_rays` is written (each tile is in exactly one list); the
+ *    result equals, bit for bit, the separate entries' (tests/test_zz_no_alloc.py).  halton_vec4x128: DEVICE memory. */
+#define VKR_SSSR_STATIC_MAX_TILES 65536u
+#define VKR_SSSR_STATIC_SCRATCH_BYTES ((64u + 2u * VKR_SSSR_STATIC_MAX_TILES + 256u) * 4u)
+int vkr_sssr_trace_tiles_static(const VkrTraceParams* p, float glossy_value, const VkrImage* depth, const VkrImage* dnormal,
+                                const VkrImage* material, const float* halton_vec4x128, const VkrImage* out_rays, void* stream);
 
 /* ---- capture path (reference src/util_passes.cpp:152-180, src/image_readback.cpp:67-110, src/main.cpp:152-176) ------------ */
 /* Task "CopyImage" (blit_image): vkCmdBlitImage, VK_FILTER_LINEAR, all of src mip 0 onto all of dst mip 0 — destination texel p

@@ -303,3 +303,104 @@ extern "C" int vkr_sssr_tile_regression(const VkrRegressionParams* p, const VkrI
   sssr_tile_regression_kernel<<<grid, 64, 0, (cudaStream_t)stream>>>(k, d1, make_mip(out_planes, 0));
   return check_launch("sssr_tile_regression_kernel");
 }
+
+// ================================================================================================
+// vkr_sssr_trace_tiles_static — the whole tile path of the trace (SSSR_Clear -> SSSR_Classification -> the two indirect
+// SSSR_trace dispatches) in ONE call that allocates nothing.  No counterpart in the reference; added
+// for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it).
+//
+// The scratch the separate entries make the caller allocate — two tile lists, two indirect commands — and the sRGB decode
+// table (which the other entries cudaMalloc lazily, api.cu srgb_decode_table_device) live in ONE file-scope device array of
+// fixed size.  Every GPU that loads the library holds it (VKR_SSSR_STATIC_SCRATCH_BYTES, about 513 KB) until exit.
+//   words [0, 4)                      reflective indirect command {count, 1, 1, -}
+//   words [4, 8)                      glossy indirect command
+//   words [64, 64 + T)                reflective tile list     (T = VKR_SSSR_STATIC_MAX_TILES)
+//   words [64 + T, 64 + 2T)           glossy tile list
+//   words [64 + 2T, 64 + 2T + 256)    sRGB8 -> linear table (floats), written once per device at set-up
+// In HOST code the array's name is a host-side stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, once per device with that device current (static_scratch()).
+// Every call shares the array, which keeps the last call's contents: the two counters are reset by the clear kernel at the
+// start of every call, list entries beyond the counters are never read.  Calls that OVERLAP on the GPU (two streams, or two
+// host threads on one device) race on it: issue them on one stream or order them with events.
+#include <mutex>
+
+namespace vkr {
+
+#define SSSR_STATIC_LIST_WORD0 64u
+#define SSSR_STATIC_WORDS (SSSR_STATIC_LIST_WORD0 + 2u * VKR_SSSR_STATIC_MAX_TILES + 256u)
+static_assert(SSSR_STATIC_WORDS * 4u == VKR_SSSR_STATIC_SCRATCH_BYTES, "header and layout disagree");
+
+static __device__ __align__(256) uint32_t g_sssr_static_scratch[SSSR_STATIC_WORDS];
+
+static std::mutex g_sssr_static_mutex;
+static uint32_t* g_sssr_static_ptr[64] = {nullptr};     // device address of the array on each device, filled at set-up
+
+// Set-up, once per device, with that device current: the array's device address + the sRGB table (the same bits as
+// srgb_decode_table_device builds).  No allocation: cudaGetSymbolAddress looks the symbol up, cudaMemcpy writes into it.
+static uint32_t* static_scratch() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) { set_error("sssr_trace_tiles_static: no current CUDA device"); return nullptr; }
+  std::lock_guard<std::mutex> lock(g_sssr_static_mutex);
+  if (g_sssr_static_ptr[dev]) return g_sssr_static_ptr[dev];
+  uint32_t* ptr = nullptr;
+  cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_sssr_static_scratch);
+  if (e != cudaSuccess || !ptr) { set_error("sssr_trace_tiles_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return nullptr; }
+  float host[256];
+  for (int i = 0; i < 256; i++) {
+    const double c = i / 255.0;
+    host[i] = (float)((c <= 0.04045) ? c / 12.92 : std::pow((c + 0.055) / 1.055, 2.4));
+  }
+  e = cudaMemcpy(ptr + SSSR_STATIC_LIST_WORD0 + 2u * VKR_SSSR_STATIC_MAX_TILES, host, sizeof(host), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { set_error("sssr_trace_tiles_static: sRGB table upload: %s", cudaGetErrorString(e)); return nullptr; }
+  g_sssr_static_ptr[dev] = ptr;
+  return ptr;
+}
+
+}  // namespace vkr
+
+extern "C" int vkr_sssr_trace_tiles_static(const VkrTraceParams* p, float glossy_value, const VkrImage* depth, const VkrImage* dnormal,
+                                           const VkrImage* material, const float* halton_vec4x128, const VkrImage* out_rays, void* stream) {
+  if (!p || !halton_vec4x128 || !image_ok(depth, VKR_FORMAT_D24_UNORM_S8_UINT) || depth->mip_count < 2 || !image_ok(dnormal, VKR_FORMAT_R16G16_UNORM) ||
+      !image_ok(material, VKR_FORMAT_R8G8B8A8_SRGB) || !image_ok(out_rays, VKR_FORMAT_R16G16B16A16_UNORM)) {
+    set_error("sssr_trace_tiles_static: null argument or unexpected format");
+    return VKR_ERR_INVALID_ARGUMENT;
+  }
+  const int w = (int)out_rays->width, h = (int)out_rays->height;
+  const int tiles_x = (w + 7) / 8, tiles_y = (h + 7) / 8;
+  const unsigned long long n_tiles = (unsigned long long)tiles_x * (unsigned long long)tiles_y;
+  if (n_tiles > VKR_SSSR_STATIC_MAX_TILES) {
+    set_error("sssr_trace_tiles_static: %dx%d rays = %llu tiles of 8x8, beyond the static scratch's maximum of %u tiles (VKR_SSSR_STATIC_MAX_TILES); "
+              "use vkr_sssr_classification / vkr_sssr_trace_indirect with caller-allocated lists", w, h, n_tiles, (unsigned)VKR_SSSR_STATIC_MAX_TILES);
+    return VKR_ERR_UNSUPPORTED;
+  }
+  uint32_t* S = static_scratch();
+  if (!S) return VKR_ERR_CUDA;
+  const int sms = sm_count();
+  if (!sms) { set_error("sssr_trace_tiles_static: no CUDA device"); return VKR_ERR_CUDA; }
+  uint32_t* refl_cmd = S;
+  uint32_t* glossy_cmd = S + 4;
+  int* refl_tiles = (int*)(S + SSSR_STATIC_LIST_WORD0);
+  int* glossy_tiles = refl_tiles + VKR_SSSR_STATIC_MAX_TILES;
+  const float* srgb = (const float*)(S + SSSR_STATIC_LIST_WORD0 + 2u * VKR_SSSR_STATIC_MAX_TILES);
+  cudaStream_t st = (cudaStream_t)stream;
+  const uint32_t max_tiles = (uint32_t)n_tiles;
+
+  sssr_clear_indirect_kernel<<<1, 32, 0, st>>>(refl_cmd, glossy_cmd);                       // the counters must start at zero: every call
+  dim3 cgrid((tiles_x + 3) / 4, tiles_y);
+  sssr_classification_kernel<<<cgrid, 256, 0, st>>>(w, h, p->max_roughness, glossy_value, make_mip(material, 0), srgb, refl_tiles, glossy_tiles, refl_cmd, glossy_cmd);
+  TraceTilesK k;
+  k.normal_mat = make_mat(p->normal_mat);
+  k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
+  k.frame_random = p->frame_random; k.max_roughness = p->max_roughness;
+  PyramidView P;
+  P.count = (int)depth->mip_count - 1;
+  for (int i = 0; i < VKR_MAX_MIPS; i++) P.mip[i] = (i < P.count) ? make_mip(depth, i + 1) : Mip{nullptr, 0, 0, 0, 0};
+  uint32_t ctas = (uint32_t)sms * 8u, need = (max_tiles + 1u) / 2u;
+  if (ctas > need) ctas = need;
+  sssr_trace_indirect_kernel<0, 50, true><<<ctas, 128, 0, st>>>(k, P, make_mip(dnormal, 0), make_mip(material, 0), (const float4*)halton_vec4x128, refl_tiles,
+                                                                refl_cmd, max_tiles, make_mip(out_rays, 0), srgb);
+  sssr_trace_indirect_kernel<1, 25, false><<<ctas, 128, 0, st>>>(k, P, make_mip(dnormal, 0), make_mip(material, 0), (const float4*)halton_vec4x128, glossy_tiles,
+                                                                 glossy_cmd, max_tiles, make_mip(out_rays, 0), srgb);
+  return check_launch("sssr_trace_tiles_static");
+}

@@ -404,6 +404,15 @@ def sssr_tile_regression(p, depth, out_planes, stream=None):
     check(lib.vkr_sssr_tile_regression(C.byref(p), depth.ptr, out_planes.ptr, stream_ptr(stream)))
 
 
+SSSR_STATIC_MAX_TILES = 65536
+_sig("vkr_sssr_trace_tiles_static", PT(TraceParams), C.c_float, IP, IP, IP, FP, IP, VP)
+
+
+def sssr_trace_tiles_static(p, glossy_value, depth, dnormal, material, halton_dev, rays, stream=None):
+    """Clear + classification + both indirect traces with the library's static device scratch: allocates nothing (include/vkr_passes.h)."""
+    check(lib.vkr_sssr_trace_tiles_static(C.byref(p), float(glossy_value), depth.ptr, dnormal.ptr, material.ptr, _dp(halton_dev), rays.ptr, stream_ptr(stream)))
+
+
 _sig("vkr_blit_image", IP, IP, VP)
 _sig("vkr_readback_pack", IP, C.c_uint32, C.c_uint32, VP, VP)
 READBACK_RAW, READBACK_DEPTH24, READBACK_OPAQUE_ALPHA = 0, 1, 2
