@@ -10,6 +10,7 @@ hdr = rows[hi]
 si, ei = hdr.index("Source"), hdr.index("Instructions Executed")
 mix = collections.Counter(); total = 0
 for r in rows[hi + 1:]:
+    if r and r[0] in ("Address", "Kernel Name"): break   # the page may list the kernel a second time: one block only
     if len(r) <= ei or not r[ei]: continue
     try: n = int(float(r[ei]))
     except ValueError: continue
