@@ -380,8 +380,29 @@ def run_ours(args, rank, world):
         stream.synchronize()
         barrier()
         ms_e2e = max_over_ranks(a0.elapsed_time(a1))
+        # The bound of this path on THIS box: the same bytes through the same two copy streams, all ranks at once, nothing rendered.
+        src_fixed = taa_tensor()
+        barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record(stream)
+        cs.wait_event(c0); ds.wait_event(c0)
+        for i in range(K):
+            with torch.cuda.stream(cs):
+                for d, s_ in zip(dev_gb[i % 3].input_images(), host_frames[i % nh].input_images()):
+                    d.buf.copy_(s_.buf, non_blocking=True)
+            with torch.cuda.stream(ds):
+                out_host.buf.copy_(src_fixed, non_blocking=True)
+        stream.wait_stream(cs); stream.wait_stream(ds)
+        c1.record(stream)
+        stream.synchronize()
+        barrier()
+        ms_copy = max_over_ranks(c0.elapsed_time(c1)) / K
         e2e = {"value": world * npix * K / (ms_e2e * 1e-3) / 1e9, "unit": "Gpix/s", "ms_per_step": ms_e2e / K, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": d2h, "note": "pinned host G-buffer -> device (copy stream) -> vkr_app_bind_gbuffer -> render_frame -> TAA target -> pinned host "
+               "d2h_bytes_per_step": d2h,
+               "roofline": {"bound": "host<->device copies", "copy_only_ms_per_step": ms_copy, "copy_only_GBps": world * (h2d + d2h) / (ms_copy * 1e-3) / 1e9,
+                            "frac": ms_copy / (ms_e2e / K),
+                            "how": "the step's H2D + D2H bytes alone, on the same pinned buffers and copy streams, every rank at once (measured in this run)"},
+               "note": "pinned host G-buffer -> device (copy stream) -> vkr_app_bind_gbuffer -> render_frame -> TAA target -> pinned host "
                                                   "(read-back stream); three device G-buffers rotate so both PCIe directions overlap the chain"}
 
     fg_stats = app.frame_graph_stats()
