@@ -47,6 +47,27 @@ def util(it, key, th, tw=16):
     return float(t.mean() / wmax.mean()), float(wmax.mean())
 
 
+def compaction(it, th, points, tw=16):
+    """Warp-steps per ray if the tile's surviving rays are re-packed into full warps (in thread order) after the step counts in
+    `points` (CTA-wide, through shared memory): segment k runs from points[k-1] to points[k]; a warp's cost in a segment is the
+    largest remaining count of its lanes, clipped to the segment."""
+    h2, w2 = it.shape
+    hh, ww = h2 // th * th, w2 // tw * tw
+    t = it[:hh, :ww].reshape(hh // th, th, ww // tw, tw).transpose(0, 2, 1, 3).reshape(-1, th * tw)
+    total = 0.0
+    edges = [0] + list(points) + [10 ** 6]
+    for a, b in zip(edges[:-1], edges[1:]):
+        live = t > a                                                   # rays that still march after step a
+        rem = np.clip(t - a, 0, b - a) * live
+        if a == 0:
+            packed = rem                                               # the kernel's layout
+        else:                                                          # survivors first, in thread order (a stable partition)
+            order = np.argsort(~live, axis=1, kind="stable")
+            packed = np.take_along_axis(rem, order, axis=1)
+        total += packed.reshape(packed.shape[0], -1, 32).max(axis=2).sum()
+    return total / t.size
+
+
 for f in range(3):
     P = cc.begin_frame(scene)
     st = cc.steps(P)
@@ -67,6 +88,11 @@ for f in range(3):
         if f > 0:
             rows.append(("sorted by last frame's count", util(it, prev[:h2, :w2], th)))
         print(f"  tile 16x{th}: " + "; ".join(f"{n}: {u:.3f} (warp max {m:.1f})" for n, (u, m) in rows))
+    for th in (8, 16):
+        base = compaction(it, th, [])
+        res = [(pts, compaction(it, th, pts)) for pts in ([15], [16], [20], [24], [16, 24], [16, 32], [16, 24, 40], [20, 40])]
+        print(f"  tile 16x{th}: warp-steps per ray, no compaction {base / 32 * 32:.2f} (x 1/32 lanes = {base:.3f}); " +
+              "; ".join(f"after {pts}: {v / base:.3f} of it" for pts, v in res))
     prev = it.copy()
     for _, t, _ in st[2:]:
         t()
