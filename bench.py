@@ -51,6 +51,7 @@ def parse():
                     help="probes workload: how every rank gets all per-view results each frame — allgather: NCCL all_gather_into_tensor on a "
                          "side stream; p2p: copy-engine pushes into every rank's cudaIpc slab with stream-side flags (vkr_gather.PeerGather: no "
                          "SMs taken from the passes); none: skip it (diagnostic: what the gather costs the frame rate)")
+    ap.add_argument("--probes-gather-buffers", type=int, default=4, help="probes workload, p2p gather: landing buffers per tensor on every rank")
     ap.add_argument("--nccl-max-ctas", type=int, default=0,
                     help="probes workload: cap the CTAs NCCL may use per collective (0 = NCCL's default).  The gather moves 64 MB per frame into "
                          "every GPU while the passes want every SM; a small cap leaves the SMs to the passes")
@@ -525,7 +526,7 @@ def run_probes(args, rank, world, emit=True):
             out = [None] * world
             dist.all_gather_object(out, x)
             return out
-        pg = vkr_gather.PeerGather(args.views, [ao0.shape[1], refl0.shape[1]], rank, world, allgather_bytes, f"cuda:{local}")
+        pg = vkr_gather.PeerGather(args.views, [ao0.shape[1], refl0.shape[1]], rank, world, allgather_bytes, f"cuda:{local}", buffers=args.probes_gather_buffers)
 
     def gather(ao, refl):
         if pg is not None:

@@ -24,7 +24,8 @@ def allgather_bytes(b):
 
 
 row_bytes = [4096, 1000]                       # the second tensor's rows are strided in the source (pitch 1024)
-pg = vkr_gather.PeerGather(n_units, row_bytes, rank, world, allgather_bytes, f"cuda:{dev}")
+nbuf = int(sys.argv[4]) if len(sys.argv) > 4 else 2
+pg = vkr_gather.PeerGather(n_units, row_bytes, rank, world, allgather_bytes, f"cuda:{dev}", buffers=nbuf)
 b, e = vkr_views.shard_range(n_units, world, rank)
 st = torch.cuda.Stream()
 bad = []

@@ -123,8 +123,9 @@ def test_view_ranges_on_separate_streams_write_the_same_bytes(cuda):
             a.end_frame(); b.end_frame()
 
 
-@pytest.mark.parametrize("world,n_units,epochs", [(2, 16, 5), (3, 10, 4)])
-def test_peer_gather_equals_all_gather(cuda, world, n_units, epochs):
+# the last case: 4 landing buffers per tensor (epochs > buffers, so every buffer is reused)
+@pytest.mark.parametrize("world,n_units,epochs,buffers", [(2, 16, 5, 2), (3, 10, 4, 2), (3, 16, 11, 4)])
+def test_peer_gather_equals_all_gather(cuda, world, n_units, epochs, buffers):
     """vkr_gather.PeerGather (copy-engine pushes into every rank's cudaIpc slab + stream-side flags) against the blocks an
     all_gather would deliver, several epochs in a row (buffer reuse), ragged shards, strided source rows.  One process per rank;
     on a single-GPU box the ranks share cuda:0 (the IPC mapping, pushes and flags are exercised all the same)."""
@@ -134,7 +135,7 @@ def test_peer_gather_equals_all_gather(cuda, world, n_units, epochs):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     port = 29300 + (os.getpid() + world) % 500
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", str(port), os.path.join(root, "tests", "gather_worker.py"), root, str(n_units), str(epochs)]
+           "--master-port", str(port), os.path.join(root, "tests", "gather_worker.py"), root, str(n_units), str(epochs), str(buffers)]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("ok") == world

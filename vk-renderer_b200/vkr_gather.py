@@ -22,17 +22,24 @@ from vkr_views import shard_range
 
 
 class PeerGather:
-    def __init__(self, n_units, row_bytes, rank, world, allgather_bytes, device, timeout_ms=2000):
+    def __init__(self, n_units, row_bytes, rank, world, allgather_bytes, device, timeout_ms=2000, buffers=2):
         """row_bytes: bytes per unit of each result tensor, e.g. [65536, 65536].  allgather_bytes(b) -> list over ranks (host side,
         any transport: it only carries the 64-byte IPC handles once)."""
         self.n_units, self.row_bytes, self.rank, self.world = n_units, list(row_bytes), rank, world
         self.device, self.timeout = torch.device(device), timeout_ms
+        # `buffers` landing buffers per tensor on every rank.  Epoch e lands in buffer e % buffers, whose last tenant was epoch
+        # e - buffers; a rank may overwrite it once the owner has pushed epoch e - buffers + 1 (the consumer rule below).  With 2
+        # buffers every rank is held within ONE epoch of the slowest rank, and since the compute stream in turn waits for its own
+        # copies (sources_free), jitter on any rank stalls all of them every frame; more buffers loosen that coupling at
+        # n_units * sum(row_bytes) bytes of slab each.
+        assert buffers >= 2
+        self.nbuf = buffers
         self._fail_base = peer_wait_failures_total()
         self.first, self.end = shard_range(n_units, world, rank)
         sizes = [n_units * rb for rb in self.row_bytes]
-        self.slab = PeerSlab(2 * sum((s + 255) & ~255 for s in sizes), self.device)
+        self.slab = PeerSlab(self.nbuf * sum((s + 255) & ~255 for s in sizes), self.device)
         assert world * 4 <= PeerSlab.FLAG_BYTES
-        self.bufs = [[self.slab.carve(s).view(n_units, rb) for s, rb in zip(sizes, self.row_bytes)] for _ in range(2)]
+        self.bufs = [[self.slab.carve(s).view(n_units, rb) for s, rb in zip(sizes, self.row_bytes)] for _ in range(self.nbuf)]
         handles = allgather_bytes(self.slab.handle_bytes())
         for r in range(world):
             if r != rank:
@@ -62,8 +69,8 @@ class PeerGather:
         e, st = self.epoch, C.c_void_p(self.xfer.cuda_stream)
         self._ready.record(after_stream)
         self.xfer.wait_event(self._ready)
-        if e > 1:
-            self._wait_epoch(e - 1, st)            # every peer has finished with epoch e - 2, the last tenant of this buffer
+        if e > self.nbuf - 1:
+            self._wait_epoch(e - self.nbuf + 1, st)   # every peer has finished with epoch e - buffers, the last tenant of this buffer
         units = self.end - self.first
         self._go.record(self.xfer)
         for r in range(self.world):
@@ -75,7 +82,7 @@ class PeerGather:
                 sp = C.c_void_p(s.cuda_stream)
             for t, (blk, rb) in enumerate(zip(blocks, self.row_bytes)):
                 assert blk.shape[0] == units and blk.shape[1] >= rb and blk.stride(1) == 1
-                dst = base + (self.bufs[e & 1][t].data_ptr() - self.slab.ptr) + self.first * rb
+                dst = base + (self.bufs[e % self.nbuf][t].data_ptr() - self.slab.ptr) + self.first * rb
                 vkr.check(_P.vkr_peer_push_2d(C.c_void_p(blk.data_ptr()), blk.stride(0), C.c_void_p(dst), rb, rb, units, sp))
             if r != self.rank:
                 self._pdone[r].record(s)
@@ -95,14 +102,14 @@ class PeerGather:
     def gathered(self, epoch, stream=None):
         """Holds `stream` (default: the transfer stream) until `epoch` is complete on this rank and returns its (n_units, row_bytes)
         tensors.  Consume them on a stream that is (or is ordered before) the `after_stream` of push(epoch + 1): that push's
-        flag is what lets the peers overwrite this buffer with epoch + 2."""
+        flag is what lets the peers overwrite this buffer with epoch + buffers."""
         st = self.xfer if stream is None else stream
         if stream is not None:                       # own rows arrive through the transfer stream
             ev = torch.cuda.Event()
             ev.record(self.xfer)
             st.wait_event(ev)
         self._wait_epoch(epoch, C.c_void_p(st.cuda_stream))
-        return self.bufs[epoch & 1]
+        return self.bufs[epoch % self.nbuf]
 
     def finish(self):
         """Wait (stream-side) for the last epoch to be complete everywhere it lands here; returns its tensors."""
