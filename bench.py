@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--probes-groups", type=int, default=2,
                     help="probes workload: split a rank's views into this many layer ranges, each running its chain on its own streams inside the "
                          "frame's CUDA graph (independent views fill each other's launch gaps and tails)")
-    ap.add_argument("--probes-gather", default="allgather", choices=["allgather", "p2p", "none"],
+    ap.add_argument("--probes-gather", default="allgather", choices=["allgather", "p2p", "fused", "none"],
                     help="probes workload: how every rank gets all per-view results each frame — allgather: NCCL all_gather_into_tensor on a "
                          "side stream; p2p: copy-engine pushes into every rank's cudaIpc slab with stream-side flags (vkr_gather.PeerGather: no "
                          "SMs taken from the passes); none: skip it (diagnostic: what the gather costs the frame rate)")
@@ -482,8 +482,19 @@ def run_probes(args, rank, world, emit=True):
     gstreams = [(torch.cuda.Stream(), torch.cuda.Stream() if args.probes_lanes == 2 else None) for _ in range(max(0, args.probes_groups - 1))]
     assert e - b > 1, "the batched path needs at least 2 views per rank"
     nres = 4                                                # resident input frames (cycled); > L2 in total
+
+    def allgather_bytes(x):
+        out = [None] * world
+        dist.all_gather_object(out, x)
+        return out
+
+    fg = None
+    if world > 1 and args.probes_gather == "fused":         # the gather fused into the blur / accumulate kernels (peer stores)
+        import vkr_gather
+        fg = vkr_gather.FusedGather(args.views, {"accumulated_ao": (w // 2, h // 2, vkr.R16G16_SFLOAT), "blurred": (w // 2, h // 2, vkr.R8G8B8A8_UNORM)},
+                                    rank, world, allgather_bytes, f"cuda:{local}")
     with torch.cuda.stream(stream):
-        vb = vkr_views.ViewBatch(w, h, list(range(b, e)), device=f"cuda:{local}", stream=stream, param_sets=nres)
+        vb = vkr_views.ViewBatch(w, h, list(range(b, e)), device=f"cuda:{local}", stream=stream, param_sets=nres, fused=fg)
         frames = []
         for f in range(nres):
             vb.frame = f
@@ -521,11 +532,6 @@ def run_probes(args, rank, world, emit=True):
     pg = None
     if world > 1 and args.probes_gather == "p2p":
         import vkr_gather
-
-        def allgather_bytes(x):
-            out = [None] * world
-            dist.all_gather_object(out, x)
-            return out
         pg = vkr_gather.PeerGather(args.views, [ao0.shape[1], refl0.shape[1]], rank, world, allgather_bytes, f"cuda:{local}", buffers=args.probes_gather_buffers)
 
     def gather(ao, refl):
@@ -547,6 +553,8 @@ def run_probes(args, rank, world, emit=True):
             pg.sources_free(stream)                          # this frame overwrites the result images of two frames ago
         if i >= 2 * nres:
             graphs[f].replay()
+            if fg is not None:
+                fg.note_replayed()
             gather(*outs[f])
             return
         bind(i)
@@ -582,6 +590,8 @@ def run_probes(args, rank, world, emit=True):
         if pg is not None:
             pg.finish()                                      # the last epoch has landed here too
             stream.wait_stream(pg.xfer)
+        if fg is not None:
+            fg.gathered(fg.epoch, stream)                    # every rank's last frame has landed here too
         stream.wait_stream(side)
         e1.record(stream)
         stream.synchronize()
@@ -598,6 +608,10 @@ def run_probes(args, rank, world, emit=True):
     if pg is not None:
         gather_timeouts = pg.wait_failures()
         pg.close(dist.barrier)
+    if fg is not None:
+        gather_timeouts = fg.wait_failures()
+        vb.fused = None
+        fg.close(dist.barrier)
     del graphs, outs, frames, vb, gout
     torch.cuda.empty_cache()
     if rank != 0:
@@ -610,7 +624,7 @@ def run_probes(args, rank, world, emit=True):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.views} probe views 256x256, Hi-Z+GTAO+SSR, contiguous view blocks per rank (BASELINE configs[3])",
                        "frames_resident": nres, "launch": f"one CUDA graph per frame: {args.probes_groups} view range(s) x 9 kernels" + (" (SSR filter+blur beside the GTAO passes)" if args.probes_lanes == 2 else "") + ", parameter blocks prepared once", "l2": f"inputs larger than L2 ({args.views // world} views x 1.4 MB per frame per rank)",
-                       "parallelism": f"views sharded over {world} rank(s); " + {"allgather": "all_gather of AO + reflections per frame on a side stream", "p2p": "AO + reflections pushed into every rank's cudaIpc slab per frame by the copy engines, stream-side flags (no collective, no SMs)", "none": "NO gather (diagnostic run)"}[args.probes_gather] + (f", NCCL capped at {args.nccl_max_ctas} CTAs" if args.nccl_max_ctas > 0 else "")},
+                       "parallelism": f"views sharded over {world} rank(s); " + {"allgather": "all_gather of AO + reflections per frame on a side stream", "p2p": "AO + reflections pushed into every rank's cudaIpc slab per frame by the copy engines, stream-side flags (no collective, no SMs)", "fused": "the blur and the accumulate kernels store every result texel into every rank's arrays themselves (peer-mapped memory over NVLink; epoch flags, no collective, no copy, no SMs beyond the passes')", "none": "NO gather (diagnostic run)"}[args.probes_gather] + (f", NCCL capped at {args.nccl_max_ctas} CTAs" if args.nccl_max_ctas > 0 else "")},
             "roofline": {"bound": "hbm", "kernel": "whole step (8 batched launches)", "achieved": alg / world / (ms / K * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": alg / world / (ms / K * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src, "alg_bytes_per_step": alg},
             "gpu_launches": vkr_views.ViewBatch.KERNELS_PER_FRAME * max(1, args.probes_groups) * K, "gather_wait_timeouts": gather_timeouts, "per_rank_ms_per_step": [round(x, 4) for x in per_rank_ms],

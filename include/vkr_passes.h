@@ -185,7 +185,16 @@ typedef struct VkrLaunchExt {
                            * batch prepared once can be launched as several layer ranges (each range's VkrImage arguments then
                            * describe its first layer).  Independent ranges on separate streams fill each other's tails. */
   uint32_t reserved;
+  /* Fused gather (vkr_sssr_blur_ex and vkr_gtao_accumulate_ex only; every other entry refuses a non-zero peer_count): every texel
+   * the pass stores into its OUTPUT image is also stored at the same address + peer_delta[k], k < peer_count — the same array in
+   * peer-mapped memory of other GPUs (cudaIpc / NVLink), so that the result is "gathered" by the kernel that produces it: no
+   * collective, no copy, no SMs taken from the passes (include/vkr_peer.h vkr_peer_epoch_begin / _end order it).  No reference
+   * counterpart (the reference is single-GPU); BASELINE.json configs[3]. */
+  uint32_t peer_count;
+  uint32_t reserved2;
+  int64_t peer_delta[7];
 } VkrLaunchExt;
+#define VKR_MAX_PEERS 7
 
 /* ---- utilities ---------------------------------------------------------------- */
 const char* vkr_version(void);

@@ -46,6 +46,18 @@ int vkr_peer_wait(const uint32_t* flag, uint32_t value, uint32_t timeout_ms, voi
 /* Number of waits that timed out on the current device since the last call (resets the counter). Synchronises the device. */
 int vkr_peer_wait_failed(void);
 
+/* Epoch protocol of the fused gather (VkrLaunchExt.peer_delta in vkr_passes.h: the passes store their results into every rank's
+ * arrays themselves).  Both kernels read the epoch from device memory, so a frame containing them replays as a CUDA graph.
+ *   ctrl          one 32-bit word in THIS rank's memory: the number of epochs this rank has finished (0 at start)
+ *   flags[r]      32-bit words in this rank's peer-visible memory: the last epoch rank r finished writing into this rank
+ * vkr_peer_epoch_begin — before the frame's writers: waits (stream-side, with the timeout of vkr_peer_wait) until every other
+ *   rank r < count has flags[r] >= ctrl[0], i.e. has finished with the buffer epoch ctrl[0] + 1 is about to overwrite.
+ * vkr_peer_epoch_end — after them: ctrl[0] += 1 and that value is released (system scope) into remote_flags[r] for r < count
+ *   (HOST array of peer-mapped addresses of this rank's flag word on rank r; NULL entries, e.g. the own slot, are skipped).
+ * Consumer rule: read epoch k's gathered arrays on a stream ordered before this rank's epoch_end of k + 1.  At most 8 ranks. */
+int vkr_peer_epoch_begin(const uint32_t* ctrl, const uint32_t* flags, uint32_t count, uint32_t self, uint32_t timeout_ms, void* stream);
+int vkr_peer_epoch_end(uint32_t* ctrl, uint32_t* const* remote_flags, uint32_t count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

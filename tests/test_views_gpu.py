@@ -139,3 +139,21 @@ def test_peer_gather_equals_all_gather(cuda, world, n_units, epochs, buffers):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("ok") == world
+
+
+@pytest.mark.parametrize("world,n_views,frames", [(2, 5, 4), (3, 7, 5)])
+def test_fused_gather_equals_local_batch(cuda, world, n_views, frames):
+    """The gather fused into the producing kernels (VkrLaunchExt.peer_delta + the epoch kernels of include/vkr_peer.h,
+    vkr_gather.FusedGather): on every rank the full arrays equal, bit for bit and for every view, what a local batch of ALL views
+    computes — ragged shards, several frames (ping-pong slots reused), the last two through a captured CUDA graph."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    port = 29400 + (os.getpid() + 7 * world) % 500
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tests", "fused_worker.py"), root, str(n_views), str(frames)]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("ok") == world
+

@@ -49,8 +49,12 @@ int check_launch(const char* what) {
   return VKR_OK;
 }
 
-int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what) {
+int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what, bool peers_ok) {
   o->e = e;
+  if (e && e->peer_count && (!peers_ok || e->peer_count > VKR_MAX_PEERS)) {
+    set_error("%s: peer_count = %u (fused gather) is %s", what, e->peer_count, peers_ok ? "beyond VKR_MAX_PEERS" : "only supported by sssr_blur_ex and gtao_accumulate_ex");
+    return VKR_ERR_UNSUPPORTED;
+  }
   o->layers = (e && e->layers > 1) ? (int)e->layers : 1;
   const int total = (int)((out_h + tile_h - 1) / tile_h);
   o->yb0 = 0; o->yblocks = total;

@@ -71,6 +71,10 @@ inline Mip make_mip(const VkrImage* im, uint32_t lod) {
 struct LaunchX {
   int yb0;   // first block row of the window (blockIdx.y is relative to it)
 };
+struct PeerOut {            // fused gather: extra destinations of a pass's output stores (VkrLaunchExt.peer_delta)
+  int n;
+  long long d[7];
+};
 struct ExtInfo {
   int layers = 1;
   int yb0 = 0, yblocks = 0;
@@ -80,9 +84,10 @@ struct ExtInfo {
   unsigned first() const { return e ? e->first_param : 0u; }   // block of the prepared set the launch's layer 0 uses
   bool prepared() const { return e && (e->flags & VKR_EXT_PARAMS_PREPARED); }
   bool prepare_only() const { return e && (e->flags & VKR_EXT_PREPARE_ONLY); }
+  PeerOut peers() const { PeerOut p; p.n = e ? (int)e->peer_count : 0; for (int i = 0; i < 7; i++) p.d[i] = (e && i < p.n) ? (long long)e->peer_delta[i] : 0; return p; }
 };
 // Validates ext against a pass whose output has out_h rows processed in tiles of tile_h rows.
-int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what);
+int resolve_ext(const VkrLaunchExt* e, uint32_t out_h, int tile_h, ExtInfo* o, const char* what, bool peers_ok = false);
 inline Mip make_mip(const VkrImage* im, uint32_t lod, const ExtInfo& x, int arg_index) { Mip m = make_mip(im, lod); m.ls = x.stride(arg_index); return m; }
 // Per-layer kernel parameter blocks: converts nothing, just ships `count` POD structs to the device scratch on `stream`.
 int upload_params(const void* host, size_t elem, int count, void* scratch, cudaStream_t st, const char* what);

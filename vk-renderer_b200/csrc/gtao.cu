@@ -261,7 +261,7 @@ struct AccumK {
 // 1-ulp difference to ~1e-3 view units, and depth_err is thresholded); everything else is value-only.
 template <bool SAME, bool LAYERED>
 __global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k0, const AccumK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth, Mip prev_depth, Mip filtered,
-                                                              Mip out, Mip velocity, Mip history) {
+                                                              Mip out, Mip velocity, Mip history, PeerOut po) {
   AccumK kl;
   if (LAYERED) {
     const int z = blockIdx.z;
@@ -312,7 +312,12 @@ __global__ void __launch_bounds__(256) gtao_accumulate_kernel(AccumK k0, const A
     samples_count = samples_count + 1.f;
     if (samples_count > 255.f) samples_count = 100.f;
   }
-  *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_half2(gclamp(computed_ao, 0.f, 1.f), samples_count * (1.0f / 255.f));
+  const uint32_t texel = pack_half2(gclamp(computed_ao, 0.f, 1.f), samples_count * (1.0f / 255.f));
+  uint32_t* const dst = (uint32_t*)(out.p + (size_t)py * out.pitch) + px;
+  *dst = texel;
+#pragma unroll
+  for (int i = 0; i < 7; i++)                                                              // fused gather: the same texel into the peers' arrays (NVLink stores)
+    if (i < po.n) *(uint32_t*)((unsigned char*)dst + po.d[i]) = texel;
 }
 
 }  // namespace vkr
@@ -413,7 +418,7 @@ extern "C" int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* d
     return VKR_ERR_SIZE_MISMATCH;
   }
   ExtInfo x;
-  int rc = resolve_ext(ext, accumulated->height, 8, &x, "gtao_accumulate");
+  int rc = resolve_ext(ext, accumulated->height, 8, &x, "gtao_accumulate", true);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   AccumK k = make_accum_k(p);
@@ -433,7 +438,7 @@ extern "C" int vkr_gtao_accumulate_ex(const VkrAccumParams* p, const VkrImage* d
   auto kern = same ? (kv ? gtao_accumulate_kernel<true, true> : gtao_accumulate_kernel<true, false>)
                    : (kv ? gtao_accumulate_kernel<false, true> : gtao_accumulate_kernel<false, false>);
   kern<<<grid, 256, 0, st>>>(k, kv, LaunchX{x.yb0}, dim, make_mip(depth, depth_lod, x, 0), make_mip(prev_depth, depth_lod, x, 1), make_mip(filtered, 0, x, 2),
-                             make_mip(accumulated, 0, x, 3), make_mip(dvelocity, 0, x, 4), make_mip(history, 0, x, 5));
+                             make_mip(accumulated, 0, x, 3), make_mip(dvelocity, 0, x, 4), make_mip(history, 0, x, 5), x.peers());
   return check_launch("gtao_accumulate_kernel");
 }
 

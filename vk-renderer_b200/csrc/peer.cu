@@ -25,6 +25,38 @@ __global__ void peer_wait_kernel(const uint32_t* flag, uint32_t value, unsigned 
   }
 }
 
+// Epoch protocol of the fused gather (VkrLaunchExt.peer_delta): both kernels take the epoch from a device word, so a frame that
+// contains them can be captured into a CUDA graph once and replayed.
+//   ctrl[0]   this rank's epoch (number of frames it has finished writing)
+//   flags[r]  the last epoch rank r has finished writing INTO THIS RANK's arrays (stored by r's epoch_end)
+// begin: the frame about to run writes epoch e = ctrl[0] + 1 into buffer e & 1 of every rank, whose last tenant was epoch e - 2; a
+// peer is done reading that once it has finished ITS epoch e - 1 (the consumer rule: consume epoch k before finishing k + 1).
+__global__ void peer_epoch_begin_kernel(const uint32_t* ctrl, const uint32_t* flags, uint32_t count, uint32_t self, unsigned long long timeout_ns) {
+  const uint32_t i = threadIdx.x;
+  if (i >= count || i == self) return;
+  const uint32_t need = ctrl[0];                                      // e - 1
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+    if ((int32_t)(v - need) >= 0) return;
+    __nanosleep(200);
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) { atomicAdd(&g_wait_failed, 1u); return; }
+  }
+}
+struct PeerFlags { uint32_t* p[8]; };
+// end: everything this stream stored before (the passes' stores into the peers' arrays included) becomes visible, then the new
+// epoch is released into every peer's flag word for this rank.
+__global__ void peer_epoch_end_kernel(uint32_t* ctrl, PeerFlags remote, uint32_t count) {
+  const uint32_t e = ctrl[0] + 1u;
+  __threadfence_system();
+  if (threadIdx.x == 0) ctrl[0] = e;
+  if (threadIdx.x < count && remote.p[threadIdx.x]) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote.p[threadIdx.x]), "r"(e) : "memory");
+}
+
 static int cuda_rc(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return VKR_OK;
   set_error("%s: %s", what, cudaGetErrorString(e));
@@ -93,6 +125,20 @@ extern "C" int vkr_peer_wait(const uint32_t* flag, uint32_t value, uint32_t time
   if (!flag) { set_error("peer_wait: null flag"); return VKR_ERR_INVALID_ARGUMENT; }
   peer_wait_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value, (unsigned long long)timeout_ms * 1000000ull);
   return check_launch("peer_wait_kernel");
+}
+
+extern "C" int vkr_peer_epoch_begin(const uint32_t* ctrl, const uint32_t* flags, uint32_t count, uint32_t self, uint32_t timeout_ms, void* stream) {
+  if (!ctrl || !flags || count == 0 || count > 8 || self >= count) { set_error("peer_epoch_begin: bad arguments (at most 8 ranks)"); return VKR_ERR_INVALID_ARGUMENT; }
+  peer_epoch_begin_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ctrl, flags, count, self, (unsigned long long)timeout_ms * 1000000ull);
+  return check_launch("peer_epoch_begin_kernel");
+}
+
+extern "C" int vkr_peer_epoch_end(uint32_t* ctrl, uint32_t* const* remote_flags, uint32_t count, void* stream) {
+  if (!ctrl || !remote_flags || count == 0 || count > 8) { set_error("peer_epoch_end: bad arguments (at most 8 ranks)"); return VKR_ERR_INVALID_ARGUMENT; }
+  PeerFlags f;
+  for (uint32_t i = 0; i < 8; i++) f.p[i] = i < count ? remote_flags[i] : nullptr;
+  peer_epoch_end_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(ctrl, f, count);
+  return check_launch("peer_epoch_end_kernel");
 }
 
 extern "C" int vkr_peer_wait_failed(void) {

@@ -78,7 +78,7 @@ __device__ __forceinline__ void blur_accumulate(BlurPx& s, const BlurTap& t, f2 
 
 template <bool SAME, bool LAYERED>
 __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0, const BlurK* __restrict__ kv, LaunchX lx, Dim dim, Mip depth1, Mip normal_tex, Mip refl,
-                                                           Mip material_tex, Mip history, Mip velocity, Mip prev_depth1, Mip out, const float* __restrict__ srgb) {
+                                                           Mip material_tex, Mip history, Mip velocity, Mip prev_depth1, Mip out, const float* __restrict__ srgb, PeerOut po) {
   extern __shared__ float4 s_blur[];
   float4* const sA = s_blur;                          // {nx, nx' | ny, ny'}
   float4* const sB = sA + BLUR_PLANE;                 // {nz, nz' | depth, depth'}
@@ -315,7 +315,12 @@ __global__ void __launch_bounds__(256, BLUR_MIN_CTAS) sssr_blur_kernel(BlurK k0,
       f3 hc = mk3(wsum(a4.x, b4.x, c4.x, d4.x, t), wsum(a4.y, b4.y, c4.y, d4.y, t), wsum(a4.z, b4.z, c4.z, d4.z, t));
       color = mk3(fmaf(0.1f, color.x - hc.x, hc.x), fmaf(0.1f, color.y - hc.y, hc.y), fmaf(0.1f, color.z - hc.z, hc.z));   // mix(history, colour, 0.1)
     }
-    *((uint32_t*)(out.p + (size_t)py * out.pitch) + px) = pack_rgba8unorm(color.x, color.y, color.z, 0.f);
+    const uint32_t texel = pack_rgba8unorm(color.x, color.y, color.z, 0.f);
+    uint32_t* const dst = (uint32_t*)(out.p + (size_t)py * out.pitch) + px;
+    *dst = texel;
+#pragma unroll
+    for (int i = 0; i < 7; i++)                                                            // fused gather: the same texel into the peers' arrays (NVLink stores)
+      if (i < po.n) *(uint32_t*)((unsigned char*)dst + po.d[i]) = texel;
   }
 }
 
@@ -346,7 +351,7 @@ extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, c
     return VKR_ERR_SIZE_MISMATCH;
   }
   ExtInfo x;
-  int rc = resolve_ext(ext, out_blurred->height, BLUR_TH, &x, "sssr_blur");
+  int rc = resolve_ext(ext, out_blurred->height, BLUR_TH, &x, "sssr_blur", true);
   if (rc) return rc;
   for (int i = 0; i < x.layers; i++)
     if (!(p[i].max_roughness >= 0.f && p[i].max_roughness <= 1.f)) {   // radius bound r <= 11 assumes sigma <= 4
@@ -387,7 +392,7 @@ extern "C" int vkr_sssr_blur_ex(const VkrBlurParams* p, const VkrImage* depth, c
   }
   kern<<<grid, 256, BLUR_SMEM_BYTES, st>>>(k, kv, LaunchX{x.yb0}, make_dim(out_blurred->width, out_blurred->height), make_mip(depth, 1, x, 0), make_mip(normal, 0, x, 1),
                              make_mip(reflections, 0, x, 2), make_mip(material, 0, x, 3), make_mip(history, 0, x, 4), make_mip(dvelocity, 0, x, 5),
-                             make_mip(prev_depth, 1, x, 6), make_mip(out_blurred, 0, x, 7), srgb);
+                             make_mip(prev_depth, 1, x, 6), make_mip(out_blurred, 0, x, 7), srgb, x.peers());
   return check_launch("sssr_blur_kernel");
 }
 

@@ -473,7 +473,8 @@ def taa_resolve(p, history, prev_depth, depth, velocity, color, out, stream=None
 # ---- extended launches: array layers and row windows (include/vkr_passes.h VkrLaunchExt) ---------------
 class LaunchExt(C.Structure):
     _fields_ = [("layers", C.c_uint32), ("row_begin", C.c_uint32), ("row_end", C.c_uint32), ("flags", C.c_uint32), ("layer_stride", C.c_uint64 * 10),
-                ("params_scratch", C.c_void_p), ("first_param", C.c_uint32), ("reserved", C.c_uint32)]
+                ("params_scratch", C.c_void_p), ("first_param", C.c_uint32), ("reserved", C.c_uint32),
+                ("peer_count", C.c_uint32), ("reserved2", C.c_uint32), ("peer_delta", C.c_int64 * 7)]
 
 
 PARAMS_SCRATCH_STRIDE = 256
@@ -520,6 +521,25 @@ class ImageArray:
         self.desc.base = self.buf.data_ptr()
         self.nbytes = nbytes
 
+    @classmethod
+    def over(cls, buf, width, height, fmt, mips=1, layers=1):
+        """An ImageArray laid out over the start of an existing uint8 tensor (e.g. a slice of a peer-exported slab)."""
+        a = cls.__new__(cls)
+        a.desc = VkrImage()
+        nbytes = int(lib.vkr_image_layout(width, height, fmt, mips, C.byref(a.desc)))
+        a.layer_stride = (nbytes + 255) & ~255
+        if nbytes == 0 or buf.numel() < a.layer_stride * layers:
+            raise VkrError("ImageArray.over: bad layout or buffer too small")
+        a.layers, a.width, a.height, a.format, a.mips = layers, width, height, fmt, mips
+        a.device, a.buf, a.nbytes = buf.device, buf[:a.layer_stride * layers], nbytes
+        a.desc.base = a.buf.data_ptr()
+        return a
+
+    @staticmethod
+    def array_bytes(width, height, fmt, mips=1, layers=1):
+        d = VkrImage()
+        return ((int(lib.vkr_image_layout(width, height, fmt, mips, C.byref(d))) + 255) & ~255) * layers
+
     @property
     def ptr(self):
         return C.byref(self.desc)
@@ -544,7 +564,13 @@ class LayerRange:
         self.desc = VkrImage.from_buffer_copy(arr.desc)
         self.desc.base = arr.desc.base + first * arr.layer_stride
         self.layer_stride, self.layers = arr.layer_stride, count
+        self.nbytes = arr.nbytes
+        self.buf = arr.buf[first * arr.layer_stride:(first + count) * arr.layer_stride]     # a range of a range works too
+        self.device, self.width, self.height, self.format, self.mips = arr.device, arr.width, arr.height, arr.format, arr.mips
         self._keep = arr
+
+    def layer(self, i):
+        return ImageArray.layer(self, i)
 
     @property
     def ptr(self):
@@ -554,9 +580,14 @@ class LayerRange:
 EXT_PREPARE_ONLY, EXT_PARAMS_PREPARED = 1, 2
 
 
-def make_ext(images, layers=1, rows=None, scratch=None, flags=0, first_param=0):
-    """VkrLaunchExt for a call whose VkrImage arguments are `images` (ImageArray or Image, in argument order)."""
+def make_ext(images, layers=1, rows=None, scratch=None, flags=0, first_param=0, peers=None):
+    """VkrLaunchExt for a call whose VkrImage arguments are `images` (ImageArray or Image, in argument order).
+    peers: byte offsets from the pass's output to the same array on other GPUs (fused gather; blur and accumulate only)."""
     e = LaunchExt()
+    if peers:
+        e.peer_count = len(peers)
+        for i, d in enumerate(peers):
+            e.peer_delta[i] = int(d)
     e.layers = layers
     e.first_param = first_param
     e.flags = flags

@@ -128,3 +128,77 @@ class PeerGather:
         self.slab.close(barrier)
         if fails:
             raise PeerWaitTimeout(f"{fails} peer wait(s) timed out on rank {self.rank}: gathered blocks were stale")
+
+
+class FusedGather:
+    """The gather fused into the kernels that produce the results (VkrLaunchExt.peer_delta, include/vkr_passes.h): every rank holds
+    the FULL result arrays — `names` x 2 (ping-pong) array images of n_units layers — in a cudaIpc-shared slab; a rank's passes
+    write its own layers [first, end) and store every texel into the same address of every peer's slab as well (NVLink stores from
+    the producing kernel: no collective, no copy engine, no SMs taken from the passes).  Ordering is the epoch protocol of
+    include/vkr_peer.h: begin(stream) before the frame's writers, end(stream) after them; both read the epoch from device memory,
+    so a frame containing them replays as a CUDA graph.
+
+    Consumer rule: read the gathered arrays of epoch k (gathered(k, stream)) on a stream ordered before this rank's end() of k + 1.
+    The arrays of epoch k live in slot k & 1."""
+
+    def __init__(self, n_units, specs, rank, world, allgather_bytes, device, timeout_ms=4000):
+        """specs: {name: (width, height, format)} of the per-unit result images."""
+        assert world <= 8, "the epoch kernels handle at most 8 ranks"
+        self.n_units, self.rank, self.world, self.timeout = n_units, rank, world, timeout_ms
+        self.device = torch.device(device)
+        self.first, self.end_unit = shard_range(n_units, world, rank)
+        sizes = {n: vkr.ImageArray.array_bytes(w, h, f, 1, n_units) for n, (w, h, f) in specs.items()}
+        self.slab = PeerSlab(2 * sum(sizes.values()) + 256, self.device)
+        assert world * 4 + 4 <= PeerSlab.FLAG_BYTES
+        self.slab.tensor.zero_()                       # flags, epoch word and the arrays (histories start at zero) ...
+        torch.cuda.synchronize(self.device)            # ... before anybody can learn this slab's handle below
+        # flags[r] at slab + 4 r (written by rank r), this rank's epoch word behind them
+        self.ctrl = self.slab.ptr + 4 * 8
+        self.full = {n: [vkr.ImageArray.over(self.slab.carve(sizes[n]), *specs[n], 1, n_units) for _ in range(2)] for n in specs}
+        handles = allgather_bytes(self.slab.handle_bytes())
+        for r in range(world):
+            if r != rank:
+                self.slab.open_peer(r, handles[r])
+        self.peer_ranks = [r for r in range(world) if r != rank]
+        self.deltas = [self.slab.peers[r] - self.slab.ptr for r in self.peer_ranks]           # same layout on every rank
+        self._remote = (C.c_void_p * 8)(*[(self.slab.peers[r] + 4 * rank) if r != rank and r < world else None for r in range(8)])
+        self._fail_base = peer_wait_failures_total()
+        self.epoch = 0                                                                        # host-side count of end() calls
+
+    def own(self, name, slot):
+        """This rank's layers of the full array `name` in ping-pong slot 0 / 1, as the `_ex` entries take them."""
+        return vkr.LayerRange(self.full[name][slot], self.first, self.end_unit - self.first)
+
+    def begin(self, stream):
+        vkr.check(_P.vkr_peer_epoch_begin(C.c_void_p(self.ctrl), C.c_void_p(self.slab.ptr), self.world, self.rank, self.timeout, C.c_void_p(stream.cuda_stream)))
+
+    def end(self, stream):
+        """Call once per frame (also counts the epoch on the host; a CUDA-graph REPLAY of a frame that contains end() must be
+        followed by note_replayed())."""
+        vkr.check(_P.vkr_peer_epoch_end(C.c_void_p(self.ctrl), self._remote, self.world, C.c_void_p(stream.cuda_stream)))
+        self.epoch += 1
+
+    def note_replayed(self):
+        self.epoch += 1
+
+    def gathered(self, epoch, stream):
+        """Holds `stream` until every rank has finished writing `epoch` here; returns {name: (n_units, layer bytes) uint8 view}."""
+        st = C.c_void_p(stream.cuda_stream)
+        for r in self.peer_ranks:
+            vkr.check(_P.vkr_peer_wait(C.c_void_p(self.slab.ptr + 4 * r), epoch, self.timeout, st))
+        out = {}
+        for n, pair in self.full.items():
+            a = pair[epoch & 1]
+            out[n] = a.buf.view(a.layers, a.layer_stride)[:, :a.nbytes]
+        return out
+
+    def wait_failures(self):
+        return peer_wait_failures_total() - self._fail_base
+
+    def close(self, barrier=None):
+        torch.cuda.synchronize(self.device)
+        fails = self.wait_failures()
+        self.full = None
+        self.slab.close(barrier)
+        if fails:
+            raise PeerWaitTimeout(f"{fails} peer wait(s) timed out on rank {self.rank}: gathered arrays were stale")

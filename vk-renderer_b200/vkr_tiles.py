@@ -33,6 +33,8 @@ for _n, _a in [("vkr_peer_alloc", [C.c_uint64, C.POINTER(C.c_void_p)]), ("vkr_pe
                ("vkr_peer_push_rows", [vkr.IP, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
                ("vkr_peer_push_2d", [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p]),
                ("vkr_peer_signal", [C.c_void_p, C.c_uint32, C.c_void_p]), ("vkr_peer_wait", [C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
+               ("vkr_peer_epoch_begin", [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),
+               ("vkr_peer_epoch_end", [C.c_void_p, C.POINTER(C.c_void_p), C.c_uint32, C.c_void_p]),
                ("vkr_peer_wait_failed", [])]:
     getattr(_P, _n).restype = C.c_int
     getattr(_P, _n).argtypes = _a

@@ -83,7 +83,10 @@ def view_params(dp, frame, counter, jitter=0.0):
 class ViewBatch:
     """`views` independent w x h views on one device: images as arrays, passes batched over grid.z."""
 
-    def __init__(self, w, h, view_ids, device="cuda", luts=None, lut_size=1024, stream=None, param_sets=1):
+    def __init__(self, w, h, view_ids, device="cuda", luts=None, lut_size=1024, stream=None, param_sets=1, fused=None):
+        """fused: a vkr_gather.FusedGather whose units are ALL views of the job (this batch = its rank's shard): the two gathered
+        results (accumulated AO, blurred reflections) and their histories then live in its peer-shared full arrays, the blur and
+        the accumulate pass store every texel into every peer's copy as well, and passes() brackets them with the epoch kernels."""
         self.w, self.h, self.view_ids, self.V = w, h, list(view_ids), len(view_ids)
         self.device, self.stream = torch.device(device), stream
         V, w2, h2 = self.V, w // 2, h // 2
@@ -95,9 +98,16 @@ class ViewBatch:
         self.prev_depth.buf.view(torch.int32).fill_(0x00FFFFFF)           # clear_depth(prev_depth, 1.0), src/main.cpp:306
         self.dn, self.dv = A(w2, h2, vkr.R16G16_UNORM), A(w2, h2, vkr.R16G16_SFLOAT)
         self.raw, self.filtered = A(w2, h2, vkr.R16G16B16A16_SFLOAT), A(w2, h2, vkr.R16_SFLOAT)
-        self.accumulated_ao, self.accumulated_history = A(w2, h2, vkr.R16G16_SFLOAT), A(w2, h2, vkr.R16G16_SFLOAT)
         self.rays = A(w2, h2, vkr.R16G16B16A16_UNORM)
-        self.reflections, self.blurred, self.blurred_history = A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM)
+        self.reflections = A(w2, h2, vkr.R8G8B8A8_UNORM)
+        self.fused = fused
+        if fused is None:
+            self.accumulated_ao, self.accumulated_history = A(w2, h2, vkr.R16G16_SFLOAT), A(w2, h2, vkr.R16G16_SFLOAT)
+            self.blurred, self.blurred_history = A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM)
+        else:                                                 # epoch 1 (the first frame) writes slot 1, its history is slot 0
+            assert fused.end_unit - fused.first == V
+            self.accumulated_ao, self.accumulated_history = fused.own("accumulated_ao", 1), fused.own("accumulated_ao", 0)
+            self.blurred, self.blurred_history = fused.own("blurred", 1), fused.own("blurred", 0)
         self.halton = torch.from_numpy(vkr.halton23_seq(128)).to(device)
         if luts is None:
             self.pdf = vkr.Image(lut_size, lut_size, vkr.R32_SFLOAT, device=device)
@@ -144,6 +154,9 @@ class ViewBatch:
         G = len(lanes)
         if G > 1 and V < 2 * G:
             lanes, G = lanes[:1], 1
+        peers = self.fused.deltas if (self.fused is not None and not (flags & vkr.EXT_PREPARE_ONLY)) else None
+        if peers is not None:
+            self.fused.begin(st)                               # every peer is done with the buffers this frame overwrites
         if G > 1:
             ev0 = torch.cuda.Event()
             ev0.record(st)
@@ -153,11 +166,11 @@ class ViewBatch:
                 sm.wait_event(ev0)
 
             def R(a):                                          # the range's view of an array image (plain images are shared)
-                return vkr.LayerRange(a, first, count) if (G > 1 and isinstance(a, vkr.ImageArray)) else a
+                return vkr.LayerRange(a, first, count) if (G > 1 and isinstance(a, (vkr.ImageArray, vkr.LayerRange))) else a
 
-            def ext(imgs, slot):
+            def ext(imgs, slot, peers=None):
                 return vkr.make_ext(imgs, layers=count, scratch=self._scratch(param_set * 7 + slot), flags=flags if V > 1 else 0,
-                                    first_param=first if G > 1 else 0)
+                                    first_param=first if G > 1 else 0, peers=peers)
 
             depth, normal, velocity, dn, dv, material, albedo = (R(x) for x in (self.depth, self.normal, self.velocity, self.dn, self.dv, self.material, self.albedo))
             rays, raw, reflections, blurred, blurred_history = (R(x) for x in (self.rays, self.raw, self.reflections, self.blurred, self.blurred_history))
@@ -172,11 +185,11 @@ class ViewBatch:
                 s2.wait_event(ev)
             vkr.sssr_filter_ex(P["trace"], rays, depth, albedo, normal, material, reflections, ext([rays, depth, albedo, normal, material, reflections], 2), s2)
             vkr.sssr_blur_ex(P["blur"], depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred,
-                             ext([depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred], 3), s2)
+                             ext([depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred], 3, peers), s2)
             vkr.gtao_main_ex(P["gtao"], depth, normal, material, self.pdf, raw, ext([depth, normal, material, self.pdf, raw], 4), 1, sm)
             vkr.gtao_filter_ex(P["gtao"], depth, raw, filtered, ext([depth, raw, filtered], 5), 1, sm)
             vkr.gtao_accumulate_ex(P["accum"], depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history,
-                                   ext([depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history], 6), 1, sm)
+                                   ext([depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history], 6, peers), 1, sm)
             if fork:
                 ev2 = torch.cuda.Event()
                 ev2.record(s2)
@@ -185,6 +198,8 @@ class ViewBatch:
                 evg = torch.cuda.Event()
                 evg.record(sm)
                 st.wait_event(evg)
+        if peers is not None:
+            self.fused.end(st)                                 # this frame's results are complete on every rank
 
     def end_frame(self):
         """The remaps of src/main.cpp:416-420 that concern these passes."""
