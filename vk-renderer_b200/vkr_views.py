@@ -100,7 +100,7 @@ class ViewBatch:
         self.raw, self.filtered = A(w2, h2, vkr.R16G16B16A16_SFLOAT), A(w2, h2, vkr.R16_SFLOAT)
         self.rays = A(w2, h2, vkr.R16G16B16A16_UNORM)
         self.reflections = A(w2, h2, vkr.R8G8B8A8_UNORM)
-        self.fused = fused
+        self.fused, self._sync_stream = fused, None
         if fused is None:
             self.accumulated_ao, self.accumulated_history = A(w2, h2, vkr.R16G16_SFLOAT), A(w2, h2, vkr.R16G16_SFLOAT)
             self.blurred, self.blurred_history = A(w2, h2, vkr.R8G8B8A8_UNORM), A(w2, h2, vkr.R8G8B8A8_UNORM)
@@ -155,8 +155,18 @@ class ViewBatch:
         if G > 1 and V < 2 * G:
             lanes, G = lanes[:1], 1
         peers = self.fused.deltas if (self.fused is not None and not (flags & vkr.EXT_PREPARE_ONLY)) else None
+        ev_begin = None
         if peers is not None:
-            self.fused.begin(st)                               # every peer is done with the buffers this frame overwrites
+            # "every peer is done with the buffers this frame overwrites": only the frame's LAST kernels (blur, accumulate) need it,
+            # so the wait runs on a side branch forked here and joined just before them — off the frame's critical path
+            if self._sync_stream is None:
+                self._sync_stream = torch.cuda.Stream(device=self.device)
+            ev_fork = torch.cuda.Event()
+            ev_fork.record(st)
+            self._sync_stream.wait_event(ev_fork)
+            self.fused.begin(self._sync_stream)
+            ev_begin = torch.cuda.Event()
+            ev_begin.record(self._sync_stream)
         if G > 1:
             ev0 = torch.cuda.Event()
             ev0.record(st)
@@ -184,10 +194,14 @@ class ViewBatch:
                 ev.record(sm)
                 s2.wait_event(ev)
             vkr.sssr_filter_ex(P["trace"], rays, depth, albedo, normal, material, reflections, ext([rays, depth, albedo, normal, material, reflections], 2), s2)
+            if ev_begin is not None:
+                s2.wait_event(ev_begin)
             vkr.sssr_blur_ex(P["blur"], depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred,
                              ext([depth, normal, reflections, material, blurred_history, dv, prev_depth, blurred], 3, peers), s2)
             vkr.gtao_main_ex(P["gtao"], depth, normal, material, self.pdf, raw, ext([depth, normal, material, self.pdf, raw], 4), 1, sm)
             vkr.gtao_filter_ex(P["gtao"], depth, raw, filtered, ext([depth, raw, filtered], 5), 1, sm)
+            if ev_begin is not None and s2 is not sm:
+                sm.wait_event(ev_begin)
             vkr.gtao_accumulate_ex(P["accum"], depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history,
                                    ext([depth, prev_depth, filtered, accumulated_ao, dv, accumulated_history], 6, peers), 1, sm)
             if fork:
