@@ -404,7 +404,8 @@ def run_ours(args, rank, world):
                "d2h_bytes_per_step": d2h,
                "roofline": {"bound": "host<->device copies", "copy_only_ms_per_step": ms_copy, "copy_only_GBps": world * (h2d + d2h) / (ms_copy * 1e-3) / 1e9,
                             "frac": ms_copy / (ms_e2e / K),
-                            "how": "the step's H2D + D2H bytes alone, on the same pinned buffers and copy streams, every rank at once (measured in this run)"},
+                            "how": "the step's H2D + D2H bytes alone, on the same pinned buffers and copy streams, every rank at once (measured in this run); "
+                                   "frac >= 1 means the end-to-end step is at this bound (the two loops differ by the noise of a shared host fabric)"},
                "note": "pinned host G-buffer -> device (copy stream) -> vkr_app_bind_gbuffer -> render_frame -> TAA target -> pinned host "
                                                   "(read-back stream); three device G-buffers rotate so both PCIe directions overlap the chain"}
 
