@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-tiles-balance", dest="tiles_balance", action="store_false", help="tiles workload: keep the even row split")
     ap.add_argument("--probes-lanes", type=int, default=2, choices=[1, 2],
                     help="probes workload: 2 = SSR filter + blur on a second stream beside the GTAO passes inside the frame's CUDA graph")
-    ap.add_argument("--probes-groups", type=int, default=2,
+    ap.add_argument("--probes-groups", type=int, default=3,
                     help="probes workload: split a rank's views into this many layer ranges, each running its chain on its own streams inside the "
                          "frame's CUDA graph (independent views fill each other's launch gaps and tails)")
     ap.add_argument("--probes-gather", default="fused", choices=["allgather", "p2p", "fused", "none"],
