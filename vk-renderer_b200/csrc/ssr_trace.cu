@@ -18,11 +18,15 @@
 #endif
 namespace vkr {
 
+struct TraceDims { float ssx, ssy; };   // level-0 extent of the pyramid view as floats
+
 struct TraceK {
   Mat4 normal_mat;
   CamK cam;
   uint32_t frame_random;
   float max_roughness;
+  CamF camf;                           // make_camf(cam) and -2 * {aspect_tg, tg}, evaluated once on the host (same single roundings):
+  float m2at, m2tg;                    // constant-bank operands of the v2 march's horizon sample instead of per-step re-materialisation
 };
 
 // trace.comp:156-158, bit-defined (see oracle/passes_ssr.cpp rand_hash): unfused fp32 dot,
@@ -36,7 +40,7 @@ __device__ __forceinline__ float rand_hash(float u, float v) {
 
 template <bool LAYERED>
 __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
-                                                         const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
+                                                         const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb, TraceDims dims) {
   TraceK kl;
   unsigned long long poff = 0;                         // layer offset of the depth pyramid (one allocation per layer holds every mip)
   if (LAYERED) {
@@ -210,6 +214,18 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 #ifndef TRACE_CTA_ROWS
 #define TRACE_CTA_ROWS 8                /* 16 x TRACE_CTA_ROWS rays per CTA (one 16 x 2 strip per warp) */
 #endif
+#ifndef TRACE_FOLD_CAM
+#define TRACE_FOLD_CAM 1                /* 1: the horizon sample's camera products come from the kernel parameters (TraceK::camf) */
+#endif
+#ifndef TRACE_FOLD_T
+#define TRACE_FOLD_T 1                  /* 1: t to the cell's far planes as ONE FFMA per axis: ((cell + fo) * 2^m) * (1 / (res * dir)) + (c / dir) */
+#endif
+#ifndef TRACE_FOLD_Z
+#define TRACE_FOLD_Z 1                  /* 1: t to the depth plane as ONE FFMA, sz * (1 / dz) + (-oz / dz); for dz <= 0 the pair is (0, MAX_T) */
+#endif
+#ifndef TRACE_SS_PARAM
+#define TRACE_SS_PARAM 1                /* 1: the level-0 extent as floats in the kernel parameters (no per-step I2FP re-materialisation) */
+#endif
 namespace vkr {
 
 #define TR_MAGIC0 12582912.0f          /* 1.5 * 2^23 */
@@ -221,16 +237,22 @@ struct RayK {                          // per-ray constants of the march
   float fox, foy;                      // floor offsets (0 or 1)
   float cx, cy;                        // uv_offset - origin
   float t_exit;                        // the fast loops are valid while t < t_exit
+#if TRACE_FOLD_Z
+  float ozi;                           // -oz / dz (MAX_T with idz = 0 when dz <= 0: the depth plane is never the nearest)
+#endif
+#if TRACE_FOLD_T
+  float kx, ky, cxi, cyi;              // 1 / (res0 * direction), (uv_offset - origin) / direction; during the pinned loop cxi, cyi include fo * k
+#endif
 };
 
 // Horizon sample (trace.comp:258-262): v = reconstruct(uv, sz) - view_vec at the ray's CURRENT uv, h = max(h, n.v / |v|) if
 // |v| < 0.3.  |v| >= |v.z|, so a sample whose view z is 0.3 or more away is dropped before the rest is evaluated; a NaN sz
 // ("no sample owed") drops out at the same test.
-__device__ __forceinline__ void horizon_sample(const f3& vv, const f3& n, const CamF& camf, float px, float py, float sz, float& h) {
+__device__ __forceinline__ void horizon_sample(const f3& vv, const f3& n, const CamF& camf, float m2at, float m2tg, float px, float py, float sz, float& h) {
   const float z = linearize_fast(sz, camf);
   const float vz = z - vv.z;
   if (fabsf(vz) < 0.3f) {
-    const float vx = fmaf(fmaf(-2.0f * camf.aspect_tg, px, camf.aspect_tg), z, -vv.x), vy = fmaf(fmaf(-2.0f * camf.tg, py, camf.tg), z, -vv.y);
+    const float vx = fmaf(fmaf(m2at, px, camf.aspect_tg), z, -vv.x), vy = fmaf(fmaf(m2tg, py, camf.tg), z, -vv.y);
     const float d2 = fmaf(vz, vz, fmaf(vy, vy, vx * vx));
     if (d2 < 0.09f) h = fmaxf(h, fmaf(n.z, vz, fmaf(n.y, vy, n.x * vx)) * rsqrt_fast(d2));
   }
@@ -250,11 +272,22 @@ __device__ __forceinline__ bool fast_step(const RayK& r, const uint4* __restrict
     const uint32_t texel = (uint32_t)yi * L.z + (uint32_t)xi;                        // 32-bit index, widened once
     sz = d24_to_float(__ldg(base + texel));
   }
+#if TRACE_FOLD_T
+  // level 0: cell * k + (fo * k + c / dir), the bracket held in cxi / cyi.  Level m: (cell + fo) * 2^m = mx - (magic - fo * 2^m),
+  // and magic - 2^m is magic's bit pattern minus one: exact
+  const float qx = PINNED ? mx - TR_MAGIC0 : mx - __int_as_float(mb - (r.dx < 0 ? 0 : 1)), qy = PINNED ? my - TR_MAGIC0 : my - __int_as_float(mb - (r.dy < 0 ? 0 : 1));
+  const float tx = fmaf(qx, r.kx, r.cxi), ty = fmaf(qy, r.ky, r.cyi);
+#else
   const float p2 = PINNED ? 1.0f : __int_as_float(mb - (TR_MAGIC0_BITS - 0x3F800000));   // 2^m
   const float ex = fmaf(fmaf(p2, r.fox, mx - magic), rinvx0, r.cx), ey = fmaf(fmaf(p2, r.foy, my - magic), rinvy0, r.cy);   // xy_plane - origin
   const float tx = ex * r.idx, ty = ey * r.idy;
+#endif
+#if TRACE_FOLD_Z
+  const float tz = fmaf(sz, r.idz, r.ozi);
+#else
   float tz = (sz - r.oz) * r.idz;
   tz = r.dz > 0 ? tz : MAX_T_FLOAT;
+#endif
   const float t_min = fminf(fminf(tx, ty), tz);
   const bool above = sz > fmaf(t, r.dz, r.oz);
   skipped = above && (t_min != tz);
@@ -265,7 +298,7 @@ __device__ __forceinline__ bool fast_step(const RayK& r, const uint4* __restrict
 
 template <bool LAYERED>
 __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trace2_kernel(TraceK k0, const TraceK* __restrict__ kv, LaunchX lx, PyramidView P, Mip normal, Mip material,
-                                                          const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb) {
+                                                          const float4* __restrict__ halton, Mip pdf, Mip out_rays, Mip out_occl, const float* __restrict__ srgb, TraceDims dims) {
   __shared__ uint4 lvl[16];
   TraceK kl;
   unsigned long long poff = 0;
@@ -291,7 +324,13 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   const float tsx = (float)out_rays.w, tsy = (float)out_rays.h;
   const float su = ((float)px + 0.5f) / tsx, sv = ((float)py + 0.5f) / tsy;                  // :44
   const CamK cam = k.cam;
+#if TRACE_FOLD_CAM
+  const CamF camf = k.camf;
+  const float m2at = k.m2at, m2tg = k.m2tg;
+#else
   const CamF camf = make_camf(cam);
+  const float m2at = -2.0f * camf.aspect_tg, m2tg = -2.0f * camf.tg;
+#endif
 
   float roughness = sample_srgb8(material, su, sv, srgb).y;                                     // :49-53
   float mg = gmix(0.0f, k.max_roughness, roughness);
@@ -344,7 +383,11 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   }
 #endif
   // ---- hierarchical_raymarch_find_hor, trace.comp:206-268 ------------------------------------
+#if TRACE_SS_PARAM
+  const float ssx = dims.ssx, ssy = dims.ssy;
+#else
   const float ssx = (float)d0.w, ssy = (float)d0.h;
+#endif
   const float rinvx0 = 1.0f / ssx, rinvy0 = 1.0f / ssy;
   RayK r;
   r.ox = origin.x; r.oy = origin.y; r.oz = origin.z; r.dx = direction.x; r.dy = direction.y; r.dz = direction.z;
@@ -358,6 +401,13 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   const float uox = direction.x < 0 ? -(0.005f / ssx) : (0.005f / ssx), uoy = direction.y < 0 ? -(0.005f / ssy) : (0.005f / ssy);
   r.fox = direction.x < 0 ? 0.f : 1.f; r.foy = direction.y < 0 ? 0.f : 1.f;
   r.cx = uox - origin.x; r.cy = uoy - origin.y;
+#if TRACE_FOLD_Z
+  if (direction.z > 0) r.ozi = -origin.z * r.idz; else { r.idz = 0.0f; r.ozi = MAX_T_FLOAT; }
+#endif
+#if TRACE_FOLD_T
+  r.kx = rinvx0 * r.idx; r.ky = rinvy0 * r.idy;
+  r.cxi = fmaf(r.fox, r.kx, r.cx * r.idx); r.cyi = fmaf(r.foy, r.ky, r.cy * r.idy);       // pinned-loop form
+#endif
   {                                                    // the ray stays inside [2^-20, 1 - 2^-20]^2 while t < t_exit
     const float eps = 9.5367431640625e-07f;
     const float bx = direction.x < 0 ? eps : 1.0f - eps, by = direction.y < 0 ? eps : 1.0f - eps;
@@ -382,16 +432,19 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   bool done = false;
   for (; i < 15 && t < r.t_exit; ++i) {
     const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
-    horizon_sample(view_vec, pixel_normal, camf, cpx, cpy, owed, h);
+    horizon_sample(view_vec, pixel_normal, camf, m2at, m2tg, cpx, cpy, owed, h);
     bool skipped;
     const bool above = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, cpx, cpy, t, skipped, owed);
     if (!above) { done = true; break; }
   }
+#if TRACE_FOLD_T
+  r.cxi = fmaf(r.dx < 0 ? 0.f : -1.f, r.kx, r.cxi); r.cyi = fmaf(r.dy < 0 ? 0.f : -1.f, r.ky, r.cyi);   // back to c / dir for the levels above 0
+#endif
   if (!done && i >= 15) {
     float magic = TR_MAGIC0;
     while (i < 80 && magic >= TR_MAGIC0 && t < r.t_exit) {
       const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
-      if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, cpx, cpy, owed, h);
+      if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, m2at, m2tg, cpx, cpy, owed, h);
       bool skipped; float sz;
       fast_step<false>(r, lvl, ssx, ssy, rinvx0, rinvy0, magic, cpx, cpy, t, skipped, sz);
       magic = __int_as_float(__float_as_int(magic) + (skipped ? 0x00800000 : -0x00800000));
@@ -405,7 +458,7 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   while (!done && i < 80 && mip >= 0) {
     const float S = __int_as_float((127 + mip) << 23), s = __int_as_float((127 - mip) << 23);   // 2^mip, 2^-mip
     const float pxx = fmaf(t, r.dx, r.ox), pyy = fmaf(t, r.dy, r.oy);
-    if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, pxx, pyy, owed, h);
+    if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, m2at, m2tg, pxx, pyy, owed, h);
     const float mpx = (ssx * s) * pxx, mpy = (ssy * s) * pyy;
     const int xi = (int)mpx, yi = (int)mpy;
     const uint4 L = lvl[min(mip, 15)];
@@ -424,10 +477,18 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
     float sz = 0.0f;
     if (!oobx && !ooby)
       sz = d24_to_float(__ldg((const uint32_t*)(((unsigned long long)L.y << 32) | L.x) + ((uint32_t)yi * L.z + (uint32_t)xi)));
+#if TRACE_FOLD_T
+    const float tx = fmaf((floorf(mpx) + (r.dx < 0 ? 0.f : 1.f)) * S, r.kx, r.cxi), ty = fmaf((floorf(mpy) + (r.dy < 0 ? 0.f : 1.f)) * S, r.ky, r.cyi);
+#else
     const float ex = fmaf((floorf(mpx) + r.fox) * S, rinvx0, r.cx), ey = fmaf((floorf(mpy) + r.foy) * S, rinvy0, r.cy);
     const float tx = ex * r.idx, ty = ey * r.idy;
+#endif
+#if TRACE_FOLD_Z
+    const float tz = fmaf(sz, r.idz, r.ozi);
+#else
     float tz = (sz - r.oz) * r.idz;
     tz = r.dz > 0 ? tz : MAX_T_FLOAT;
+#endif
     const float t_min = fminf(fminf(tx, ty), tz);
     const bool above = sz > fmaf(t, r.dz, r.oz);
     const bool skipped = above && (t_min != tz);
@@ -437,7 +498,7 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
     owed = mip <= 1 ? sz : NOTHING;
   }
   const f3 out_ray = mk3(fmaf(t, r.dx, r.ox), fmaf(t, r.dy, r.oy), fmaf(t, r.dz, r.oz));
-  if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, out_ray.x, out_ray.y, owed, h);
+  if (owed == owed) horizon_sample(view_vec, pixel_normal, camf, m2at, m2tg, out_ray.x, out_ray.y, owed, h);
   bool valid_hit = true;                              // (i <= max) is always true, App. A.6 #8
 
   {                                                                                              // :94-99
@@ -506,6 +567,9 @@ static TraceK make_trace_k(const VkrTraceParams* p) {
   k.normal_mat = make_mat(p->normal_mat);
   k.cam = make_cam(p->fovy, p->aspect, p->znear, p->zfar);
   k.frame_random = p->frame_random; k.max_roughness = p->max_roughness;
+  k.camf.aspect_tg = k.cam.aspect * k.cam.tg; k.camf.tg = k.cam.tg;      // make_camf's roundings: one multiply / subtract each
+  k.camf.nf = k.cam.znear * k.cam.zfar; k.camf.fmn = k.cam.zfar - k.cam.znear; k.camf.zfar = k.cam.zfar;
+  k.m2at = -2.0f * k.camf.aspect_tg; k.m2tg = -2.0f * k.cam.tg;
   return k;
 }
 
@@ -554,7 +618,8 @@ extern "C" int vkr_sssr_trace_ex(const VkrTraceParams* p, const VkrImage* depth,
 #endif
   const int threads = TRACE_V2 ? 16 * TRACE_CTA_ROWS : 128;
   kern<<<grid, threads, 0, st>>>(k, kv, LaunchX{x.yb0}, P, make_mip(dnormal, 0, x, 1), make_mip(material, 0, x, 2), (const float4*)halton_vec4x128,
-                             make_mip(pdf_lut, 0, x, 3), make_mip(out_rays, 0, x, 4), make_mip(out_occlusion, 0, x, 5), srgb);
+                             make_mip(pdf_lut, 0, x, 3), make_mip(out_rays, 0, x, 4), make_mip(out_occlusion, 0, x, 5), srgb,
+                             TraceDims{(float)P.mip[0].w, (float)P.mip[0].h});
   return check_launch("sssr_trace_kernel");
 }
 
