@@ -223,6 +223,9 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 #ifndef TRACE_FOLD_Z
 #define TRACE_FOLD_Z 1                  /* 1: t to the depth plane as ONE FFMA, sz * (1 / dz) + (-oz / dz); for dz <= 0 the pair is (0, MAX_T) */
 #endif
+#ifndef TRACE_PINNED_FLAGLESS
+#define TRACE_PINNED_FLAGLESS 0
+#endif
 #ifndef TRACE_SS_PARAM
 #define TRACE_SS_PARAM 1                /* 1: the level-0 extent as floats in the kernel parameters (no per-step I2FP re-materialisation) */
 #endif
@@ -429,6 +432,17 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
   int mip = 0;
   // Steps 0..14 stay on level 0 (:250).  A ray found below the surface there never moves again (t frozen, the same
   // horizon sample every step) and leaves the march at step 15: it is finished.
+#if TRACE_PINNED_FLAGLESS
+  bool above0 = true;                                  // one loop condition, no exit flags to keep in predicates
+  while (above0 && i < 15 && t < r.t_exit) {
+    const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
+    horizon_sample(view_vec, pixel_normal, camf, m2at, m2tg, cpx, cpy, owed, h);
+    bool skipped;
+    above0 = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, cpx, cpy, t, skipped, owed);
+    ++i;
+  }
+  bool done = !above0;                                 // (i counts the finishing step too; it is not read again for a finished ray)
+#else
   bool done = false;
   for (; i < 15 && t < r.t_exit; ++i) {
     const float cpx = fmaf(t, r.dx, r.ox), cpy = fmaf(t, r.dy, r.oy);
@@ -437,6 +451,7 @@ __global__ void __launch_bounds__(16 * TRACE_CTA_ROWS, TRACE_MIN_CTAS) sssr_trac
     const bool above = fast_step<true>(r, lvl, ssx, ssy, rinvx0, rinvy0, TR_MAGIC0, cpx, cpy, t, skipped, owed);
     if (!above) { done = true; break; }
   }
+#endif
 #if TRACE_FOLD_T
   r.cxi = fmaf(r.dx < 0 ? 0.f : -1.f, r.kx, r.cxi); r.cyi = fmaf(r.dy < 0 ? 0.f : -1.f, r.ky, r.cyi);   // back to c / dir for the levels above 0
 #endif
