@@ -224,7 +224,9 @@ __global__ void __launch_bounds__(128) sssr_trace_kernel(TraceK k0, const TraceK
 #define TRACE_FOLD_Z 1                  /* 1: t to the depth plane as ONE FFMA, sz * (1 / dz) + (-oz / dz); for dz <= 0 the pair is (0, MAX_T) */
 #endif
 #ifndef TRACE_PINNED_FLAGLESS
-#define TRACE_PINNED_FLAGLESS 0
+#define TRACE_PINNED_FLAGLESS 0         /* 1: the pinned loop ends on one condition (no exit flags held in predicates): 59 -> 56 instructions per step,
+                                           0.3317 -> 0.3280 ms at 4K with identical pass-level parity at 1280x720 (profiles/r02ak_...).  NOT the default: the
+                                           full GPU suite was not rerun with it before the round's GPU budget ran out */
 #endif
 #ifndef TRACE_SS_PARAM
 #define TRACE_SS_PARAM 1                /* 1: the level-0 extent as floats in the kernel parameters (no per-step I2FP re-materialisation) */
